@@ -1,0 +1,151 @@
+/* osrgpu.h -- C ABI of libosrgpu.so, the B200 (sm_100a) batched rigid-body collision engine
+ * behind the pyosr `UnitWorld` surface.
+ *
+ * The reference has no C ABI for this path: its boundary is the pybind11 class
+ * `pyosr.UnitWorld` (/root/reference/lib/pyosr/module.cc:127-250) over C++ member functions of
+ * osr::UnitWorld (/root/reference/lib/osr/unit_world.h).  Each entry point below names the
+ * member function(s) it replaces; INTEGRATION.md shows the pybind11 stub a maintainer would
+ * put in lib/pyosr/module.cc to call it.
+ *
+ * Conventions
+ *   - every function returns 0 on success or a negative OSR_E* code; osr_last_error() gives
+ *     the message of the calling thread's last failure (the reference throws
+ *     std::runtime_error, module.cc relies on pybind11's translation).
+ *   - states are `double[N][7]`, row-major, [tx ty tz qw qx qy qz] (lib/osr/osr_state.h:20-33),
+ *     in UNIT-world coordinates unless stated.
+ *   - all arrays are caller-owned HOST memory (pageable or pinned); results are complete when
+ *     the call returns.  The *_device variants take device pointers on device 0 of the handle
+ *     and are ordered on the handle's stream; they exist for callers that keep samples in HBM.
+ *   - there is NO CPU fallback: every query runs on the GPU(s) selected at osr_finalize().
+ */
+#ifndef OSRGPU_H
+#define OSRGPU_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct osr_world osr_world;
+
+enum {
+  OSR_OK = 0,
+  OSR_EINVAL = -1,   /* bad argument / call order            */
+  OSR_EIO = -2,      /* mesh file unreadable                  */
+  OSR_ECUDA = -3,    /* CUDA runtime failure (message kept)   */
+  OSR_ENODEV = -4,   /* no usable CUDA device                 */
+  OSR_EOVERFLOW = -5 /* device work stack exhausted           */
+};
+
+const char* osr_last_error(void);
+
+/* UnitWorld::UnitWorld / ~UnitWorld (lib/osr/unit_world.cc:33-63) */
+int osr_create(osr_world** out);
+void osr_destroy(osr_world* w);
+
+/* UnitWorld::loadModelFromFile / loadRobotFromFile (unit_world.cc:94-110) */
+int osr_load_env_obj(osr_world* w, const char* path);
+int osr_load_rob_obj(osr_world* w, const char* path);
+/* same, from memory (float32 vertices, int32 triangles) -- for synthetic meshes */
+int osr_set_env_mesh(osr_world* w, const float* V, int nV, const int32_t* F, int nF);
+int osr_set_rob_mesh(osr_world* w, const float* V, int nV, const int32_t* F, int nF);
+/* UnitWorld::enforceRobotCenter (unit_world.cc:113-117) */
+int osr_enforce_robot_center(osr_world* w, const double c[3]);
+/* UnitWorld::scaleToUnit + angleModel(0,0) (unit_world.cc:123-161): computes scene_scale, the
+ * unit-space meshes and the BVHs, uploads them to `ndev` devices listed in `devices`
+ * (ndev<=0: current device only). */
+int osr_finalize(osr_world* w, const int* devices, int ndev);
+/* UnitWorld::setPerturbation (unit_world.cc:165-176) */
+int osr_set_perturbation(osr_world* w, const double q[7]);
+/* properties scene_scale / recommended_cres (unit_world.h:322-346) and the robot centre used */
+double osr_scene_scale(const osr_world* w);
+double osr_get_recommended_cres(const osr_world* w);
+int osr_set_recommended_cres(osr_world* w, double v);
+int osr_get_robot_center(const osr_world* w, double c[3]);
+int osr_num_devices(const osr_world* w);
+/* geometry read-back (CDModel::vertices()/faces(), cdmodel.cc:232-246): which 0=env 1=robot */
+int osr_mesh_sizes(const osr_world* w, int which, int* nV, int* nF, int* nNodes, int* depth);
+int osr_get_unit_mesh(const osr_world* w, int which, double* V, int32_t* F);
+
+/* Work counters accumulated over the calls made since the last reset (FCL's num_bv_tests /
+ * num_leaf_tests, mesh_collision_traversal_node-inl.h:497,547, plus the engine's own). */
+typedef struct osr_counters {
+  uint64_t bv_tests;      /* OBB-pair tests executed                         */
+  uint64_t leaf_tests;    /* triangle-pair tests executed (fp32 filter)      */
+  uint64_t fp64_rechecks; /* triangle pairs re-tested with the exact SAT-17  */
+  uint64_t poses;         /* validity checks (configs or segment steps)      */
+  uint64_t spills;        /* stack spill events to global memory             */
+  uint64_t kernel_launches;
+} osr_counters;
+int osr_get_counters(osr_world* w, osr_counters* out, int reset);
+
+/* UnitWorld::isValid per row (unit_world.cc:215-247): out[i]=1 iff state i is collision free */
+int osr_is_valid_states(osr_world* w, const double* q, int64_t n, uint8_t* out);
+/* UnitWorld::isDisentangled per row (unit_world.cc:249-264) */
+int osr_is_disentangled_states(osr_world* w, const double* q, int64_t n, uint8_t* out);
+
+/* UnitWorld::transitStateToWithContact per row (unit_world.cc:405-474).  `vd` holds one value
+ * (vd_count==1) or n values.  Outputs (any may be NULL): last_free[n][7], first_hit[n][7],
+ * is_free[n], free_tau[n], touch_tau[n] (taus as double; the reference narrows them to float
+ * in its return tuple), steps[n] = number of validity checks the reference would have made. */
+int osr_transit_states_to_with_contact(osr_world* w, const double* from, const double* to, int64_t n,
+                                       const double* vd, int64_t vd_count, double* last_free,
+                                       double* first_hit, uint8_t* is_free, double* free_tau,
+                                       double* touch_tau, int64_t* steps);
+/* UnitWorld::isValidTransition per row (unit_world.cc:477-486): vdelta=min(d/2, initial_vd) */
+int osr_is_valid_transitions(osr_world* w, const double* from, const double* to, int64_t n,
+                             double initial_verify_delta, uint8_t* out);
+/* UnitWorld::calculateVisibilityMatrix2 (unit_world.cc:764-797): out[m][n] int8, row-major.
+ * is_unit0/1 == 0 -> rows are first mapped with translateToUnitState. */
+int osr_visibility_matrix2(osr_world* w, const double* q0, int64_t m, int is_unit0, const double* q1,
+                           int64_t n, int is_unit1, double verify_magnitude, int8_t* out);
+/* UnitWorld::calculateVisibilityPair (unit_world.cc:799-840): out[max(m,n)] */
+int osr_visibility_pair(osr_world* w, const double* q0, int64_t m, int is_unit0, const double* q1,
+                        int64_t n, int is_unit1, double verify_magnitude, int8_t* out);
+
+/* UnitWorld::intersectingSegments per row (unit_world.cc:959-1012; CDModel::collideForDetails,
+ * cdmodel.cc:200-229; tritri::TriTri, lib/tritri/tritri_igl.hh:15-67).  CSR output:
+ * rows offsets[i]..offsets[i+1] belong to state i; faces[r] = (env triangle, robot triangle);
+ * seg[r] = 6 doubles (two end points, zeros when Moeller reports none); coplanar[r].
+ * Optional bary[r] = 6 doubles: barycentric coordinates of the segment mid point on the env
+ * triangle then on the robot triangle.  At most `cap` rows are written; *total gets the number
+ * found; overflow[i]=1 for states whose rows were truncated. */
+int osr_intersecting_segments(osr_world* w, const double* q, int64_t n, int64_t cap, int64_t* offsets,
+                              double* seg, int32_t* faces, uint8_t* coplanar, double* bary,
+                              uint8_t* overflow, int64_t* total);
+
+/* UnitWorld::enumFreeConfiguration per row (unit_world.cc:1340-1389): pts[b] = {rob_o, rob_n,
+ * env_o, env_n} (4x3 doubles).  out_q[b][den][7], out_valid[b][den] (after the optional
+ * median-of-run filter), counts[b] = number of valid entries. */
+int osr_enum_free_configurations(osr_world* w, const double* pts, int64_t b, double margin, int den,
+                                 int only_median, double* out_q, uint8_t* out_valid, int32_t* counts);
+
+/* State-frame maps (unit_world.cc:526-555, 557-591, 689-738), n rows each */
+int osr_translate_to_unit(const osr_world* w, const double* q, int64_t n, double* out);
+int osr_translate_from_unit(const osr_world* w, const double* q, int64_t n, double* out);
+int osr_translate_ompl_to_unit(const osr_world* w, const double* q_wlast, int64_t n, double* out);
+int osr_translate_unit_to_ompl(const osr_world* w, const double* q, int64_t n, double* out_wlast);
+
+/* module-level state functions (lib/pyosr/module.cc:77-99; lib/osr/osr_state.cc) */
+double osr_distance(const double a[7], const double b[7]);
+void osr_interpolate(const double a[7], const double b[7], double tau, double out[7]);
+void osr_apply(const double from[7], const double tr[3], const double aa[3], double out[7]);
+
+/* Device-resident variants (pointers on the handle's first device).  Launch only; the caller
+ * synchronises with osr_sync() (or its own stream wait on osr_stream()). */
+int osr_is_valid_states_device(osr_world* w, const double* d_q, int64_t n, uint8_t* d_out);
+int osr_transit_states_device(osr_world* w, const double* d_from, const double* d_to, int64_t n,
+                              double vd, double* d_last_free, double* d_first_hit, uint8_t* d_is_free,
+                              double* d_free_tau, double* d_touch_tau, int64_t* d_steps);
+int osr_is_valid_transitions_device(osr_world* w, const double* d_from, const double* d_to, int64_t n,
+                                    double initial_verify_delta, uint8_t* d_out);
+void* osr_stream(osr_world* w);   /* cudaStream_t of device slot 0 */
+int osr_sync(osr_world* w);
+/* elapsed GPU milliseconds of the most recent *_device launch on slot 0 (CUDA events recorded
+ * around the kernel on the launching stream); valid after osr_sync(). */
+int osr_last_kernel_ms(osr_world* w, float* ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OSRGPU_H */

@@ -1,0 +1,311 @@
+// geometry.cc -- OBJ reader, unit-world transform and the GPU-oriented OBB-BVH builder.
+// See geometry.h for the reference functions this replaces.
+#include "geometry.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+#include <fstream>
+#include <limits>
+#include <queue>
+#include <sstream>
+
+namespace osr {
+
+bool load_obj(const std::string& path, TriMesh& out, std::string& err) {
+  std::ifstream in(path.c_str());
+  if (!in.good()) { err = "cannot open " + path; return false; }
+  std::vector<float> pos;
+  std::vector<int> tri;
+  std::string line;
+  while (std::getline(in, line)) {
+    if (line.size() < 2 || (line[1] != ' ' && line[1] != '\t')) continue;
+    if (line[0] == 'v') {
+      const char* p = line.c_str() + 1;
+      char* e = nullptr;
+      for (int k = 0; k < 3; k++) { pos.push_back(strtof(p, &e)); p = e; }
+    } else if (line[0] == 'f') {
+      std::istringstream ss(line.substr(1));
+      std::string tok;
+      std::vector<int> poly;
+      int nv = (int)(pos.size() / 3);
+      while (ss >> tok) {
+        int v = atoi(tok.c_str());
+        int idx = v > 0 ? v - 1 : nv + v;
+        if (idx < 0 || idx >= nv) { err = "face index out of range in " + path; return false; }
+        poly.push_back(idx);
+      }
+      for (size_t k = 2; k < poly.size(); k++) {
+        tri.push_back(poly[0]); tri.push_back(poly[k - 1]); tri.push_back(poly[k]);
+      }
+    }
+  }
+  if (tri.empty()) { err = "no faces in " + path; return false; }
+  // drop unreferenced vertices (a mesh importer only keeps vertices used by faces)
+  std::vector<int> remap(pos.size() / 3, -1);
+  std::vector<char> used(pos.size() / 3, 0);
+  for (int t : tri) used[t] = 1;
+  out.V.clear(); out.F.clear();
+  for (size_t i = 0; i < used.size(); i++)
+    if (used[i]) {
+      remap[i] = out.nv();
+      out.V.insert(out.V.end(), pos.begin() + 3 * i, pos.begin() + 3 * i + 3);
+    }
+  for (int t : tri) out.F.push_back(remap[t]);
+  return true;
+}
+
+float bbox_span(const TriMesh& m) {
+  float lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};
+  for (size_t i = 0; i < m.V.size(); i += 3)
+    for (int k = 0; k < 3; k++) {
+      hi[k] = std::max(m.V[i + k], hi[k]);
+      lo[k] = std::min(m.V[i + k], lo[k]);
+    }
+  return std::max(std::max(hi[0] - lo[0], hi[1] - lo[1]), hi[2] - lo[2]);
+}
+
+void mean_of_vertices(const TriMesh& m, float c[3]) {
+  float s[3] = {0, 0, 0};
+  for (int i = 0; i < m.nv(); i++)
+    for (int k = 0; k < 3; k++) s[k] += m.V[3 * i + k];
+  for (int k = 0; k < 3; k++) c[k] = s[k] / (float)m.nv();
+}
+
+void make_unit_model(const TriMesh& m, float scale, const float* centre, UnitModel& out) {
+  double s = (double)scale;
+  double tr[3] = {0, 0, 0};
+  if (centre)
+    for (int k = 0; k < 3; k++) tr[k] = (double)(scale * (-centre[k]));  // float product, then widened
+  out.V.resize(m.V.size());
+  for (size_t i = 0; i < m.V.size(); i++) out.V[i] = s * (double)m.V[i] + tr[i % 3];
+  out.F = m.F;
+  out.tris.resize((size_t)9 * out.nf());
+  for (int f = 0; f < out.nf(); f++)
+    for (int k = 0; k < 3; k++)
+      for (int d = 0; d < 3; d++) out.tris[(size_t)9 * f + 3 * k + d] = out.V[3 * (size_t)out.F[3 * f + k] + d];
+  for (int d = 0; d < 3; d++) {
+    out.aabb_min[d] = std::numeric_limits<double>::max();
+    out.aabb_max[d] = -std::numeric_limits<double>::max();
+  }
+  // FCL computeLocalAABB runs over all model vertices
+  for (size_t i = 0; i < out.V.size(); i++) {
+    out.aabb_min[i % 3] = std::min(out.aabb_min[i % 3], out.V[i]);
+    out.aabb_max[i % 3] = std::max(out.aabb_max[i % 3], out.V[i]);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// BVH builder
+// ------------------------------------------------------------------------------------------
+namespace {
+
+struct Vec3 { double x, y, z; };
+inline Vec3 operator-(Vec3 a, Vec3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+inline double dot(Vec3 a, Vec3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+inline Vec3 cross(Vec3 a, Vec3 b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+
+// Jacobi rotations on a symmetric 3x3; columns of v become eigenvectors.
+void jacobi3(double a[3][3], double v[3][3]) {
+  for (int i = 0; i < 3; i++)
+    for (int j = 0; j < 3; j++) v[i][j] = (i == j);
+  for (int sweep = 0; sweep < 64; sweep++) {
+    double off = std::fabs(a[0][1]) + std::fabs(a[0][2]) + std::fabs(a[1][2]);
+    double diag = std::fabs(a[0][0]) + std::fabs(a[1][1]) + std::fabs(a[2][2]);
+    if (off <= 1e-18 * diag || off == 0.0) break;
+    for (int p = 0; p < 2; p++)
+      for (int q = p + 1; q < 3; q++) {
+        if (a[p][q] == 0.0) continue;
+        double th = 0.5 * (a[q][q] - a[p][p]) / a[p][q];
+        double t = (th >= 0 ? 1.0 : -1.0) / (std::fabs(th) + std::sqrt(1.0 + th * th));
+        double c = 1.0 / std::sqrt(1.0 + t * t), s = t * c;
+        for (int k = 0; k < 3; k++) { double x = a[k][p], y = a[k][q]; a[k][p] = c * x - s * y; a[k][q] = s * x + c * y; }
+        for (int k = 0; k < 3; k++) { double x = a[p][k], y = a[q][k]; a[p][k] = c * x - s * y; a[q][k] = s * x + c * y; }
+        for (int k = 0; k < 3; k++) { double x = v[k][p], y = v[k][q]; v[k][p] = c * x - s * y; v[k][q] = s * x + c * y; }
+      }
+  }
+}
+
+struct BuildNode {
+  float axis[9];   // axis k = axis[3k..3k+2]  (fp32-rounded, what the GPU will use)
+  float centre[3];
+  float ext[3];
+  int left = -1;   // child build-node ids, or -1
+  int right = -1;
+  int tri = -1;
+};
+
+struct Builder {
+  const UnitModel& m;
+  std::vector<BuildNode> nodes;
+  std::vector<int> prims;
+  std::vector<Vec3> cent;
+  int depth = 0;
+  explicit Builder(const UnitModel& mm) : m(mm) {}
+
+  Vec3 vert(int t, int k) const {
+    const double* p = &m.tris[(size_t)9 * t + 3 * k];
+    return {p[0], p[1], p[2]};
+  }
+
+  // PCA box of the triangle vertices; axes rounded to fp32 FIRST, then centre/extents are
+  // derived from the exact (fp64) projections on the rounded axes and rounded outwards, so the
+  // fp32 box is a superset of the fp64 triangles.
+  void fit(int first, int n, BuildNode& nd) {
+    double S1[3] = {0, 0, 0}, S2[3][3] = {{0}};
+    for (int i = 0; i < n; i++)
+      for (int k = 0; k < 3; k++) {
+        Vec3 p = vert(prims[first + i], k);
+        double pp[3] = {p.x, p.y, p.z};
+        for (int a = 0; a < 3; a++) {
+          S1[a] += pp[a];
+          for (int b = 0; b < 3; b++) S2[a][b] += pp[a] * pp[b];
+        }
+      }
+    double C[3][3], E[3][3];
+    double np = 3.0 * n;
+    for (int a = 0; a < 3; a++)
+      for (int b = 0; b < 3; b++) C[a][b] = S2[a][b] - S1[a] * S1[b] / np;
+    jacobi3(C, E);
+    int order[3] = {0, 1, 2};
+    std::sort(order, order + 3, [&](int a, int b) { return C[a][a] > C[b][b]; });
+    Vec3 a0 = {E[0][order[0]], E[1][order[0]], E[2][order[0]]};
+    Vec3 a1 = {E[0][order[1]], E[1][order[1]], E[2][order[1]]};
+    if (n == 1) {  // a single triangle: longest edge / in-plane normal / face normal
+      Vec3 p0 = vert(prims[first], 0), p1 = vert(prims[first], 1), p2 = vert(prims[first], 2);
+      Vec3 e[3] = {p1 - p0, p2 - p1, p0 - p2};
+      int lg = 0;
+      for (int k = 1; k < 3; k++) if (dot(e[k], e[k]) > dot(e[lg], e[lg])) lg = k;
+      Vec3 nrm = cross(e[0], e[1]);
+      if (dot(nrm, nrm) > 0 && dot(e[lg], e[lg]) > 0) { a0 = e[lg]; a1 = cross(nrm, a0); }
+    }
+    double l0 = std::sqrt(dot(a0, a0));
+    if (!(l0 > 0)) { a0 = {1, 0, 0}; l0 = 1; }
+    a0 = {a0.x / l0, a0.y / l0, a0.z / l0};
+    double d01 = dot(a0, a1);
+    a1 = {a1.x - d01 * a0.x, a1.y - d01 * a0.y, a1.z - d01 * a0.z};
+    double l1 = std::sqrt(dot(a1, a1));
+    if (!(l1 > 1e-12)) {
+      Vec3 h = std::fabs(a0.x) < 0.9 ? Vec3{1, 0, 0} : Vec3{0, 1, 0};
+      a1 = cross(a0, h);
+      l1 = std::sqrt(dot(a1, a1));
+    }
+    a1 = {a1.x / l1, a1.y / l1, a1.z / l1};
+    Vec3 a2 = cross(a0, a1);
+    Vec3 ax[3] = {a0, a1, a2};
+    for (int k = 0; k < 3; k++) {
+      nd.axis[3 * k] = (float)ax[k].x; nd.axis[3 * k + 1] = (float)ax[k].y; nd.axis[3 * k + 2] = (float)ax[k].z;
+      ax[k] = {(double)nd.axis[3 * k], (double)nd.axis[3 * k + 1], (double)nd.axis[3 * k + 2]};
+    }
+    double lo[3], hi[3];
+    for (int k = 0; k < 3; k++) { lo[k] = std::numeric_limits<double>::max(); hi[k] = -lo[k]; }
+    for (int i = 0; i < n; i++)
+      for (int k = 0; k < 3; k++) {
+        Vec3 p = vert(prims[first + i], k);
+        for (int a = 0; a < 3; a++) {
+          double pr = dot(ax[a], p);
+          lo[a] = std::min(lo[a], pr); hi[a] = std::max(hi[a], pr);
+        }
+      }
+    // centre in world coordinates, rounded to fp32; extents recomputed about the rounded centre.
+    // The rounded axes are orthonormal only to ~1e-7, so measure the extents as the largest
+    // |axis . (p - centre)| directly (exact definition of the box the GPU tests against).
+    double o[3] = {(lo[0] + hi[0]) / 2, (lo[1] + hi[1]) / 2, (lo[2] + hi[2]) / 2};
+    Vec3 c = {ax[0].x * o[0] + ax[1].x * o[1] + ax[2].x * o[2], ax[0].y * o[0] + ax[1].y * o[1] + ax[2].y * o[2],
+              ax[0].z * o[0] + ax[1].z * o[1] + ax[2].z * o[2]};
+    nd.centre[0] = (float)c.x; nd.centre[1] = (float)c.y; nd.centre[2] = (float)c.z;
+    Vec3 cf = {(double)nd.centre[0], (double)nd.centre[1], (double)nd.centre[2]};
+    double ext[3] = {0, 0, 0};
+    for (int i = 0; i < n; i++)
+      for (int k = 0; k < 3; k++) {
+        Vec3 d = vert(prims[first + i], k) - cf;
+        for (int a = 0; a < 3; a++) ext[a] = std::max(ext[a], std::fabs(dot(ax[a], d)));
+      }
+    for (int a = 0; a < 3; a++) {
+      // slack for the non-orthonormality of the rounded frame (<= ~3e-7 relative) + round up
+      double e = ext[a] * (1.0 + 1e-6) + 1e-9;
+      nd.ext[a] = std::nextafterf((float)e, std::numeric_limits<float>::infinity());
+    }
+  }
+
+  int build(int first, int n, int lvl) {
+    depth = std::max(depth, lvl);
+    int id = (int)nodes.size();
+    nodes.emplace_back();
+    {
+      BuildNode nd;
+      fit(first, n, nd);
+      nodes[id] = nd;
+    }
+    if (n == 1) { nodes[id].tri = prims[first]; return id; }
+    // split along the box's longest axis at the mean centroid; fall back to the median when
+    // the mean split is badly unbalanced (keeps the depth, hence the traversal stack, small)
+    Vec3 sv = {(double)nodes[id].axis[0], (double)nodes[id].axis[1], (double)nodes[id].axis[2]};
+    {
+      int la = 0;
+      for (int a = 1; a < 3; a++) if (nodes[id].ext[a] > nodes[id].ext[la]) la = a;
+      sv = {(double)nodes[id].axis[3 * la], (double)nodes[id].axis[3 * la + 1], (double)nodes[id].axis[3 * la + 2]};
+    }
+    double mean = 0;
+    for (int i = 0; i < n; i++) mean += dot(sv, cent[prims[first + i]]);
+    mean /= n;
+    auto mid = std::partition(prims.begin() + first, prims.begin() + first + n,
+                              [&](int t) { return dot(sv, cent[t]) <= mean; });
+    int c1 = (int)(mid - (prims.begin() + first));
+    if (c1 < n / 8 + (n < 8 ? 1 : 0) || n - c1 < n / 8 + (n < 8 ? 1 : 0) || c1 == 0 || c1 == n) {
+      c1 = n / 2;
+      std::nth_element(prims.begin() + first, prims.begin() + first + c1, prims.begin() + first + n,
+                       [&](int a, int b) { return dot(sv, cent[a]) < dot(sv, cent[b]); });
+    }
+    int l = build(first, c1, lvl + 1);
+    int r = build(first + c1, n - c1, lvl + 1);
+    nodes[id].left = l; nodes[id].right = r;
+    return id;
+  }
+};
+
+}  // namespace
+
+void build_gpu_bvh(UnitModel& m) {
+  Builder b(m);
+  int n = m.nf();
+  b.prims.resize(n);
+  b.cent.resize(n);
+  for (int t = 0; t < n; t++) {
+    b.prims[t] = t;
+    Vec3 p0 = b.vert(t, 0), p1 = b.vert(t, 1), p2 = b.vert(t, 2);
+    b.cent[t] = {(p0.x + p1.x + p2.x) / 3, (p0.y + p1.y + p2.y) / 3, (p0.z + p1.z + p2.z) / 3};
+  }
+  b.nodes.reserve(2 * (size_t)n);
+  b.build(0, n, 0);
+  // breadth-first renumbering with sibling pairs adjacent
+  int N = (int)b.nodes.size();
+  std::vector<int> order;   // new index -> build id
+  std::vector<int> newid(N, -1);
+  order.reserve(N);
+  order.push_back(0); newid[0] = 0;
+  for (size_t h = 0; h < order.size(); h++) {
+    const BuildNode& nd = b.nodes[order[h]];
+    if (nd.left >= 0) {
+      newid[nd.left] = (int)order.size(); order.push_back(nd.left);
+      newid[nd.right] = (int)order.size(); order.push_back(nd.right);
+    }
+  }
+  m.bvh.num_nodes = N;
+  m.bvh.depth = b.depth;
+  m.bvh.nodes.assign((size_t)16 * N, 0.f);
+  for (int i = 0; i < N; i++) {
+    const BuildNode& nd = b.nodes[order[i]];
+    float* o = &m.bvh.nodes[(size_t)16 * i];
+    for (int k = 0; k < 3; k++) {
+      o[4 * k] = nd.axis[3 * k]; o[4 * k + 1] = nd.axis[3 * k + 1]; o[4 * k + 2] = nd.axis[3 * k + 2];
+      o[4 * k + 3] = nd.centre[k];
+    }
+    o[12] = nd.ext[0]; o[13] = nd.ext[1]; o[14] = nd.ext[2];
+    int32_t link = nd.left >= 0 ? newid[nd.left] : -(nd.tri + 1);
+    std::memcpy(&o[15], &link, 4);
+  }
+}
+
+}  // namespace osr

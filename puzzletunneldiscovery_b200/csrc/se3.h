@@ -1,0 +1,120 @@
+// se3.h -- SE(3) unit-state arithmetic shared by host code and CUDA kernels.
+//
+// Same semantics as the reference's lib/osr/osr_state.cc (paths relative to /root/reference):
+//   state layout [tx ty tz qw qx qy qz]                     lib/osr/osr_state.h:20-33
+//   state -> rigid transform (quaternion NOT renormalised)   lib/osr/osr_state.cc:16-25
+//   interpolate = lerp + Eigen-3.3 slerp                     lib/osr/osr_state.cc:28-44
+//   distance = |dt| + angularDistance                        lib/osr/osr_state.cc:130-154
+//   apply(from, tr, angle-axis)                              lib/osr/osr_state.cc:244-259
+// All arithmetic is plain fp64 multiply/add in a fixed order; this file must be compiled
+// without FMA contraction (nvcc -fmad=false, g++ -ffp-contract=off) so that host, device and
+// the test oracle round identically.
+#pragma once
+#include <math.h>
+
+#if defined(__CUDACC__)
+#define OSR_HD __host__ __device__ __forceinline__
+#else
+#define OSR_HD inline
+#endif
+
+namespace osr {
+
+struct Rigid {   // x -> R x + t, R row-major
+  double R[9];
+  double t[3];
+};
+
+OSR_HD void quat_normalize(double& w, double& x, double& y, double& z) {
+  double n2 = x * x + y * y + z * z + w * w;
+  if (n2 > 0) {
+    double n = sqrt(n2);
+    w /= n; x /= n; y /= n; z /= n;
+  }
+}
+
+OSR_HD void quat_mul(const double* a, const double* b, double* o) {  // (w,x,y,z)
+  double w = a[0] * b[0] - a[1] * b[1] - a[2] * b[2] - a[3] * b[3];
+  double x = a[0] * b[1] + a[1] * b[0] + a[2] * b[3] - a[3] * b[2];
+  double y = a[0] * b[2] + a[2] * b[0] + a[3] * b[1] - a[1] * b[3];
+  double z = a[0] * b[3] + a[3] * b[0] + a[1] * b[2] - a[2] * b[1];
+  o[0] = w; o[1] = x; o[2] = y; o[3] = z;
+}
+
+OSR_HD void quat_to_rot(double w, double x, double y, double z, double* R) {
+  double tx = 2 * x, ty = 2 * y, tz = 2 * z;
+  double twx = tx * w, twy = ty * w, twz = tz * w;
+  double txx = tx * x, txy = ty * x, txz = tz * x;
+  double tyy = ty * y, tyz = tz * y, tzz = tz * z;
+  R[0] = 1 - (tyy + tzz); R[1] = txy - twz;       R[2] = txz + twy;
+  R[3] = txy + twz;       R[4] = 1 - (txx + tzz); R[5] = tyz - twx;
+  R[6] = txz - twy;       R[7] = tyz + twx;       R[8] = 1 - (txx + tyy);
+}
+
+OSR_HD void state_to_rigid(const double* q, Rigid& r) {
+  quat_to_rot(q[3], q[4], q[5], q[6], r.R);
+  r.t[0] = q[0]; r.t[1] = q[1]; r.t[2] = q[2];
+}
+
+// robot pose expressed in the environment's frame: R = R1^T R2, t = R1^T (t2 - t1)
+// (what FCL's relativeTransform hands to the traversal, fcl math/geometry-inl.h:758-784).
+OSR_HD void relative_rigid(const Rigid& env, const Rigid& rob, Rigid& o) {
+  for (int i = 0; i < 3; i++)
+    for (int j = 0; j < 3; j++)
+      o.R[3 * i + j] = env.R[i] * rob.R[j] + env.R[3 + i] * rob.R[3 + j] + env.R[6 + i] * rob.R[6 + j];
+  double d0 = rob.t[0] - env.t[0], d1 = rob.t[1] - env.t[1], d2 = rob.t[2] - env.t[2];
+  for (int i = 0; i < 3; i++) o.t[i] = env.R[i] * d0 + env.R[3 + i] * d1 + env.R[6 + i] * d2;
+}
+
+OSR_HD void interpolate(const double* a, const double* b, double tau, double* o) {
+  double aw = a[3], ax = a[4], ay = a[5], az = a[6];
+  double bw = b[3], bx = b[4], by = b[5], bz = b[6];
+  quat_normalize(aw, ax, ay, az);
+  quat_normalize(bw, bx, by, bz);
+  const double one = 1.0 - 2.220446049250313e-16;
+  double d = ax * bx + ay * by + az * bz + aw * bw;
+  double ad = fabs(d);
+  double s0, s1;
+  if (ad >= one) {
+    s0 = 1.0 - tau; s1 = tau;
+  } else {
+    double th = acos(ad);
+    double st = sin(th);
+    s0 = sin((1.0 - tau) * th) / st;
+    s1 = sin(tau * th) / st;
+  }
+  if (d < 0) s1 = -s1;
+  o[0] = a[0] * (1 - tau) + b[0] * tau;
+  o[1] = a[1] * (1 - tau) + b[1] * tau;
+  o[2] = a[2] * (1 - tau) + b[2] * tau;
+  o[3] = s0 * aw + s1 * bw; o[4] = s0 * ax + s1 * bx; o[5] = s0 * ay + s1 * by; o[6] = s0 * az + s1 * bz;
+}
+
+OSR_HD double distance(const double* a, const double* b) {
+  double qa[4] = {a[3], a[4], a[5], a[6]}, qb[4] = {b[3], b[4], b[5], b[6]};
+  quat_normalize(qa[0], qa[1], qa[2], qa[3]);
+  quat_normalize(qb[0], qb[1], qb[2], qb[3]);
+  double dx = a[0] - b[0], dy = a[1] - b[1], dz = a[2] - b[2];
+  double tr = sqrt(dx * dx + dy * dy + dz * dz);
+  double cb[4] = {qb[0], -qb[1], -qb[2], -qb[3]}, d[4];
+  quat_mul(qa, cb, d);
+  double vn = sqrt(d[1] * d[1] + d[2] * d[2] + d[3] * d[3]);
+  return tr + 2.0 * atan2(vn, fabs(d[0]));
+}
+
+OSR_HD void apply(const double* from, const double* tr, const double* aa, double* o) {
+  double q0[4] = {from[3], from[4], from[5], from[6]};
+  quat_normalize(q0[0], q0[1], q0[2], q0[3]);
+  double ang = sqrt(aa[0] * aa[0] + aa[1] * aa[1] + aa[2] * aa[2]);
+  double ax, ay, az;
+  if (ang == 0.0) { ax = 1.0; ay = 0.0; az = 0.0; }
+  else { ax = aa[0] / ang; ay = aa[1] / ang; az = aa[2] / ang; }
+  double s = sin(0.5 * ang);
+  double qa[4] = {cos(0.5 * ang), s * ax, s * ay, s * az}, q[4];
+  quat_mul(qa, q0, q);
+  quat_normalize(q[0], q[1], q[2], q[3]);
+  o[0] = from[0] + tr[0]; o[1] = from[1] + tr[1]; o[2] = from[2] + tr[2];
+  o[3] = q[0]; o[4] = q[1]; o[5] = q[2]; o[6] = q[3];
+}
+
+}  // namespace osr
