@@ -53,7 +53,8 @@ int osr_set_rob_mesh(osr_world* w, const float* V, int nV, const int32_t* F, int
 int osr_enforce_robot_center(osr_world* w, const double c[3]);
 /* UnitWorld::scaleToUnit + angleModel(0,0) (unit_world.cc:123-161): computes scene_scale, the
  * unit-space meshes and the BVHs, uploads them to `ndev` devices listed in `devices`
- * (ndev<=0: current device only). */
+ * (ndev<=0: current device only).  Without a CUDA device it returns OSR_ENODEV after building the
+ * host-side geometry, so the getters below still work; every query then fails (no CPU fallback). */
 int osr_finalize(osr_world* w, const int* devices, int ndev);
 /* UnitWorld::setPerturbation (unit_world.cc:165-176) */
 int osr_set_perturbation(osr_world* w, const double q[7]);
@@ -66,6 +67,8 @@ int osr_num_devices(const osr_world* w);
 /* geometry read-back (CDModel::vertices()/faces(), cdmodel.cc:232-246): which 0=env 1=robot */
 int osr_mesh_sizes(const osr_world* w, int which, int* nV, int* nF, int* nNodes, int* depth);
 int osr_get_unit_mesh(const osr_world* w, int which, double* V, int32_t* F);
+/* the engine's own OBB tree (16 floats per node, layout in csrc/geometry.h); for conservativeness tests */
+int osr_get_bvh_nodes(const osr_world* w, int which, float* out);
 
 /* Work counters accumulated over the calls made since the last reset (FCL's num_bv_tests /
  * num_leaf_tests, mesh_collision_traversal_node-inl.h:497,547, plus the engine's own). */

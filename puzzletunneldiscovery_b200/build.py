@@ -1,0 +1,43 @@
+"""Builds libosrgpu.so (sm_100a) in-tree with nvcc.  No JIT cache: the .so travels with the repo."""
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+OUT = os.path.join(HERE, "libosrgpu.so")
+SOURCES = ["engine.cu", "geometry.cc"]
+DEPS = SOURCES + ["kernels.cuh", "se3.h", "geometry.h", os.path.join("..", "..", "include", "osrgpu.h")]
+
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+    "-fmad=false",            # fp64 code must round like the reference (no FMA contraction)
+    "-Xcompiler", "-fPIC,-O3,-ffp-contract=off,-Wall",
+    "-shared", "-Xptxas", "-v",
+]
+
+
+def stale():
+    if not os.path.exists(OUT):
+        return True
+    t = os.path.getmtime(OUT)
+    return any(os.path.getmtime(os.path.join(CSRC, d)) > t for d in DEPS)
+
+
+def build(force=False, verbose=False):
+    if not force and not stale():
+        return OUT
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    cmd = [nvcc] + NVCC_FLAGS + ["-ccbin", "g++", "-o", OUT] + [os.path.join(CSRC, s) for s in SOURCES]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    with open(os.path.join(HERE, "build.log"), "w") as f:
+        f.write(" ".join(cmd) + "\n" + r.stdout)
+    if verbose or r.returncode != 0:
+        sys.stderr.write(r.stdout)
+    if r.returncode != 0:
+        raise RuntimeError("nvcc failed building libosrgpu.so (see puzzletunneldiscovery_b200/build.log)")
+    return OUT
+
+
+if __name__ == "__main__":
+    build(force=True, verbose=True)

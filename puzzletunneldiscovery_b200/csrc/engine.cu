@@ -1,0 +1,899 @@
+// engine.cu -- libosrgpu.so: world handle, device management and the C ABI of include/osrgpu.h.
+// Host-side replacement of osr::UnitWorld's query methods (/root/reference/lib/osr/unit_world.cc);
+// every query runs on the GPU, there is no CPU fallback.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/osrgpu.h"
+#include "geometry.h"
+#include "kernels.cuh"
+
+namespace {
+
+thread_local std::string g_err;
+int fail(int code, const std::string& msg) {
+  g_err = msg;
+  return code;
+}
+#define CU(call)                                                                                         \
+  do {                                                                                                   \
+    cudaError_t e_ = (call);                                                                             \
+    if (e_ != cudaSuccess)                                                                               \
+      return fail(OSR_ECUDA, std::string(#call) + ": " + cudaGetErrorString(e_) + " @" + __FILE__ + ":" + \
+                                 std::to_string(__LINE__));                                              \
+  } while (0)
+
+struct DevBuf {  // grow-only device buffer
+  void* p = nullptr;
+  size_t cap = 0;
+  cudaError_t need(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    size_t want = bytes + bytes / 4 + 256;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e == cudaSuccess) cap = want;
+    return e;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+struct Slot {  // one GPU
+  int dev = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  float4* env_nodes = nullptr; double* env_tris = nullptr;
+  float4* rob_nodes = nullptr; double* rob_tris = nullptr;
+  osr::DevCounters* counters = nullptr;
+  unsigned long long* work = nullptr;   // [0] tile queue, [1] contact record count
+  unsigned long long* spill = nullptr;
+  int* err = nullptr;
+  int grid_valid = 0, grid_transit = 0, grid_contacts = 0;
+  int spill_cap = 0;
+  DevBuf in0, in1, vd, out[6], recs, rowrec, seg, faces, cop, bary;
+};
+
+}  // namespace
+
+struct osr_world {
+  std::mutex mu;
+  osr::TriMesh env_mesh, rob_mesh;
+  bool has_env = false, has_rob = false, finalized = false;
+  bool host_ready = false;  // unit meshes + BVHs built (true even when no CUDA device could be opened)
+  bool centre_enforced = false;
+  float centre[3] = {0, 0, 0};        // centre used for the robot (Scene::center_)
+  float ompl_centre[3] = {0, 0, 0};   // mean of vertices (Scene::mean_of_vertices_)
+  float scene_scale = 1.0f;
+  double recommended_cres = 0.001;
+  double perturb[7] = {0, 0, 0, 1, 0, 0, 0};
+  osr::UnitModel env, rob;
+  std::vector<Slot> slots;
+  osr_counters host_counters = {0, 0, 0, 0, 0, 0};
+
+  osr::KParams params(const Slot& s) const {
+    osr::KParams P;
+    P.env.nodes = s.env_nodes; P.env.tris = s.env_tris;
+    P.env.num_nodes = env.bvh.num_nodes; P.env.num_tris = env.nf();
+    P.rob.nodes = s.rob_nodes; P.rob.tris = s.rob_tris;
+    P.rob.num_nodes = rob.bvh.num_nodes; P.rob.num_tris = rob.nf();
+    osr::state_to_rigid(perturb, P.env_tf);
+    P.counters = s.counters;
+    P.work_counter = s.work;
+    P.spill = s.spill;
+    P.spill_cap = s.spill_cap;
+    P.error_flag = s.err;
+    return P;
+  }
+};
+
+namespace {
+
+constexpr size_t SMEM_PER_BLOCK = sizeof(osr::WarpShared) * osr::WARPS_PER_BLOCK;
+
+void free_slot(Slot& s) {
+  cudaSetDevice(s.dev);
+  if (s.stream) cudaStreamSynchronize(s.stream);
+  cudaFree(s.env_nodes); cudaFree(s.env_tris); cudaFree(s.rob_nodes); cudaFree(s.rob_tris);
+  cudaFree(s.counters); cudaFree(s.work); cudaFree(s.spill); cudaFree(s.err);
+  s.in0.release(); s.in1.release(); s.vd.release();
+  for (auto& b : s.out) b.release();
+  s.recs.release(); s.rowrec.release(); s.seg.release(); s.faces.release(); s.cop.release(); s.bary.release();
+  if (s.ev0) cudaEventDestroy(s.ev0);
+  if (s.ev1) cudaEventDestroy(s.ev1);
+  if (s.stream) cudaStreamDestroy(s.stream);
+  s = Slot();
+}
+
+int init_slot(osr_world* w, Slot& s, int dev) {
+  s.dev = dev;
+  CU(cudaSetDevice(dev));
+  CU(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+  CU(cudaEventCreate(&s.ev0));
+  CU(cudaEventCreate(&s.ev1));
+  auto up = [&](void** d, const void* h, size_t bytes) -> cudaError_t {
+    cudaError_t e = cudaMalloc(d, bytes);
+    if (e != cudaSuccess) return e;
+    return cudaMemcpy(*d, h, bytes, cudaMemcpyHostToDevice);
+  };
+  CU(up((void**)&s.env_nodes, w->env.bvh.nodes.data(), w->env.bvh.nodes.size() * 4));
+  CU(up((void**)&s.env_tris, w->env.tris.data(), w->env.tris.size() * 8));
+  CU(up((void**)&s.rob_nodes, w->rob.bvh.nodes.data(), w->rob.bvh.nodes.size() * 4));
+  CU(up((void**)&s.rob_tris, w->rob.tris.data(), w->rob.tris.size() * 8));
+  CU(cudaMalloc((void**)&s.counters, sizeof(osr::DevCounters)));
+  CU(cudaMemset(s.counters, 0, sizeof(osr::DevCounters)));
+  CU(cudaMalloc((void**)&s.work, 2 * sizeof(unsigned long long)));
+  CU(cudaMalloc((void**)&s.err, sizeof(int)));
+  CU(cudaMemset(s.err, 0, sizeof(int)));
+  // persistent grid: as many blocks as fit, on every SM
+  CU(cudaFuncSetAttribute(osr::k_is_valid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_PER_BLOCK));
+  CU(cudaFuncSetAttribute(osr::k_transit, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_PER_BLOCK));
+  CU(cudaFuncSetAttribute(osr::k_contacts, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_PER_BLOCK));
+  int nsm = 0, bpsm = 0, b2 = 0, b3 = 0;
+  CU(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev));
+  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bpsm, osr::k_is_valid, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK));
+  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b2, osr::k_transit, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK));
+  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b3, osr::k_contacts, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK));
+  s.grid_valid = nsm * std::max(1, bpsm);
+  s.grid_transit = nsm * std::max(1, b2);
+  s.grid_contacts = nsm * std::max(1, b3);
+  s.spill_cap = 8192;
+  size_t warps = (size_t)std::max(s.grid_valid, std::max(s.grid_transit, s.grid_contacts)) * osr::WARPS_PER_BLOCK;
+  CU(cudaMalloc((void**)&s.spill, warps * s.spill_cap * sizeof(unsigned long long)));
+  return OSR_OK;
+}
+
+// contiguous index-range shards, the reference's partt.get_task_chunk rule
+// (/root/reference/src/GP/pipeline/partt.py:22-35)
+inline void shard(int64_t n, int parts, int i, int64_t& lo, int64_t& hi) {
+  lo = n * i / parts;
+  hi = n * (i + 1) / parts;
+}
+
+int check_ready(osr_world* w) {
+  if (!w) return fail(OSR_EINVAL, "null world");
+  if (!w->finalized) return fail(OSR_EINVAL, "osr_finalize() has not been called");
+  return OSR_OK;
+}
+
+int check_device_error(osr_world* w, Slot& s) {
+  int flag = 0;
+  CU(cudaMemcpyAsync(&flag, s.err, sizeof(int), cudaMemcpyDeviceToHost, s.stream));
+  CU(cudaStreamSynchronize(s.stream));
+  if (flag) {
+    cudaMemsetAsync(s.err, 0, sizeof(int), s.stream);
+    return fail(OSR_EOVERFLOW, "device traversal stack spill area exhausted");
+  }
+  (void)w;
+  return OSR_OK;
+}
+
+}  // namespace
+
+// =============================================================================================
+// C ABI
+// =============================================================================================
+extern "C" {
+
+const char* osr_last_error(void) { return g_err.c_str(); }
+
+int osr_create(osr_world** out) {
+  if (!out) return fail(OSR_EINVAL, "null out");
+  *out = new osr_world();
+  return OSR_OK;
+}
+
+void osr_destroy(osr_world* w) {
+  if (!w) return;
+  for (auto& s : w->slots) free_slot(s);
+  delete w;
+}
+
+static int set_mesh(osr_world* w, bool rob, const float* V, int nV, const int32_t* F, int nF) {
+  if (!w || !V || !F || nV <= 0 || nF <= 0) return fail(OSR_EINVAL, "bad mesh arguments");
+  for (int i = 0; i < 3 * nF; i++)
+    if (F[i] < 0 || F[i] >= nV) return fail(OSR_EINVAL, "face index out of range");
+  osr::TriMesh& m = rob ? w->rob_mesh : w->env_mesh;
+  m.V.assign(V, V + 3 * (size_t)nV);
+  m.F.assign(F, F + 3 * (size_t)nF);
+  (rob ? w->has_rob : w->has_env) = true;
+  w->finalized = false;
+  return OSR_OK;
+}
+int osr_set_env_mesh(osr_world* w, const float* V, int nV, const int32_t* F, int nF) { return set_mesh(w, false, V, nV, F, nF); }
+int osr_set_rob_mesh(osr_world* w, const float* V, int nV, const int32_t* F, int nF) { return set_mesh(w, true, V, nV, F, nF); }
+
+static int load_mesh(osr_world* w, bool rob, const char* path) {
+  if (!w || !path) return fail(OSR_EINVAL, "bad arguments");
+  std::string err;
+  osr::TriMesh m;
+  if (!osr::load_obj(path, m, err)) return fail(OSR_EIO, err);
+  (rob ? w->rob_mesh : w->env_mesh) = std::move(m);
+  (rob ? w->has_rob : w->has_env) = true;
+  w->finalized = false;
+  return OSR_OK;
+}
+int osr_load_env_obj(osr_world* w, const char* path) { return load_mesh(w, false, path); }
+int osr_load_rob_obj(osr_world* w, const char* path) { return load_mesh(w, true, path); }
+
+int osr_enforce_robot_center(osr_world* w, const double c[3]) {
+  if (!w || !c) return fail(OSR_EINVAL, "bad arguments");
+  for (int k = 0; k < 3; k++) w->centre[k] = (float)c[k];
+  w->centre_enforced = true;
+  w->finalized = false;
+  return OSR_OK;
+}
+
+int osr_finalize(osr_world* w, const int* devices, int ndev) {
+  if (!w) return fail(OSR_EINVAL, "null world");
+  std::lock_guard<std::mutex> lk(w->mu);
+  if (!w->has_env || !w->has_rob) return fail(OSR_EINVAL, "both the environment and the robot mesh must be loaded");
+  w->finalized = false;
+  w->host_ready = false;
+  // UnitWorld::scaleToUnit (unit_world.cc:123-131)
+  {
+    float es = osr::bbox_span(w->env_mesh), rs = osr::bbox_span(w->rob_mesh);
+    w->scene_scale = (float)(1.0 / std::max(es, rs));
+    osr::mean_of_vertices(w->rob_mesh, w->ompl_centre);
+    if (!w->centre_enforced)
+      for (int k = 0; k < 3; k++) w->centre[k] = w->ompl_centre[k];
+    // UnitWorld::angleModel(0,0) (unit_world.cc:137-161) -> CDModel (cdmodel.cc:85-160)
+    osr::make_unit_model(w->env_mesh, w->scene_scale, nullptr, w->env);
+    osr::make_unit_model(w->rob_mesh, w->scene_scale, w->centre, w->rob);
+    osr::build_gpu_bvh(w->env);
+    osr::build_gpu_bvh(w->rob);
+    if (w->env.bvh.num_nodes >= (1 << 27) || w->rob.bvh.num_nodes >= (1 << 27))
+      return fail(OSR_EINVAL, "mesh too large for the 27-bit node index of the work stack");
+    w->host_ready = true;
+  }
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0)
+    return fail(OSR_ENODEV, "no CUDA device available (the engine has no CPU fallback)");
+  std::vector<int> devs;
+  if (ndev <= 0 || !devices) {
+    int cur = 0;
+    cudaGetDevice(&cur);
+    devs.push_back(cur);
+  } else {
+    for (int i = 0; i < ndev; i++) {
+      if (devices[i] < 0 || devices[i] >= count) return fail(OSR_ENODEV, "device index out of range");
+      devs.push_back(devices[i]);
+    }
+  }
+  for (auto& s : w->slots) free_slot(s);
+  w->slots.assign(devs.size(), Slot());
+  for (size_t i = 0; i < devs.size(); i++) {
+    int rc = init_slot(w, w->slots[i], devs[i]);
+    if (rc != OSR_OK) return rc;
+  }
+  w->finalized = true;
+  return OSR_OK;
+}
+
+int osr_set_perturbation(osr_world* w, const double q[7]) {
+  if (!w || !q) return fail(OSR_EINVAL, "bad arguments");
+  std::lock_guard<std::mutex> lk(w->mu);
+  memcpy(w->perturb, q, sizeof(w->perturb));
+  return OSR_OK;
+}
+double osr_scene_scale(const osr_world* w) { return w ? (double)w->scene_scale : 0.0; }
+double osr_get_recommended_cres(const osr_world* w) { return w ? w->recommended_cres : 0.0; }
+int osr_set_recommended_cres(osr_world* w, double v) {
+  if (!w) return fail(OSR_EINVAL, "null world");
+  w->recommended_cres = v;
+  return OSR_OK;
+}
+int osr_get_robot_center(const osr_world* w, double c[3]) {
+  if (!w || !c) return fail(OSR_EINVAL, "bad arguments");
+  for (int k = 0; k < 3; k++) c[k] = w->centre[k];
+  return OSR_OK;
+}
+int osr_num_devices(const osr_world* w) { return w ? (int)w->slots.size() : 0; }
+int osr_mesh_sizes(const osr_world* w, int which, int* nV, int* nF, int* nNodes, int* depth) {
+  if (!w || !w->host_ready) return fail(OSR_EINVAL, "geometry not built: call osr_finalize()");
+  const osr::UnitModel& m = which ? w->rob : w->env;
+  if (nV) *nV = (int)(m.V.size() / 3);
+  if (nF) *nF = m.nf();
+  if (nNodes) *nNodes = m.bvh.num_nodes;
+  if (depth) *depth = m.bvh.depth;
+  return OSR_OK;
+}
+int osr_get_unit_mesh(const osr_world* w, int which, double* V, int32_t* F) {
+  if (!w || !w->host_ready) return fail(OSR_EINVAL, "geometry not built: call osr_finalize()");
+  const osr::UnitModel& m = which ? w->rob : w->env;
+  if (V) memcpy(V, m.V.data(), m.V.size() * 8);
+  if (F) memcpy(F, m.F.data(), m.F.size() * 4);
+  return OSR_OK;
+}
+
+int osr_get_counters(osr_world* w, osr_counters* out, int reset) {
+  int rc = check_ready(w);
+  if (rc) return rc;
+  std::lock_guard<std::mutex> lk(w->mu);
+  osr_counters tot = w->host_counters;
+  for (auto& s : w->slots) {
+    CU(cudaSetDevice(s.dev));
+    osr::DevCounters c;
+    CU(cudaMemcpyAsync(&c, s.counters, sizeof(c), cudaMemcpyDeviceToHost, s.stream));
+    CU(cudaStreamSynchronize(s.stream));
+    tot.bv_tests += c.bv; tot.leaf_tests += c.leaf; tot.fp64_rechecks += c.fp64; tot.poses += c.poses;
+    tot.spills += c.spills;
+    if (reset) CU(cudaMemsetAsync(s.counters, 0, sizeof(c), s.stream));
+  }
+  if (out) *out = tot;
+  if (reset) w->host_counters = osr_counters{0, 0, 0, 0, 0, 0};
+  return OSR_OK;
+}
+
+// ---- launch helpers ---------------------------------------------------------------------------
+static int launch_valid(osr_world* w, Slot& s, const double* d_q, int64_t n, uint8_t* d_out) {
+  CU(cudaMemsetAsync(s.work, 0, 2 * sizeof(unsigned long long), s.stream));
+  osr::KParams P = w->params(s);
+  CU(cudaEventRecord(s.ev0, s.stream));
+  osr::k_is_valid<<<s.grid_valid, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK, s.stream>>>(P, d_q, (long long)n, d_out);
+  CU(cudaGetLastError());
+  CU(cudaEventRecord(s.ev1, s.stream));
+  w->host_counters.kernel_launches++;
+  return OSR_OK;
+}
+static int launch_transit(osr_world* w, Slot& s, const double* d_from, const double* d_to, int64_t n,
+                          const double* d_vd, int64_t vd_count, double vd_scalar, int transition_mode,
+                          osr::SegOut O) {
+  CU(cudaMemsetAsync(s.work, 0, 2 * sizeof(unsigned long long), s.stream));
+  osr::KParams P = w->params(s);
+  CU(cudaEventRecord(s.ev0, s.stream));
+  osr::k_transit<<<s.grid_transit, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK, s.stream>>>(
+      P, d_from, d_to, (long long)n, d_vd, (long long)vd_count, vd_scalar, transition_mode, O);
+  CU(cudaGetLastError());
+  CU(cudaEventRecord(s.ev1, s.stream));
+  w->host_counters.kernel_launches++;
+  return OSR_OK;
+}
+
+// ---- validity ---------------------------------------------------------------------------------
+int osr_is_valid_states(osr_world* w, const double* q, int64_t n, uint8_t* out) {
+  int rc = check_ready(w);
+  if (rc) return rc;
+  if (n < 0 || (n > 0 && (!q || !out))) return fail(OSR_EINVAL, "bad arguments");
+  if (n == 0) return OSR_OK;
+  std::lock_guard<std::mutex> lk(w->mu);
+  int parts = (int)w->slots.size();
+  for (int i = 0; i < parts; i++) {
+    Slot& s = w->slots[i];
+    int64_t lo, hi;
+    shard(n, parts, i, lo, hi);
+    if (hi == lo) continue;
+    CU(cudaSetDevice(s.dev));
+    CU(s.in0.need((size_t)(hi - lo) * 56));
+    CU(s.out[0].need((size_t)(hi - lo)));
+    CU(cudaMemcpyAsync(s.in0.p, q + 7 * lo, (size_t)(hi - lo) * 56, cudaMemcpyHostToDevice, s.stream));
+    rc = launch_valid(w, s, (const double*)s.in0.p, hi - lo, (uint8_t*)s.out[0].p);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(out + lo, s.out[0].p, (size_t)(hi - lo), cudaMemcpyDeviceToHost, s.stream));
+  }
+  for (int i = 0; i < parts; i++) {
+    Slot& s = w->slots[i];
+    CU(cudaSetDevice(s.dev));
+    rc = check_device_error(w, s);
+    if (rc) return rc;
+  }
+  return OSR_OK;
+}
+
+int osr_is_valid_states_device(osr_world* w, const double* d_q, int64_t n, uint8_t* d_out) {
+  int rc = check_ready(w);
+  if (rc) return rc;
+  if (n <= 0) return n == 0 ? OSR_OK : fail(OSR_EINVAL, "bad n");
+  std::lock_guard<std::mutex> lk(w->mu);
+  Slot& s = w->slots[0];
+  CU(cudaSetDevice(s.dev));
+  return launch_valid(w, s, d_q, n, d_out);
+}
+
+// ---- segments ---------------------------------------------------------------------------------
+static int transit_host(osr_world* w, const double* from, const double* to, int64_t n, const double* vd,
+                        int64_t vd_count, double vd_scalar, int transition_mode, double* last_free,
+                        double* first_hit, uint8_t* is_free, double* free_tau, double* touch_tau, int64_t* steps) {
+  int parts = (int)w->slots.size();
+  int rc;
+  for (int i = 0; i < parts; i++) {
+    Slot& s = w->slots[i];
+    int64_t lo, hi;
+    shard(n, parts, i, lo, hi);
+    int64_t m = hi - lo;
+    if (m == 0) continue;
+    CU(cudaSetDevice(s.dev));
+    CU(s.in0.need((size_t)m * 56));
+    CU(s.in1.need((size_t)m * 56));
+    CU(cudaMemcpyAsync(s.in0.p, from + 7 * lo, (size_t)m * 56, cudaMemcpyHostToDevice, s.stream));
+    CU(cudaMemcpyAsync(s.in1.p, to + 7 * lo, (size_t)m * 56, cudaMemcpyHostToDevice, s.stream));
+    const double* d_vd = nullptr;
+    if (vd && vd_count > 1) {
+      CU(s.vd.need((size_t)m * 8));
+      CU(cudaMemcpyAsync(s.vd.p, vd + lo, (size_t)m * 8, cudaMemcpyHostToDevice, s.stream));
+      d_vd = (const double*)s.vd.p;
+    }
+    osr::SegOut O = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    if (last_free) { CU(s.out[0].need((size_t)m * 56)); O.last_free = (double*)s.out[0].p; }
+    if (first_hit) { CU(s.out[1].need((size_t)m * 56)); O.first_hit = (double*)s.out[1].p; }
+    if (is_free) { CU(s.out[2].need((size_t)m)); O.is_free = (uint8_t*)s.out[2].p; }
+    if (free_tau) { CU(s.out[3].need((size_t)m * 8)); O.free_tau = (double*)s.out[3].p; }
+    if (touch_tau) { CU(s.out[4].need((size_t)m * 8)); O.touch_tau = (double*)s.out[4].p; }
+    if (steps) { CU(s.out[5].need((size_t)m * 8)); O.steps = (long long*)s.out[5].p; }
+    rc = launch_transit(w, s, (const double*)s.in0.p, (const double*)s.in1.p, m, d_vd, d_vd ? m : 1,
+                        (vd && vd_count == 1) ? vd[0] : vd_scalar, transition_mode, O);
+    if (rc) return rc;
+    if (last_free) CU(cudaMemcpyAsync(last_free + 7 * lo, O.last_free, (size_t)m * 56, cudaMemcpyDeviceToHost, s.stream));
+    if (first_hit) CU(cudaMemcpyAsync(first_hit + 7 * lo, O.first_hit, (size_t)m * 56, cudaMemcpyDeviceToHost, s.stream));
+    if (is_free) CU(cudaMemcpyAsync(is_free + lo, O.is_free, (size_t)m, cudaMemcpyDeviceToHost, s.stream));
+    if (free_tau) CU(cudaMemcpyAsync(free_tau + lo, O.free_tau, (size_t)m * 8, cudaMemcpyDeviceToHost, s.stream));
+    if (touch_tau) CU(cudaMemcpyAsync(touch_tau + lo, O.touch_tau, (size_t)m * 8, cudaMemcpyDeviceToHost, s.stream));
+    if (steps) CU(cudaMemcpyAsync(steps + lo, O.steps, (size_t)m * 8, cudaMemcpyDeviceToHost, s.stream));
+  }
+  for (int i = 0; i < parts; i++) {
+    Slot& s = w->slots[i];
+    CU(cudaSetDevice(s.dev));
+    rc = check_device_error(w, s);
+    if (rc) return rc;
+  }
+  return OSR_OK;
+}
+
+int osr_transit_states_to_with_contact(osr_world* w, const double* from, const double* to, int64_t n,
+                                       const double* vd, int64_t vd_count, double* last_free, double* first_hit,
+                                       uint8_t* is_free, double* free_tau, double* touch_tau, int64_t* steps) {
+  int rc = check_ready(w);
+  if (rc) return rc;
+  if (n < 0 || (n > 0 && (!from || !to || !vd)) || (vd_count != 1 && vd_count != n))
+    return fail(OSR_EINVAL, "bad arguments");
+  if (n == 0) return OSR_OK;
+  std::lock_guard<std::mutex> lk(w->mu);
+  return transit_host(w, from, to, n, vd, vd_count, 0.0, 0, last_free, first_hit, is_free, free_tau, touch_tau, steps);
+}
+
+int osr_is_valid_transitions(osr_world* w, const double* from, const double* to, int64_t n,
+                             double initial_verify_delta, uint8_t* out) {
+  int rc = check_ready(w);
+  if (rc) return rc;
+  if (n < 0 || (n > 0 && (!from || !to || !out))) return fail(OSR_EINVAL, "bad arguments");
+  if (n == 0) return OSR_OK;
+  std::lock_guard<std::mutex> lk(w->mu);
+  return transit_host(w, from, to, n, nullptr, 1, initial_verify_delta, 1, nullptr, nullptr, out, nullptr, nullptr,
+                      nullptr);
+}
+
+int osr_transit_states_device(osr_world* w, const double* d_from, const double* d_to, int64_t n, double vd,
+                              double* d_last_free, double* d_first_hit, uint8_t* d_is_free, double* d_free_tau,
+                              double* d_touch_tau, int64_t* d_steps) {
+  int rc = check_ready(w);
+  if (rc) return rc;
+  if (n <= 0) return n == 0 ? OSR_OK : fail(OSR_EINVAL, "bad n");
+  std::lock_guard<std::mutex> lk(w->mu);
+  Slot& s = w->slots[0];
+  CU(cudaSetDevice(s.dev));
+  osr::SegOut O = {d_last_free, d_first_hit, d_is_free, d_free_tau, d_touch_tau, (long long*)d_steps};
+  return launch_transit(w, s, d_from, d_to, n, nullptr, 1, vd, 0, O);
+}
+int osr_is_valid_transitions_device(osr_world* w, const double* d_from, const double* d_to, int64_t n,
+                                    double initial_verify_delta, uint8_t* d_out) {
+  int rc = check_ready(w);
+  if (rc) return rc;
+  if (n <= 0) return n == 0 ? OSR_OK : fail(OSR_EINVAL, "bad n");
+  std::lock_guard<std::mutex> lk(w->mu);
+  Slot& s = w->slots[0];
+  CU(cudaSetDevice(s.dev));
+  osr::SegOut O = {nullptr, nullptr, d_out, nullptr, nullptr, nullptr};
+  return launch_transit(w, s, d_from, d_to, n, nullptr, 1, initial_verify_delta, 1, O);
+}
+
+void* osr_stream(osr_world* w) { return (w && !w->slots.empty()) ? (void*)w->slots[0].stream : nullptr; }
+int osr_sync(osr_world* w) {
+  int rc = check_ready(w);
+  if (rc) return rc;
+  for (auto& s : w->slots) {
+    CU(cudaSetDevice(s.dev));
+    CU(cudaStreamSynchronize(s.stream));
+  }
+  return OSR_OK;
+}
+int osr_last_kernel_ms(osr_world* w, float* ms) {
+  int rc = check_ready(w);
+  if (rc) return rc;
+  Slot& s = w->slots[0];
+  CU(cudaSetDevice(s.dev));
+  CU(cudaEventSynchronize(s.ev1));
+  CU(cudaEventElapsedTime(ms, s.ev0, s.ev1));
+  return OSR_OK;
+}
+
+// ---- disentangled -----------------------------------------------------------------------------
+int osr_is_disentangled_states(osr_world* w, const double* q, int64_t n, uint8_t* out) {
+  int rc = check_ready(w);
+  if (rc) return rc;
+  if (n < 0 || (n > 0 && (!q || !out))) return fail(OSR_EINVAL, "bad arguments");
+  if (n == 0) return OSR_OK;
+  std::lock_guard<std::mutex> lk(w->mu);
+  osr::BoxPair bp;
+  for (int k = 0; k < 3; k++) {  // fcl AABB::center() = (min+max)*0.5, width = max-min
+    bp.rob_c[k] = (w->rob.aabb_min[k] + w->rob.aabb_max[k]) * 0.5;
+    bp.rob_side[k] = w->rob.aabb_max[k] - w->rob.aabb_min[k];
+    bp.env_c[k] = (w->env.aabb_min[k] + w->env.aabb_max[k]) * 0.5;
+    bp.env_side[k] = w->env.aabb_max[k] - w->env.aabb_min[k];
+  }
+  osr::Rigid env_tf;
+  osr::state_to_rigid(w->perturb, env_tf);
+  int parts = (int)w->slots.size();
+  for (int i = 0; i < parts; i++) {
+    Slot& s = w->slots[i];
+    int64_t lo, hi;
+    shard(n, parts, i, lo, hi);
+    int64_t m = hi - lo;
+    if (m == 0) continue;
+    CU(cudaSetDevice(s.dev));
+    CU(s.in0.need((size_t)m * 56));
+    CU(s.out[0].need((size_t)m));
+    CU(cudaMemcpyAsync(s.in0.p, q + 7 * lo, (size_t)m * 56, cudaMemcpyHostToDevice, s.stream));
+    osr::k_disentangled<<<(unsigned)((m + 255) / 256), 256, 0, s.stream>>>(env_tf, bp, (const double*)s.in0.p,
+                                                                           (long long)m, (uint8_t*)s.out[0].p);
+    CU(cudaGetLastError());
+    w->host_counters.kernel_launches++;
+    CU(cudaMemcpyAsync(out + lo, s.out[0].p, (size_t)m, cudaMemcpyDeviceToHost, s.stream));
+  }
+  for (auto& s : w->slots) {
+    CU(cudaSetDevice(s.dev));
+    CU(cudaStreamSynchronize(s.stream));
+  }
+  return OSR_OK;
+}
+
+// ---- state-frame maps (host, fp64) --------------------------------------------------------------
+static void apply_perturbation(const double* pert, const double* in, double* out) {  // unit_world.cc:713-724
+  double r[4] = {in[3], in[4], in[5], in[6]}, p[4] = {pert[3], pert[4], pert[5], pert[6]};
+  osr::quat_normalize(r[0], r[1], r[2], r[3]);
+  osr::quat_normalize(p[0], p[1], p[2], p[3]);
+  double qr[4], R[9];
+  osr::quat_mul(p, r, qr);
+  osr::quat_to_rot(p[0], p[1], p[2], p[3], R);
+  double t[3];
+  for (int k = 0; k < 3; k++) t[k] = pert[k] + (R[3 * k] * in[0] + R[3 * k + 1] * in[1] + R[3 * k + 2] * in[2]);
+  osr::quat_normalize(qr[0], qr[1], qr[2], qr[3]);
+  out[0] = t[0]; out[1] = t[1]; out[2] = t[2];
+  out[3] = qr[0]; out[4] = qr[1]; out[5] = qr[2]; out[6] = qr[3];
+}
+static void unapply_perturbation(const double* pert, const double* in, double* out) {  // unit_world.cc:726-738
+  double r[4] = {in[3], in[4], in[5], in[6]}, p[4] = {pert[3], pert[4], pert[5], pert[6]};
+  osr::quat_normalize(r[0], r[1], r[2], r[3]);
+  osr::quat_normalize(p[0], p[1], p[2], p[3]);
+  double n2 = p[0] * p[0] + p[1] * p[1] + p[2] * p[2] + p[3] * p[3];
+  double pi[4] = {p[0] / n2, -p[1] / n2, -p[2] / n2, -p[3] / n2};  // Eigen inverse(): conj / squaredNorm
+  double R[9];
+  osr::quat_to_rot(pi[0], pi[1], pi[2], pi[3], R);
+  double d[3] = {-pert[0] + in[0], -pert[1] + in[1], -pert[2] + in[2]}, t[3], qr[4];
+  for (int k = 0; k < 3; k++) t[k] = R[3 * k] * d[0] + R[3 * k + 1] * d[1] + R[3 * k + 2] * d[2];
+  osr::quat_mul(pi, r, qr);
+  osr::quat_normalize(qr[0], qr[1], qr[2], qr[3]);
+  out[0] = t[0]; out[1] = t[1]; out[2] = t[2];
+  out[3] = qr[0]; out[4] = qr[1]; out[5] = qr[2]; out[6] = qr[3];
+}
+static void to_unit_one(const osr_world* w, const double* q, double* out) {  // unit_world.cc:526-539
+  double s = (double)w->scene_scale;
+  double tmp[7] = {s * q[0], s * q[1], s * q[2], q[3], q[4], q[5], q[6]};
+  apply_perturbation(w->perturb, tmp, out);
+}
+int osr_translate_to_unit(const osr_world* w, const double* q, int64_t n, double* out) {
+  if (!w || !w->finalized) return fail(OSR_EINVAL, "not finalized");
+  for (int64_t i = 0; i < n; i++) to_unit_one(w, q + 7 * i, out + 7 * i);
+  return OSR_OK;
+}
+int osr_translate_from_unit(const osr_world* w, const double* q, int64_t n, double* out) {  // unit_world.cc:541-555
+  if (!w || !w->finalized) return fail(OSR_EINVAL, "not finalized");
+  double inv = 1.0 / (double)w->scene_scale;
+  for (int64_t i = 0; i < n; i++) {
+    double tmp[7];
+    unapply_perturbation(w->perturb, q + 7 * i, tmp);
+    double* o = out + 7 * i;
+    o[0] = inv * tmp[0]; o[1] = inv * tmp[1]; o[2] = inv * tmp[2];
+    o[3] = tmp[3]; o[4] = tmp[4]; o[5] = tmp[5]; o[6] = tmp[6];
+  }
+  return OSR_OK;
+}
+// Eigen quaternion * vector: v + w*(2 u x v) + u x (2 u x v)
+static void quat_rotate(const double* q, const double* v, double* o) {
+  double u[3] = {q[1], q[2], q[3]};
+  double uv[3] = {u[1] * v[2] - u[2] * v[1], u[2] * v[0] - u[0] * v[2], u[0] * v[1] - u[1] * v[0]};
+  for (int k = 0; k < 3; k++) uv[k] += uv[k];
+  double c[3] = {u[1] * uv[2] - u[2] * uv[1], u[2] * uv[0] - u[0] * uv[2], u[0] * uv[1] - u[1] * uv[0]};
+  for (int k = 0; k < 3; k++) o[k] = v[k] + q[0] * uv[k] + c[k];
+}
+int osr_translate_ompl_to_unit(const osr_world* w, const double* qin, int64_t n, double* out) {  // unit_world.cc:689-711
+  if (!w || !w->finalized) return fail(OSR_EINVAL, "not finalized");
+  double dc[3];
+  for (int k = 0; k < 3; k++) dc[k] = (double)(w->ompl_centre[k] - w->centre[k]) * (double)w->scene_scale;
+  for (int64_t i = 0; i < n; i++) {
+    const double* q = qin + 7 * i;
+    double wf[7] = {q[0], q[1], q[2], q[6], q[3], q[4], q[5]}, u[7];
+    to_unit_one(w, wf, u);
+    double r[4] = {u[3], u[4], u[5], u[6]}, rot[3];
+    osr::quat_normalize(r[0], r[1], r[2], r[3]);
+    quat_rotate(r, dc, rot);
+    double* o = out + 7 * i;
+    for (int k = 0; k < 3; k++) o[k] = u[k] - rot[k];
+    o[3] = r[0]; o[4] = r[1]; o[5] = r[2]; o[6] = r[3];
+  }
+  return OSR_OK;
+}
+int osr_translate_unit_to_ompl(const osr_world* w, const double* qin, int64_t n, double* out) {  // unit_world.cc:557-591
+  if (!w || !w->finalized) return fail(OSR_EINVAL, "not finalized");
+  double dc[3];
+  for (int k = 0; k < 3; k++) dc[k] = (double)(w->ompl_centre[k] - w->centre[k]) * (double)w->scene_scale;
+  for (int64_t i = 0; i < n; i++) {
+    const double* q = qin + 7 * i;
+    double r[4] = {q[3], q[4], q[5], q[6]}, rot[3];
+    osr::quat_normalize(r[0], r[1], r[2], r[3]);
+    quat_rotate(r, dc, rot);
+    double shifted[7] = {q[0] + rot[0], q[1] + rot[1], q[2] + rot[2], r[0], r[1], r[2], r[3]}, v[7];
+    osr_translate_from_unit(w, shifted, 1, v);
+    double* o = out + 7 * i;
+    o[0] = v[0]; o[1] = v[1]; o[2] = v[2];
+    o[3] = v[4]; o[4] = v[5]; o[5] = v[6]; o[6] = v[3];
+  }
+  return OSR_OK;
+}
+
+double osr_distance(const double a[7], const double b[7]) { return osr::distance(a, b); }
+void osr_interpolate(const double a[7], const double b[7], double tau, double out[7]) { osr::interpolate(a, b, tau, out); }
+void osr_apply(const double from[7], const double tr[3], const double aa[3], double out[7]) { osr::apply(from, tr, aa, out); }
+
+// ---- visibility (batched isValidTransition) -----------------------------------------------------
+static int visibility_common(osr_world* w, const double* q0, int64_t m, int unit0, const double* q1, int64_t n,
+                             int unit1, double vmag, int8_t* out, bool pairwise) {
+  int rc = check_ready(w);
+  if (rc) return rc;
+  if (m <= 0 || n <= 0 || !q0 || !q1 || !out) return fail(OSR_EINVAL, "bad arguments");
+  std::vector<double> u0((size_t)m * 7), u1((size_t)n * 7);
+  if (unit0) memcpy(u0.data(), q0, (size_t)m * 56); else osr_translate_to_unit(w, q0, m, u0.data());
+  if (unit1) memcpy(u1.data(), q1, (size_t)n * 56); else osr_translate_to_unit(w, q1, n, u1.data());
+  int64_t total = pairwise ? std::max(m, n) : m * n;
+  std::vector<double> fr((size_t)total * 7), to((size_t)total * 7);
+  if (pairwise) {  // unit_world.cc:822-827: rows i % M and i % N
+    for (int64_t i = 0; i < total; i++) {
+      memcpy(&fr[(size_t)7 * i], &u0[(size_t)7 * (i % m)], 56);
+      memcpy(&to[(size_t)7 * i], &u1[(size_t)7 * (i % n)], 56);
+    }
+  } else {
+    for (int64_t i = 0; i < m; i++)
+      for (int64_t j = 0; j < n; j++) {
+        memcpy(&fr[(size_t)7 * (i * n + j)], &u0[(size_t)7 * i], 56);
+        memcpy(&to[(size_t)7 * (i * n + j)], &u1[(size_t)7 * j], 56);
+      }
+  }
+  std::vector<uint8_t> res((size_t)total);
+  rc = osr_is_valid_transitions(w, fr.data(), to.data(), total, vmag, res.data());
+  if (rc) return rc;
+  for (int64_t i = 0; i < total; i++) out[i] = (int8_t)res[i];
+  return OSR_OK;
+}
+int osr_visibility_matrix2(osr_world* w, const double* q0, int64_t m, int is_unit0, const double* q1, int64_t n,
+                           int is_unit1, double vmag, int8_t* out) {
+  return visibility_common(w, q0, m, is_unit0, q1, n, is_unit1, vmag, out, false);
+}
+int osr_visibility_pair(osr_world* w, const double* q0, int64_t m, int is_unit0, const double* q1, int64_t n,
+                        int is_unit1, double vmag, int8_t* out) {
+  return visibility_common(w, q0, m, is_unit0, q1, n, is_unit1, vmag, out, true);
+}
+
+// ---- contacts -----------------------------------------------------------------------------------
+int osr_intersecting_segments(osr_world* w, const double* q, int64_t n, int64_t cap, int64_t* offsets, double* seg,
+                              int32_t* faces, uint8_t* coplanar, double* bary, uint8_t* overflow, int64_t* total) {
+  int rc = check_ready(w);
+  if (rc) return rc;
+  if (n < 0 || cap < 0 || !offsets || (n > 0 && !q) || (cap > 0 && (!seg || !faces || !coplanar)))
+    return fail(OSR_EINVAL, "bad arguments");
+  std::lock_guard<std::mutex> lk(w->mu);
+  offsets[0] = 0;
+  if (overflow) memset(overflow, 0, (size_t)n);
+  if (total) *total = 0;
+  if (n == 0) return OSR_OK;
+  // Pass 1 (every device, index-range shards): all intersecting (state, env tri, rob tri) records.
+  int parts = (int)w->slots.size();
+  std::vector<std::vector<osr::ContactRec>> host_recs(parts);
+  std::vector<int64_t> los(parts);
+  for (int i = 0; i < parts; i++) {
+    Slot& s = w->slots[i];
+    int64_t lo, hi;
+    shard(n, parts, i, lo, hi);
+    los[i] = lo;
+    int64_t m = hi - lo;
+    if (m == 0) continue;
+    CU(cudaSetDevice(s.dev));
+    CU(s.in0.need((size_t)m * 56));
+    CU(cudaMemcpyAsync(s.in0.p, q + 7 * lo, (size_t)m * 56, cudaMemcpyHostToDevice, s.stream));
+    unsigned long long rec_cap = (unsigned long long)std::max<int64_t>(2 * cap + 1024, 1 << 16);
+    for (int attempt = 0; attempt < 2; attempt++) {
+      CU(s.recs.need((size_t)rec_cap * sizeof(osr::ContactRec)));
+      CU(cudaMemsetAsync(s.work, 0, 2 * sizeof(unsigned long long), s.stream));
+      osr::KParams P = w->params(s);
+      CU(cudaEventRecord(s.ev0, s.stream));
+      osr::k_contacts<<<s.grid_contacts, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK, s.stream>>>(
+          P, (const double*)s.in0.p, (long long)m, (osr::ContactRec*)s.recs.p, s.work + 1, rec_cap);
+      CU(cudaGetLastError());
+      CU(cudaEventRecord(s.ev1, s.stream));
+      w->host_counters.kernel_launches++;
+      unsigned long long found = 0;
+      CU(cudaMemcpyAsync(&found, s.work + 1, 8, cudaMemcpyDeviceToHost, s.stream));
+      rc = check_device_error(w, s);
+      if (rc) return rc;
+      if (found <= rec_cap) {
+        host_recs[i].resize((size_t)found);
+        if (found) CU(cudaMemcpy(host_recs[i].data(), s.recs.p, (size_t)found * sizeof(osr::ContactRec), cudaMemcpyDeviceToHost));
+        break;
+      }
+      if (attempt == 1) return fail(OSR_EOVERFLOW, "contact record buffer overflow");
+      rec_cap = found + 1024;  // exact size known now: run again
+    }
+  }
+  // Host: canonical order (state, env tri, rob tri), FCL row multiplicity, CSR offsets, truncation.
+  int64_t rows_found = 0, rows_written = 0;
+  std::vector<int64_t> per_state((size_t)n, 0);
+  for (int i = 0; i < parts; i++) {
+    auto& v = host_recs[i];
+    for (auto& r : v) r.state += (int)los[i];
+    std::sort(v.begin(), v.end(), [](const osr::ContactRec& a, const osr::ContactRec& b) {
+      if (a.state != b.state) return a.state < b.state;
+      if (a.env_tri != b.env_tri) return a.env_tri < b.env_tri;
+      return a.rob_tri < b.rob_tri;
+    });
+    for (auto& r : v) per_state[r.state] += r.mult;
+  }
+  for (int64_t i = 0; i < n; i++) {
+    rows_found += per_state[i];
+    int64_t room = cap - rows_written;
+    int64_t take = std::min(per_state[i], std::max<int64_t>(room, 0));
+    if (take < per_state[i] && overflow) overflow[i] = 1;
+    rows_written += take;
+    offsets[i + 1] = rows_written;
+  }
+  if (total) *total = rows_found;
+  // Pass 2: one thread per output row (Moeller segment + optional barycentrics), per device.
+  for (int i = 0; i < parts; i++) {
+    Slot& s = w->slots[i];
+    auto& v = host_recs[i];
+    if (v.empty()) continue;
+    std::vector<int> row_rec;
+    int64_t first_row = -1;
+    for (size_t r = 0; r < v.size(); r++) {
+      int st = v[r].state;
+      // rows of state st start at offsets[st]; records of a state are consecutive in v
+      if (r == 0 || v[r - 1].state != st) {
+        if (first_row < 0) first_row = offsets[st];
+      }
+      v[r].state -= (int)los[i];  // back to shard-local index for the device lookup
+    }
+    // rebuild row list honouring truncation
+    {
+      size_t r = 0;
+      while (r < v.size()) {
+        int st = v[r].state + (int)los[i];
+        int64_t budget = offsets[st + 1] - offsets[st];
+        while (r < v.size() && v[r].state + (int)los[i] == st) {
+          for (int k = 0; k < v[r].mult && budget > 0; k++, budget--) row_rec.push_back((int)r);
+          r++;
+        }
+      }
+    }
+    int64_t nrows = (int64_t)row_rec.size();
+    if (nrows == 0) continue;
+    CU(cudaSetDevice(s.dev));
+    CU(cudaMemcpyAsync(s.recs.p, v.data(), v.size() * sizeof(osr::ContactRec), cudaMemcpyHostToDevice, s.stream));
+    CU(s.rowrec.need((size_t)nrows * 4));
+    CU(cudaMemcpyAsync(s.rowrec.p, row_rec.data(), (size_t)nrows * 4, cudaMemcpyHostToDevice, s.stream));
+    CU(s.seg.need((size_t)nrows * 48));
+    CU(s.faces.need((size_t)nrows * 8));
+    CU(s.cop.need((size_t)nrows));
+    if (bary) CU(s.bary.need((size_t)nrows * 48));
+    osr::KParams P = w->params(s);
+    osr::k_contact_rows<<<(unsigned)((nrows + 127) / 128), 128, 0, s.stream>>>(
+        P, (const double*)s.in0.p, (const osr::ContactRec*)s.recs.p, (const int*)s.rowrec.p, (long long)nrows,
+        (double*)s.seg.p, (int*)s.faces.p, (uint8_t*)s.cop.p, bary ? (double*)s.bary.p : nullptr);
+    CU(cudaGetLastError());
+    w->host_counters.kernel_launches++;
+    CU(cudaMemcpyAsync(seg + 6 * first_row, s.seg.p, (size_t)nrows * 48, cudaMemcpyDeviceToHost, s.stream));
+    CU(cudaMemcpyAsync(faces + 2 * first_row, s.faces.p, (size_t)nrows * 8, cudaMemcpyDeviceToHost, s.stream));
+    CU(cudaMemcpyAsync(coplanar + first_row, s.cop.p, (size_t)nrows, cudaMemcpyDeviceToHost, s.stream));
+    if (bary) CU(cudaMemcpyAsync(bary + 6 * first_row, s.bary.p, (size_t)nrows * 48, cudaMemcpyDeviceToHost, s.stream));
+  }
+  for (auto& s : w->slots) {
+    CU(cudaSetDevice(s.dev));
+    CU(cudaStreamSynchronize(s.stream));
+  }
+  return OSR_OK;
+}
+
+// ---- key-configuration enumeration ---------------------------------------------------------------
+// Eigen Quaternion::setFromTwoVectors (unit inputs), the generic branch and the antiparallel
+// branch (axis from the smallest singular direction is replaced by any perpendicular vector:
+// the reference never hits it with opposing surface normals unless rob_n == env_n).
+static void quat_from_two_vectors(const double* a, const double* b, double* q) {
+  double la = std::sqrt(a[0] * a[0] + a[1] * a[1] + a[2] * a[2]), lb = std::sqrt(b[0] * b[0] + b[1] * b[1] + b[2] * b[2]);
+  double v0[3] = {a[0] / la, a[1] / la, a[2] / la}, v1[3] = {b[0] / lb, b[1] / lb, b[2] / lb};
+  double c = v1[0] * v0[0] + v1[1] * v0[1] + v1[2] * v0[2];
+  if (c < -1.0 + 1e-12) {
+    double h[3] = {1, 0, 0};
+    if (std::fabs(v0[0]) > 0.9) { h[0] = 0; h[1] = 1; }
+    double ax[3] = {v0[1] * h[2] - v0[2] * h[1], v0[2] * h[0] - v0[0] * h[2], v0[0] * h[1] - v0[1] * h[0]};
+    double l = std::sqrt(ax[0] * ax[0] + ax[1] * ax[1] + ax[2] * ax[2]);
+    q[0] = 0; q[1] = ax[0] / l; q[2] = ax[1] / l; q[3] = ax[2] / l;
+    return;
+  }
+  double ax[3] = {v0[1] * v1[2] - v0[2] * v1[1], v0[2] * v1[0] - v0[0] * v1[2], v0[0] * v1[1] - v0[1] * v1[0]};
+  double s = std::sqrt((1.0 + c) * 2.0), inv = 1.0 / s;
+  q[0] = s * 0.5; q[1] = ax[0] * inv; q[2] = ax[1] * inv; q[3] = ax[2] * inv;
+}
+
+int osr_enum_free_configurations(osr_world* w, const double* pts, int64_t b, double margin, int den, int only_median,
+                                 double* out_q, uint8_t* out_valid, int32_t* counts) {
+  int rc = check_ready(w);
+  if (rc) return rc;
+  if (b <= 0 || den <= 0 || !pts || !out_q || !out_valid) return fail(OSR_EINVAL, "bad arguments");
+  // unit_world.cc:1340-1389: rot_1 aligns rob_n with -env_n, rot_2 spins about env_n
+  const double PI2 = 2.0 * 3.14159265358979323846;
+  for (int64_t r = 0; r < b; r++) {
+    const double* ro = pts + 12 * r; const double* rn = ro + 3; const double* eo = ro + 6; const double* en = ro + 9;
+    double men[3] = {-en[0], -en[1], -en[2]}, rot1[4];
+    quat_from_two_vectors(rn, men, rot1);
+    double eo_m[3] = {eo[0] + en[0] * margin, eo[1] + en[1] * margin, eo[2] + en[2] * margin};
+    double ro_m[3] = {ro[0] + rn[0] * margin, ro[1] + rn[1] * margin, ro[2] + rn[2] * margin};
+    const double delta = PI2 / (double)den;
+    for (int i = 0; i < den; i++) {
+      double ang = (double)i * delta, sh = std::sin(0.5 * ang);
+      // Eigen AngleAxis -> Quaternion does not normalise the axis
+      double rot2[4] = {std::cos(0.5 * ang), sh * en[0], sh * en[1], sh * en[2]}, rot[4], p[3];
+      osr::quat_mul(rot2, rot1, rot);
+      quat_rotate(rot, ro_m, p);
+      double* o = out_q + 7 * (r * den + i);
+      osr::quat_normalize(rot[0], rot[1], rot[2], rot[3]);
+      o[0] = eo_m[0] - p[0]; o[1] = eo_m[1] - p[1]; o[2] = eo_m[2] - p[2];
+      o[3] = rot[0]; o[4] = rot[1]; o[5] = rot[2]; o[6] = rot[3];
+    }
+  }
+  rc = osr_is_valid_states(w, out_q, b * den, out_valid);
+  if (rc) return rc;
+  for (int64_t r = 0; r < b; r++) {
+    uint8_t* v = out_valid + r * den;
+    if (only_median) {  // keep the middle element of every contiguous valid run (:1375-1386)
+      std::vector<uint8_t> keep((size_t)den, 0);
+      int i = 0;
+      while (i < den) {
+        if (!v[i]) { i++; continue; }
+        int j = i;
+        while (j + 1 < den && v[j + 1]) j++;
+        // a run is only flushed by a following invalid sample; mid = begin + size/2
+        if (j + 1 < den) keep[(size_t)(i + (j - i + 1) / 2)] = 1;
+        i = j + 1;
+      }
+      memcpy(v, keep.data(), (size_t)den);
+    }
+    if (counts) {
+      int c = 0;
+      for (int i = 0; i < den; i++) c += v[i];
+      counts[r] = c;
+    }
+  }
+  return OSR_OK;
+}
+
+int osr_get_bvh_nodes(const osr_world* w, int which, float* out) {
+  if (!w || !w->host_ready) return fail(OSR_EINVAL, "geometry not built: call osr_finalize()");
+  const osr::UnitModel& m = which ? w->rob : w->env;
+  memcpy(out, m.bvh.nodes.data(), m.bvh.nodes.size() * 4);
+  return OSR_OK;
+}
+
+}  // extern "C"

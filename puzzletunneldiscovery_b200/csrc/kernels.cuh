@@ -287,3 +287,703 @@ __device__ __forceinline__ bool tri_pair_intersect(const Tri6<double>& td, unsig
   return r == 1;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Warp-cooperative traversal of one tile of poses.
+// ---------------------------------------------------------------------------------------------
+struct WarpCtx {
+  unsigned long long* spill;  // this warp's global spill area
+  int spill_cap;
+  int nspill;
+  unsigned n_bv, n_leaf, n_fp64, n_spill;
+  bool overflow;
+};
+
+__device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }
+
+// Contact record emitted by the all-contacts mode.
+struct ContactRec {
+  int state;     // index of the state in the batch
+  int env_tri;
+  int rob_tri;
+  int mult;      // number of rows FCL emits for this pair (0..2)
+};
+
+__device__ __forceinline__ unsigned contact_multiplicity_dev(const double* P, const double* Q, const double* Rd);
+
+enum { MODE_VALID = 0, MODE_SEGMENT = 1, MODE_CONTACTS = 2 };
+
+// alive: bit p set = pose p takes part.  Returns the mask of poses with at least one
+// intersecting triangle pair.  MODE_SEGMENT: once pose p hits, poses >= p are abandoned (only
+// the FIRST colliding step matters, unit_world.cc:452-458).  MODE_CONTACTS: no early out, every
+// intersecting pair is appended to `recs`.
+template <int MODE>
+__device__ __forceinline__ unsigned traverse_tile(const KParams& P, WarpShared& S, WarpCtx& C, unsigned alive,
+                                                  int lane, int state_base = 0, ContactRec* recs = nullptr,
+                                                  unsigned long long* rec_count = nullptr,
+                                                  unsigned long long rec_cap = 0) {
+  const unsigned ltmask = (1u << lane) - 1u;
+  unsigned dead = ~alive;
+  unsigned hits = 0;
+  int top = __popc(alive);
+  int nleaf = 0;
+  if (alive >> lane & 1u) S.stack[__popc(alive & ltmask)] = make_entry(lane, 0, 0);
+  __syncwarp();
+  while (true) {
+    if (top == 0 && C.nspill > 0) {  // refill from the global spill area
+      int take = min(C.nspill, SPILL_CHUNK);
+      for (int i = lane; i < take; i += 32) S.stack[i] = C.spill[C.nspill - take + i];
+      C.nspill -= take;
+      top = take;
+      __syncwarp();
+    }
+    if (top == 0 || nleaf >= 32) {
+      if (nleaf == 0) break;
+      // ---- leaf phase: up to 32 triangle pairs
+      int cnt = min(32, nleaf);
+      bool act = lane < cnt;
+      unsigned long long e = act ? S.leafq[nleaf - 1 - lane] : 0ull;
+      nleaf -= cnt;
+      unsigned pose = entry_pose(e);
+      act = act && !((dead >> pose) & 1u);
+      bool hit = false;
+      if (act) {
+        C.n_leaf++;
+        const double* tp = P.env.tris + (size_t)9 * entry_n1(e);
+        const double* tq = P.rob.tris + (size_t)9 * entry_n2(e);
+        Tri6<double> td;
+        load_pair_exact(tp, tq, &S.Rd[0][pose], td);
+        hit = tri_pair_intersect(td, C.n_fp64);
+        if (MODE == MODE_CONTACTS && hit) {
+          unsigned long long slot = atomicAdd(rec_count, 1ull);
+          if (slot < rec_cap) {
+            ContactRec r;
+            r.state = state_base + (int)pose;
+            r.env_tri = (int)entry_n1(e);
+            r.rob_tri = (int)entry_n2(e);
+            r.mult = (int)contact_multiplicity_dev(tp, tq, &S.Rd[0][pose]);
+            recs[slot] = r;
+          }
+        }
+      }
+      unsigned hm = __reduce_or_sync(FULL, hit ? (1u << pose) : 0u);
+      hits |= hm;
+      if (MODE == MODE_VALID) dead |= hm;
+      else if (MODE == MODE_SEGMENT) { if (hm) dead |= FULL << (__ffs(hm) - 1); }
+      __syncwarp();
+      continue;
+    }
+    if (top > STACK_CAP - 32) {  // make room: move the oldest entries to global memory
+      if (C.nspill + SPILL_CHUNK > C.spill_cap) { C.overflow = true; break; }
+      for (int i = lane; i < SPILL_CHUNK; i += 32) C.spill[C.nspill + i] = S.stack[i];
+      C.nspill += SPILL_CHUNK;
+      C.n_spill++;
+      int rem = top - SPILL_CHUNK;
+      for (int i0 = 0; i0 < rem; i0 += 32) {
+        unsigned long long v = (i0 + lane < rem) ? S.stack[SPILL_CHUNK + i0 + lane] : 0ull;
+        __syncwarp();
+        if (i0 + lane < rem) S.stack[i0 + lane] = v;
+      }
+      top = rem;
+      __syncwarp();
+    }
+    // ---- node phase: up to 32 box pairs
+    int cnt = min(32, top);
+    bool act = lane < cnt;
+    unsigned long long e = act ? S.stack[top - 1 - lane] : 0ull;
+    top -= cnt;
+    __syncwarp();
+    unsigned pose = entry_pose(e), n1 = entry_n1(e), n2 = entry_n2(e);
+    act = act && !((dead >> pose) & 1u);
+    bool leafpair = false, expand = false;
+    unsigned long long c0 = 0, c1 = 0, lf = 0;
+    if (act) {
+      C.n_bv++;
+      const float4* na = P.env.nodes + (size_t)4 * n1;
+      const float4* nb = P.rob.nodes + (size_t)4 * n2;
+      float4 a0 = ldg4(na), a1 = ldg4(na + 1), a2 = ldg4(na + 2), a3 = ldg4(na + 3);
+      float4 b0 = ldg4(nb), b1 = ldg4(nb + 1), b2 = ldg4(nb + 2), b3 = ldg4(nb + 3);
+      if (obb_overlap_f32(a0, a1, a2, a3, b0, b1, b2, b3, &S.Rf[0][pose], S.eta[pose])) {
+        int l1 = __float_as_int(a3.w), l2 = __float_as_int(b3.w);
+        if (l1 < 0 && l2 < 0) {
+          leafpair = true;
+          lf = make_entry(pose, (unsigned)(-(l1 + 1)), (unsigned)(-(l2 + 1)));
+        } else {
+          expand = true;
+          float s1 = a3.x * a3.x + a3.y * a3.y + a3.z * a3.z;
+          float s2 = b3.x * b3.x + b3.y * b3.y + b3.z * b3.z;
+          if (l2 < 0 || (l1 >= 0 && s1 > s2)) {  // descend the env node
+            c0 = make_entry(pose, (unsigned)l1, n2);
+            c1 = make_entry(pose, (unsigned)l1 + 1u, n2);
+          } else {
+            c0 = make_entry(pose, n1, (unsigned)l2);
+            c1 = make_entry(pose, n1, (unsigned)l2 + 1u);
+          }
+        }
+      }
+    }
+    unsigned bl = __ballot_sync(FULL, leafpair);
+    if (leafpair) S.leafq[nleaf + __popc(bl & ltmask)] = lf;
+    nleaf += __popc(bl);
+    unsigned be = __ballot_sync(FULL, expand);
+    if (expand) {
+      int off = top + 2 * __popc(be & ltmask);
+      S.stack[off] = c0;
+      S.stack[off + 1] = c1;
+    }
+    top += 2 * __popc(be);
+    __syncwarp();
+  }
+  return hits;
+}
+
+// Fill pose slot `lane` from a unit state.
+__device__ __forceinline__ void set_pose(const KParams& P, WarpShared& S, int lane, const double* q) {
+  Rigid rob, rel;
+  state_to_rigid(q, rob);
+  relative_rigid(P.env_tf, rob, rel);
+#pragma unroll
+  for (int k = 0; k < 9; k++) { S.Rd[k][lane] = rel.R[k]; S.Rf[k][lane] = (float)rel.R[k]; }
+#pragma unroll
+  for (int k = 0; k < 3; k++) { S.Rd[9 + k][lane] = rel.t[k]; S.Rf[9 + k][lane] = (float)rel.t[k]; }
+  S.eta[lane] = 2e-5f * (1.0f + fabsf((float)rel.t[0]) + fabsf((float)rel.t[1]) + fabsf((float)rel.t[2]));
+}
+
+__device__ __forceinline__ void ctx_init(const KParams& P, WarpCtx& C) {
+  int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  C.spill = P.spill + (size_t)gw * P.spill_cap;
+  C.spill_cap = P.spill_cap;
+  C.nspill = 0;
+  C.n_bv = C.n_leaf = C.n_fp64 = C.n_spill = 0;
+  C.overflow = false;
+}
+__device__ __forceinline__ void ctx_flush(const KParams& P, WarpCtx& C, unsigned long long poses, int lane) {
+  unsigned bv = __reduce_add_sync(FULL, C.n_bv), lf = __reduce_add_sync(FULL, C.n_leaf),
+           f64 = __reduce_add_sync(FULL, C.n_fp64);
+  if (lane == 0) {
+    atomicAdd(&P.counters->bv, (unsigned long long)bv);
+    atomicAdd(&P.counters->leaf, (unsigned long long)lf);
+    atomicAdd(&P.counters->fp64, (unsigned long long)f64);
+    atomicAdd(&P.counters->poses, poses);
+    if (C.n_spill) atomicAdd(&P.counters->spills, (unsigned long long)C.n_spill);
+    if (C.overflow) atomicExch(P.error_flag, 1);
+  }
+}
+
+constexpr int WARPS_PER_BLOCK = 4;
+
+// ---------------------------------------------------------------------------------------------
+// K1: batched validity.  out[i] = 1 iff state i is collision free (UnitWorld::isValid,
+// /root/reference/lib/osr/unit_world.cc:215-247).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_is_valid(KParams P, const double* __restrict__ q,
+                                                                    long long n, uint8_t* __restrict__ out) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  WarpShared& S = reinterpret_cast<WarpShared*>(smem_raw)[threadIdx.x >> 5];
+  const int lane = threadIdx.x & 31;
+  WarpCtx C;
+  ctx_init(P, C);
+  const long long ntiles = (n + 31) >> 5;
+  unsigned long long nposes = 0;
+  while (true) {
+    unsigned long long tile = 0;
+    if (lane == 0) tile = atomicAdd(P.work_counter, 1ull);
+    tile = __shfl_sync(FULL, tile, 0);
+    if ((long long)tile >= ntiles) break;
+    long long i = (long long)tile * 32 + lane;
+    bool have = i < n;
+    if (have) {
+      double s[7];
+#pragma unroll
+      for (int k = 0; k < 7; k++) s[k] = __ldg(q + 7 * i + k);
+      set_pose(P, S, lane, s);
+    }
+    unsigned alive = __ballot_sync(FULL, have);
+    nposes += __popc(alive);
+    __syncwarp();
+    unsigned hits = traverse_tile<MODE_VALID>(P, S, C, alive, lane);
+    if (have) out[i] = (hits >> lane & 1u) ? 0 : 1;
+    __syncwarp();
+    if (C.overflow) break;
+  }
+  ctx_flush(P, C, nposes, lane);
+}
+
+// ---------------------------------------------------------------------------------------------
+// K2: segment walk / first contact (UnitWorld::transitStateToWithContact,
+// /root/reference/lib/osr/unit_world.cc:405-474; isValidTransition :477-486).
+// One warp per segment; each tile is 32 consecutive steps of the reference's linear walk
+//   delta_1 = vd;  delta_{k+1} = delta_k < dist ? min(dist, delta_k + vd) : delta_k + vd
+// (the running fp64 sum is reproduced add by add so every tau is bit-identical), and the FIRST
+// colliding step is returned -- validity along a segment is not monotone, so no bisection.
+// ---------------------------------------------------------------------------------------------
+struct SegOut {
+  double* last_free;   // [n][7] or null
+  double* first_hit;   // [n][7] or null
+  uint8_t* is_free;    // [n] or null
+  double* free_tau;    // [n] or null
+  double* touch_tau;   // [n] or null
+  long long* steps;    // [n] or null
+};
+
+// transition_mode: vd := min(dist/2, vd) (isValidTransition)
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
+    k_transit(KParams P, const double* __restrict__ from, const double* __restrict__ to, long long n,
+              const double* __restrict__ vd_arr, long long vd_count, double vd_scalar, int transition_mode,
+              SegOut O) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  WarpShared& S = reinterpret_cast<WarpShared*>(smem_raw)[threadIdx.x >> 5];
+  const int lane = threadIdx.x & 31;
+  WarpCtx C;
+  ctx_init(P, C);
+  unsigned long long nposes = 0;
+  while (true) {
+    unsigned long long seg = 0;
+    if (lane == 0) seg = atomicAdd(P.work_counter, 1ull);
+    seg = __shfl_sync(FULL, seg, 0);
+    if ((long long)seg >= n) break;
+    double a[7], b[7];
+#pragma unroll
+    for (int k = 0; k < 7; k++) { a[k] = __ldg(from + 7 * seg + k); b[k] = __ldg(to + 7 * seg + k); }
+    double vd = vd_arr ? __ldg(vd_arr + (vd_count > 1 ? seg : 0)) : vd_scalar;
+    const double dist = distance(a, b);
+    if (transition_mode) vd = fmin(dist / 2.0, vd);
+    // results (warp-uniform)
+    bool free_flag = false;
+    double free_tau = 0.0, touch_tau = 1.0;
+    long long steps = 0;
+    double lf[7], fh[7];
+#pragma unroll
+    for (int k = 0; k < 7; k++) { lf[k] = a[k]; fh[k] = b[k]; }
+    if (!(vd >= dist)) {
+      const double inv_dist = 1.0 / dist;
+      double carry = 0.0;       // delta of the last step of the previous tile (0 before the first)
+      double prev_tau = 0.0;    // tau of that step
+      bool first = true;
+      long long k0 = 0;         // steps completed before this tile
+      bool done = false;
+      while (!done) {
+        // step deltas of this tile: lane j takes the (j+1)-th value after `carry`
+        double d = carry, mine = 0.0;
+        bool mine_ok = false, ok = true;
+#pragma unroll 1
+        for (int j = 0; j < 32; j++) {
+          if (first && j == 0) d = vd;
+          else if (d < dist) d = fmin(dist, d + vd);
+          else { d = d + vd; }
+          ok = ok && (d <= dist);
+          if (j == lane) { mine = d; mine_ok = ok; }
+        }
+        first = false;
+        carry = d;  // delta of slot 31 (only used when all 32 slots were valid)
+        double tau = mine * inv_dist;
+        if (mine_ok) {
+          double s[7];
+          interpolate(a, b, tau, s);
+          set_pose(P, S, lane, s);
+          S.tau[lane] = tau;
+        }
+        unsigned alive = __ballot_sync(FULL, mine_ok);
+        __syncwarp();
+        unsigned hits = traverse_tile<MODE_SEGMENT>(P, S, C, alive, lane);
+        if (C.overflow) { done = true; break; }
+        int nalive = __popc(alive);
+        if (hits) {
+          int j = __ffs(hits) - 1;
+          nposes += j + 1;
+          touch_tau = S.tau[j];
+          free_tau = j > 0 ? S.tau[j - 1] : prev_tau;
+          interpolate(a, b, touch_tau, fh);
+          if (j > 0 || k0 > 0) interpolate(a, b, free_tau, lf);
+          steps = k0 + j + 1;
+          free_flag = false;
+          done = true;
+        } else {
+          nposes += nalive;
+          k0 += nalive;
+          if (nalive > 0) prev_tau = S.tau[nalive - 1];
+          if (nalive < 32) {  // walked past dist: the whole segment is free
+            free_tau = prev_tau;
+            touch_tau = 0.0;  // the reference returns its shadowed outer `tau` (unit_world.cc:452-455,473)
+            interpolate(a, b, prev_tau, lf);
+#pragma unroll
+            for (int k = 0; k < 7; k++) fh[k] = lf[k];
+            steps = k0;
+            free_flag = true;
+            done = true;
+          }
+        }
+        __syncwarp();
+      }
+    }
+    if (lane == 0) {
+      if (O.is_free) O.is_free[seg] = free_flag ? 1 : 0;
+      if (O.free_tau) O.free_tau[seg] = free_tau;
+      if (O.touch_tau) O.touch_tau[seg] = touch_tau;
+      if (O.steps) O.steps[seg] = steps;
+    }
+    if (lane < 7) {
+      if (O.last_free) O.last_free[7 * seg + lane] = lf[lane];
+      if (O.first_hit) O.first_hit[7 * seg + lane] = fh[lane];
+    }
+    if (C.overflow) break;
+  }
+  ctx_flush(P, C, nposes, lane);
+}
+
+// ---------------------------------------------------------------------------------------------
+// K3: all contacts of a state + Moeller intersection segment per contact
+// (CDModel::collideForDetails, /root/reference/lib/osr/cdmodel.cc:200-229;
+//  UnitWorld::intersectingSegments, lib/osr/unit_world.cc:959-1012).
+// ---------------------------------------------------------------------------------------------
+
+// FCL emits one contact per "deepest point" (0..2) of an intersecting pair in enable_contact mode
+// (third-party/fcl/.../intersect-inl.h:801-849 with computeDeepestPoints :853-893 and
+// buildTrianglePlane :1040-1053); each contact becomes one facePairs row (cdmodel.cc:213-227).
+__device__ __forceinline__ bool tri_plane_dev(const double* v1, const double* v2, const double* v3, double* n,
+                                              double& t) {
+  double a[3] = {v2[0] - v1[0], v2[1] - v1[1], v2[2] - v1[2]};
+  double b[3] = {v3[0] - v1[0], v3[1] - v1[1], v3[2] - v1[2]};
+  double c[3];
+  crossT(a, b, c);
+  double sq = dotT(c, c);
+  if (sq > 0) {
+    double l = sqrt(sq);
+    n[0] = c[0] / l; n[1] = c[1] / l; n[2] = c[2] / l;
+    t = dotT(n, v1);
+    return true;
+  }
+  return false;
+}
+__device__ __forceinline__ void deepest_dev(const double (*pts)[3], const double* n, double t, double& depth,
+                                            unsigned& num) {
+  const double eps = 1e-5;
+  double max_depth = -1.7976931348623157e308;
+  unsigned cnt = 0, nneg = 0, npos = 0, nzero = 0;
+#pragma unroll
+  for (int i = 0; i < 3; i++) {
+    double dist = -(dotT(n, pts[i]) - t);
+    if (dist > eps) npos++; else if (dist < -eps) nneg++; else nzero++;
+    if (dist > max_depth) { max_depth = dist; cnt = 1; }
+    else if (dist + 1e-6 >= max_depth) cnt++;
+  }
+  if (max_depth < -eps) cnt = 0;
+  if (nzero == 0 && (nneg == 0 || npos == 0)) cnt = 0;
+  depth = max_depth;
+  num = cnt;
+}
+__device__ __forceinline__ unsigned contact_multiplicity_dev(const double* Pt, const double* Qt, const double* Rd) {
+  double R[12];
+#pragma unroll
+  for (int k = 0; k < 12; k++) R[k] = Rd[k * 32];
+  double P[3][3], Q[3][3];
+#pragma unroll
+  for (int v = 0; v < 3; v++) {
+    double x = __ldg(Qt + 3 * v), y = __ldg(Qt + 3 * v + 1), z = __ldg(Qt + 3 * v + 2);
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+      P[v][k] = __ldg(Pt + 3 * v + k);
+      Q[v][k] = (R[3 * k] * x + R[3 * k + 1] * y + R[3 * k + 2] * z) + R[9 + k];
+    }
+  }
+  double n1[3] = {0, 0, 0}, n2[3] = {0, 0, 0}, t1 = 0, t2 = 0, d1, d2;
+  unsigned k1, k2;
+  tri_plane_dev(P[0], P[1], P[2], n1, t1);
+  tri_plane_dev(Q[0], Q[1], Q[2], n2, t2);
+  deepest_dev(Q, n1, t1, d2, k2);
+  deepest_dev(P, n2, t2, d1, k1);
+  if (d1 > d2) return min(k2, 2u);
+  return min(k1, 2u);
+}
+
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
+    k_contacts(KParams P, const double* __restrict__ q, long long n, ContactRec* recs,
+               unsigned long long* rec_count, unsigned long long rec_cap) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  WarpShared& S = reinterpret_cast<WarpShared*>(smem_raw)[threadIdx.x >> 5];
+  const int lane = threadIdx.x & 31;
+  WarpCtx C;
+  ctx_init(P, C);
+  // tiles of 8 states: contact states run deep traversals, a few poses already fill the warp
+  const int TP = 8;
+  const long long ntiles = (n + TP - 1) / TP;
+  unsigned long long nposes = 0;
+  while (true) {
+    unsigned long long tile = 0;
+    if (lane == 0) tile = atomicAdd(P.work_counter, 1ull);
+    tile = __shfl_sync(FULL, tile, 0);
+    if ((long long)tile >= ntiles) break;
+    long long i = (long long)tile * TP + lane;
+    bool have = lane < TP && i < n;
+    if (have) {
+      double s[7];
+#pragma unroll
+      for (int k = 0; k < 7; k++) s[k] = __ldg(q + 7 * i + k);
+      set_pose(P, S, lane, s);
+    }
+    unsigned alive = __ballot_sync(FULL, have);
+    nposes += __popc(alive);
+    __syncwarp();
+    traverse_tile<MODE_CONTACTS>(P, S, C, alive, lane, (int)(tile * TP), recs, rec_count, rec_cap);
+    __syncwarp();
+    if (C.overflow) break;
+  }
+  ctx_flush(P, C, nposes, lane);
+}
+
+// --- Moeller 1997 interval-overlap test with intersection segment, fp64 -----------------------
+// Follows the published algorithm as used by the reference (lib/tritri/Moller97d.cc:579-717,
+// helpers :474-543, coplanar case :169-217) including its EPSILON=1e-6 snapping of the plane
+// distances.  Output: returns 1 if the triangles intersect; *coplanar set when both lie in one
+// plane (then no segment is produced).
+struct MollerIv {
+  double s0, s1;     // interval parameters
+  double p0[3], p1[3];
+};
+__device__ __forceinline__ void moller_isect2(const double* V0, const double* V1, const double* V2, double vv0,
+                                              double vv1, double vv2, double d0, double d1, double d2,
+                                              MollerIv& iv) {
+  double tmp = d0 / (d0 - d1);
+  iv.s0 = vv0 + (vv1 - vv0) * tmp;
+#pragma unroll
+  for (int k = 0; k < 3; k++) iv.p0[k] = tmp * (V1[k] - V0[k]) + V0[k];
+  tmp = d0 / (d0 - d2);
+  iv.s1 = vv0 + (vv2 - vv0) * tmp;
+#pragma unroll
+  for (int k = 0; k < 3; k++) iv.p1[k] = V0[k] + tmp * (V2[k] - V0[k]);
+}
+// returns true when the triangle lies in the other's plane
+__device__ __forceinline__ bool moller_interval(const double* V0, const double* V1, const double* V2, double vv0,
+                                                double vv1, double vv2, double d0, double d1, double d2,
+                                                double d0d1, double d0d2, MollerIv& iv) {
+  if (d0d1 > 0.0) moller_isect2(V2, V0, V1, vv2, vv0, vv1, d2, d0, d1, iv);
+  else if (d0d2 > 0.0) moller_isect2(V1, V0, V2, vv1, vv0, vv2, d1, d0, d2, iv);
+  else if (d1 * d2 > 0.0 || d0 != 0.0) moller_isect2(V0, V1, V2, vv0, vv1, vv2, d0, d1, d2, iv);
+  else if (d1 != 0.0) moller_isect2(V1, V0, V2, vv1, vv0, vv2, d1, d0, d2, iv);
+  else if (d2 != 0.0) moller_isect2(V2, V0, V1, vv2, vv0, vv1, d2, d0, d1, iv);
+  else return true;
+  return false;
+}
+__device__ __forceinline__ bool moller_edge_edge(const double* V0, const double* U0, const double* U1, int i0,
+                                                 int i1, double Ax, double Ay) {
+  double Bx = U0[i0] - U1[i0], By = U0[i1] - U1[i1];
+  double Cx = V0[i0] - U0[i0], Cy = V0[i1] - U0[i1];
+  double f = Ay * Bx - Ax * By;
+  double d = By * Cx - Bx * Cy;
+  if ((f > 0 && d >= 0 && d <= f) || (f < 0 && d <= 0 && d >= f)) {
+    double e = Ax * Cy - Ay * Cx;
+    if (f > 0) { if (e >= 0 && e <= f) return true; }
+    else { if (e <= 0 && e >= f) return true; }
+  }
+  return false;
+}
+__device__ __forceinline__ bool moller_edge_tri(const double* V0, const double* V1, const double* U0,
+                                                const double* U1, const double* U2, int i0, int i1) {
+  double Ax = V1[i0] - V0[i0], Ay = V1[i1] - V0[i1];
+  return moller_edge_edge(V0, U0, U1, i0, i1, Ax, Ay) || moller_edge_edge(V0, U1, U2, i0, i1, Ax, Ay) ||
+         moller_edge_edge(V0, U2, U0, i0, i1, Ax, Ay);
+}
+__device__ __forceinline__ bool moller_point_in_tri(const double* V0, const double* U0, const double* U1,
+                                                    const double* U2, int i0, int i1) {
+  double a = U1[i1] - U0[i1], b = -(U1[i0] - U0[i0]);
+  double c = -a * U0[i0] - b * U0[i1];
+  double d0 = a * V0[i0] + b * V0[i1] + c;
+  a = U2[i1] - U1[i1]; b = -(U2[i0] - U1[i0]);
+  c = -a * U1[i0] - b * U1[i1];
+  double d1 = a * V0[i0] + b * V0[i1] + c;
+  a = U0[i1] - U2[i1]; b = -(U0[i0] - U2[i0]);
+  c = -a * U2[i0] - b * U2[i1];
+  double d2 = a * V0[i0] + b * V0[i1] + c;
+  return d0 * d1 > 0.0 && d0 * d2 > 0.0;
+}
+__device__ __forceinline__ int moller_coplanar(const double* N, const double* V0, const double* V1,
+                                               const double* V2, const double* U0, const double* U1,
+                                               const double* U2) {
+  double A[3] = {fabs(N[0]), fabs(N[1]), fabs(N[2])};
+  int i0, i1;
+  if (A[0] > A[1]) {
+    if (A[0] > A[2]) { i0 = 1; i1 = 2; } else { i0 = 0; i1 = 1; }
+  } else {
+    if (A[2] > A[1]) { i0 = 0; i1 = 1; } else { i0 = 0; i1 = 2; }
+  }
+  if (moller_edge_tri(V0, V1, U0, U1, U2, i0, i1)) return 1;
+  if (moller_edge_tri(V1, V2, U0, U1, U2, i0, i1)) return 1;
+  if (moller_edge_tri(V2, V0, U0, U1, U2, i0, i1)) return 1;
+  if (moller_point_in_tri(V0, U0, U1, U2, i0, i1)) return 1;
+  if (moller_point_in_tri(U0, V0, V1, V2, i0, i1)) return 1;
+  return 0;
+}
+__device__ __forceinline__ int moller_isectline(const double (*V)[3], const double (*U)[3], int* coplanar,
+                                                double* pt1, double* pt2) {
+  const double EPS = 0.000001;
+  double E1[3], E2[3], N1[3], N2[3];
+#pragma unroll
+  for (int k = 0; k < 3; k++) { E1[k] = V[1][k] - V[0][k]; E2[k] = V[2][k] - V[0][k]; }
+  crossT(E1, E2, N1);
+  double d1 = -dotT(N1, V[0]);
+  double du0 = dotT(N1, U[0]) + d1, du1 = dotT(N1, U[1]) + d1, du2 = dotT(N1, U[2]) + d1;
+  if (fabs(du0) < EPS) du0 = 0.0;
+  if (fabs(du1) < EPS) du1 = 0.0;
+  if (fabs(du2) < EPS) du2 = 0.0;
+  double du0du1 = du0 * du1, du0du2 = du0 * du2;
+  if (du0du1 > 0.0 && du0du2 > 0.0) return 0;
+#pragma unroll
+  for (int k = 0; k < 3; k++) { E1[k] = U[1][k] - U[0][k]; E2[k] = U[2][k] - U[0][k]; }
+  crossT(E1, E2, N2);
+  double d2 = -dotT(N2, U[0]);
+  double dv0 = dotT(N2, V[0]) + d2, dv1 = dotT(N2, V[1]) + d2, dv2 = dotT(N2, V[2]) + d2;
+  if (fabs(dv0) < EPS) dv0 = 0.0;
+  if (fabs(dv1) < EPS) dv1 = 0.0;
+  if (fabs(dv2) < EPS) dv2 = 0.0;
+  double dv0dv1 = dv0 * dv1, dv0dv2 = dv0 * dv2;
+  if (dv0dv1 > 0.0 && dv0dv2 > 0.0) return 0;
+  double D[3];
+  crossT(N1, N2, D);
+  double mx = fabs(D[0]);
+  int idx = 0;
+  if (fabs(D[1]) > mx) { mx = fabs(D[1]); idx = 1; }
+  if (fabs(D[2]) > mx) { mx = fabs(D[2]); idx = 2; }
+  MollerIv A, B;
+  *coplanar = moller_interval(V[0], V[1], V[2], V[0][idx], V[1][idx], V[2][idx], dv0, dv1, dv2, dv0dv1, dv0dv2, A)
+                  ? 1 : 0;
+  if (*coplanar) return moller_coplanar(N1, V[0], V[1], V[2], U[0], U[1], U[2]);
+  moller_interval(U[0], U[1], U[2], U[0][idx], U[1][idx], U[2][idx], du0, du1, du2, du0du1, du0du2, B);
+  bool swapA = A.s0 > A.s1, swapB = B.s0 > B.s1;
+  double a0 = swapA ? A.s1 : A.s0, a1 = swapA ? A.s0 : A.s1;
+  double b0 = swapB ? B.s1 : B.s0, b1 = swapB ? B.s0 : B.s1;
+  if (a1 < b0 || b1 < a0) return 0;
+  const double* Alo = swapA ? A.p1 : A.p0; const double* Ahi = swapA ? A.p0 : A.p1;
+  const double* Blo = swapB ? B.p1 : B.p0; const double* Bhi = swapB ? B.p0 : B.p1;
+  const double* r1; const double* r2;
+  if (b0 < a0) { r1 = Alo; r2 = (b1 < a1) ? Bhi : Ahi; }
+  else { r1 = Blo; r2 = (b1 > a1) ? Ahi : Bhi; }
+#pragma unroll
+  for (int k = 0; k < 3; k++) { pt1[k] = r1[k]; pt2[k] = r2[k]; }
+  return 1;
+}
+
+// barycentric coordinates of p w.r.t. (a,b,c), areas ratio form
+__device__ __forceinline__ void barycentric_dev(const double* p, const double* a, const double* b, const double* c,
+                                                double* out) {
+  double v0[3] = {b[0] - a[0], b[1] - a[1], b[2] - a[2]}, v1[3] = {c[0] - a[0], c[1] - a[1], c[2] - a[2]},
+         v2[3] = {p[0] - a[0], p[1] - a[1], p[2] - a[2]};
+  double d00 = dotT(v0, v0), d01 = dotT(v0, v1), d11 = dotT(v1, v1), d20 = dotT(v2, v0), d21 = dotT(v2, v1);
+  double den = d00 * d11 - d01 * d01;
+  double v = (d11 * d20 - d01 * d21) / den, w = (d00 * d21 - d01 * d20) / den;
+  out[0] = 1.0 - v - w; out[1] = v; out[2] = w;
+}
+
+// One thread per output row.  row_rec[r] = index of the contact record the row belongs to.
+__global__ void k_contact_rows(KParams P, const double* __restrict__ q, const ContactRec* __restrict__ recs,
+                               const int* __restrict__ row_rec, long long nrows, double* __restrict__ seg,
+                               int* __restrict__ faces, uint8_t* __restrict__ coplanar, double* __restrict__ bary) {
+  long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= nrows) return;
+  ContactRec rec = recs[row_rec[r]];
+  double s[7];
+#pragma unroll
+  for (int k = 0; k < 7; k++) s[k] = __ldg(q + 7 * (long long)rec.state + k);
+  Rigid rob;
+  state_to_rigid(s, rob);
+  const double* Pt = P.env.tris + (size_t)9 * rec.env_tri;
+  const double* Qt = P.rob.tris + (size_t)9 * rec.rob_tri;
+  double V[3][3], U[3][3];
+#pragma unroll
+  for (int v = 0; v < 3; v++) {
+    double px = Pt[3 * v], py = Pt[3 * v + 1], pz = Pt[3 * v + 2];
+    double qx = Qt[3 * v], qy = Qt[3 * v + 1], qz = Qt[3 * v + 2];
+#pragma unroll
+    for (int k = 0; k < 3; k++) {   // world space: env_tf * v, rob_tf * v (unit_world.cc:981-982)
+      V[v][k] = (P.env_tf.R[3 * k] * px + P.env_tf.R[3 * k + 1] * py + P.env_tf.R[3 * k + 2] * pz) + P.env_tf.t[k];
+      U[v][k] = (rob.R[3 * k] * qx + rob.R[3 * k + 1] * qy + rob.R[3 * k + 2] * qz) + rob.t[k];
+    }
+  }
+  int cop = 0;
+  double p1[3] = {0, 0, 0}, p2[3] = {0, 0, 0};
+  moller_isectline(V, U, &cop, p1, p2);
+#pragma unroll
+  for (int k = 0; k < 3; k++) { seg[6 * r + k] = p1[k]; seg[6 * r + 3 + k] = p2[k]; }
+  faces[2 * r] = rec.env_tri;
+  faces[2 * r + 1] = rec.rob_tri;
+  coplanar[r] = (uint8_t)(cop != 0);
+  if (bary) {
+    double mid[3] = {0.5 * (p1[0] + p2[0]), 0.5 * (p1[1] + p2[1]), 0.5 * (p1[2] + p2[2])};
+    barycentric_dev(mid, V[0], V[1], V[2], bary + 6 * r);
+    barycentric_dev(mid, U[0], U[1], U[2], bary + 6 * r + 3);
+  }
+}
+
+}  // namespace osr
+
+namespace osr {
+// ---------------------------------------------------------------------------------------------
+// K4: bounding-box "disentangled" filter (UnitWorld::isDisentangled,
+// /root/reference/lib/osr/unit_world.cc:249-264 -> CDModel::collideBB, lib/osr/cdmodel.cc:180-197):
+// fcl::collide of the two models' local AABBs as fcl::Box shapes, robot first.  FCL routes
+// Box-Box to boxBoxIntersect (third-party/fcl/.../primitive_shape_algorithm/box_box-inl.h:827-1117,
+// 1395-1412): a 15-axis SAT, fp64, +1e-6 on |R| for the 9 edge axes only.  out = 1 iff separated.
+// ---------------------------------------------------------------------------------------------
+struct BoxPair {
+  double rob_c[3], rob_side[3];
+  double env_c[3], env_side[3];
+};
+__global__ void k_disentangled(Rigid env_tf, BoxPair bp, const double* __restrict__ q, long long n,
+                               uint8_t* __restrict__ out) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double s[7];
+#pragma unroll
+  for (int k = 0; k < 7; k++) s[k] = __ldg(q + 7 * i + k);
+  Rigid rob;
+  state_to_rigid(s, rob);
+  // tf1 = robTf * translate(rob centre), tf2 = envTf * translate(env centre)
+  double t1[3], t2[3];
+#pragma unroll
+  for (int k = 0; k < 3; k++) {
+    t1[k] = (rob.R[3 * k] * bp.rob_c[0] + rob.R[3 * k + 1] * bp.rob_c[1] + rob.R[3 * k + 2] * bp.rob_c[2]) + rob.t[k];
+    t2[k] = (env_tf.R[3 * k] * bp.env_c[0] + env_tf.R[3 * k + 1] * bp.env_c[1] + env_tf.R[3 * k + 2] * bp.env_c[2]) +
+            env_tf.t[k];
+  }
+  const double* R1 = rob.R;
+  const double* R2 = env_tf.R;
+  double p[3] = {t2[0] - t1[0], t2[1] - t1[1], t2[2] - t1[2]};
+  double pp[3], A[3], B[3], R[3][3], Q[3][3];
+#pragma unroll
+  for (int k = 0; k < 3; k++) {
+    pp[k] = R1[k] * p[0] + R1[3 + k] * p[1] + R1[6 + k] * p[2];
+    A[k] = bp.rob_side[k] * 0.5;
+    B[k] = bp.env_side[k] * 0.5;
+  }
+#pragma unroll
+  for (int a = 0; a < 3; a++)
+#pragma unroll
+    for (int b = 0; b < 3; b++) {
+      R[a][b] = R1[a] * R2[b] + R1[3 + a] * R2[3 + b] + R1[6 + a] * R2[6 + b];
+      Q[a][b] = fabs(R[a][b]);
+    }
+  bool sep = false;
+#pragma unroll
+  for (int a = 0; a < 3; a++)
+    sep |= fabs(pp[a]) - ((Q[a][0] * B[0] + Q[a][1] * B[1] + Q[a][2] * B[2]) + A[a]) > 0;
+#pragma unroll
+  for (int b = 0; b < 3; b++) {
+    double tmp = R2[b] * p[0] + R2[3 + b] * p[1] + R2[6 + b] * p[2];
+    sep |= fabs(tmp) - ((Q[0][b] * A[0] + Q[1][b] * A[1] + Q[2][b] * A[2]) + B[b]) > 0;
+  }
+#pragma unroll
+  for (int a = 0; a < 3; a++)
+#pragma unroll
+    for (int b = 0; b < 3; b++) Q[a][b] += 1.0e-6;
+#define OSR_EDGE(t, rhs) sep |= fabs(t) - (rhs) > 0
+  OSR_EDGE(pp[2] * R[1][0] - pp[1] * R[2][0], A[1] * Q[2][0] + A[2] * Q[1][0] + B[1] * Q[0][2] + B[2] * Q[0][1]);
+  OSR_EDGE(pp[2] * R[1][1] - pp[1] * R[2][1], A[1] * Q[2][1] + A[2] * Q[1][1] + B[0] * Q[0][2] + B[2] * Q[0][0]);
+  OSR_EDGE(pp[2] * R[1][2] - pp[1] * R[2][2], A[1] * Q[2][2] + A[2] * Q[1][2] + B[0] * Q[0][1] + B[1] * Q[0][0]);
+  OSR_EDGE(pp[0] * R[2][0] - pp[2] * R[0][0], A[0] * Q[2][0] + A[2] * Q[0][0] + B[1] * Q[1][2] + B[2] * Q[1][1]);
+  OSR_EDGE(pp[0] * R[2][1] - pp[2] * R[0][1], A[0] * Q[2][1] + A[2] * Q[0][1] + B[0] * Q[1][2] + B[2] * Q[1][0]);
+  OSR_EDGE(pp[0] * R[2][2] - pp[2] * R[0][2], A[0] * Q[2][2] + A[2] * Q[0][2] + B[0] * Q[1][1] + B[1] * Q[1][0]);
+  OSR_EDGE(pp[1] * R[0][0] - pp[0] * R[1][0], A[0] * Q[1][0] + A[1] * Q[0][0] + B[1] * Q[2][2] + B[2] * Q[2][1]);
+  OSR_EDGE(pp[1] * R[0][1] - pp[0] * R[1][1], A[0] * Q[1][1] + A[1] * Q[0][1] + B[0] * Q[2][2] + B[2] * Q[2][0]);
+  OSR_EDGE(pp[1] * R[0][2] - pp[0] * R[1][2], A[0] * Q[1][2] + A[1] * Q[0][2] + B[0] * Q[2][1] + B[1] * Q[2][0]);
+#undef OSR_EDGE
+  out[i] = sep ? 1 : 0;
+}
+}  // namespace osr
