@@ -64,6 +64,7 @@ def lib():
     L.orc_is_valid_transitions.argtypes = [C.c_void_p, _dp, _dp, C.c_longlong, C.c_double, _u8p, _llp, C.c_int]
     L.orc_intersecting_segments.argtypes = [C.c_void_p, _dp, C.c_longlong, C.c_longlong, _llp, _dp, _ip, _u8p, _llp]
     L.orc_intersecting_segments.restype = C.c_longlong
+    L.orc_is_disentangled_states.argtypes = [C.c_void_p, _dp, C.c_longlong, _u8p]
     L.orc_interpolate.argtypes = [_dp, _dp, C.c_double, _dp]
     L.orc_distance.argtypes = [_dp, _dp]
     L.orc_distance.restype = C.c_double
@@ -214,6 +215,13 @@ class OracleWorld:
 
     def is_valid_state(self, q):
         return bool(self.is_valid_states(q)[0])
+
+    def is_disentangled_states(self, q):
+        """unit_world.cc:249-264 per row."""
+        q = _states(q)
+        out = np.zeros(len(q), np.uint8)
+        self.L.orc_is_disentangled_states(self.h, _ptr(q, _dp), len(q), _ptr(out, _u8p))
+        return out
 
     def transit_states_to_with_contact(self, fr, to, vd, threads=0, counters=False):
         """unit_world.cc:405-474 per row -> (last_free, first_hit, is_free, free_tau, touch_tau)."""

@@ -641,6 +641,50 @@ struct World {
     finalized = true;
   }
 
+
+  // unit_world.cc:249-264 -> cdmodel.cc:180-197 -> FCL boxBoxIntersect
+  // (third-party/fcl/include/fcl/narrowphase/detail/primitive_shape_algorithm/box_box-inl.h:827-1117,1395-1412):
+  // the two local AABBs as boxes, robot first; 15-axis SAT, +1e-6 on |R| for the edge axes only.
+  bool is_disentangled(const double* q) const {
+    double lo1[3], hi1[3], lo2[3], hi2[3];
+    for (int k = 0; k < 3; k++) { lo1[k] = lo2[k] = std::numeric_limits<double>::max(); hi1[k] = hi2[k] = -lo1[k]; }
+    for (const V3& v : rob.V) for (int k = 0; k < 3; k++) { lo1[k] = std::min(lo1[k], v[k]); hi1[k] = std::max(hi1[k], v[k]); }
+    for (const V3& v : env.V) for (int k = 0; k < 3; k++) { lo2[k] = std::min(lo2[k], v[k]); hi2[k] = std::max(hi2[k], v[k]); }
+    V3 c1 = {(lo1[0] + hi1[0]) * 0.5, (lo1[1] + hi1[1]) * 0.5, (lo1[2] + hi1[2]) * 0.5};
+    V3 c2 = {(lo2[0] + hi2[0]) * 0.5, (lo2[1] + hi2[1]) * 0.5, (lo2[2] + hi2[2]) * 0.5};
+    double A[3], B[3];
+    for (int k = 0; k < 3; k++) { A[k] = (hi1[k] - lo1[k]) * 0.5; B[k] = (hi2[k] - lo2[k]) * 0.5; }
+    M3 R1 = qtorot({q[3], q[4], q[5], q[6]});
+    M3 R2 = qtorot({perturb[3], perturb[4], perturb[5], perturb[6]});
+    V3 t1 = mul(R1, c1) + V3{q[0], q[1], q[2]};
+    V3 t2 = mul(R2, c2) + V3{perturb[0], perturb[1], perturb[2]};
+    V3 p = t2 - t1;
+    V3 ppv = mulT(R1, p);
+    double pp[3] = {ppv.x, ppv.y, ppv.z};
+    M3 R = matmulTA(R1, R2);
+    double Q[3][3];
+    for (int a = 0; a < 3; a++) for (int b = 0; b < 3; b++) Q[a][b] = std::fabs(R(a, b));
+    for (int a = 0; a < 3; a++)
+      if (std::fabs(pp[a]) - ((Q[a][0] * B[0] + Q[a][1] * B[1] + Q[a][2] * B[2]) + A[a]) > 0) return true;
+    for (int b = 0; b < 3; b++) {
+      double tmp = R2(0, b) * p.x + R2(1, b) * p.y + R2(2, b) * p.z;
+      if (std::fabs(tmp) - ((Q[0][b] * A[0] + Q[1][b] * A[1] + Q[2][b] * A[2]) + B[b]) > 0) return true;
+    }
+    for (int a = 0; a < 3; a++) for (int b = 0; b < 3; b++) Q[a][b] += 1.0e-6;
+#define ORC_EDGE(t, rhs) if (std::fabs(t) - (rhs) > 0) return true
+    ORC_EDGE(pp[2] * R(1, 0) - pp[1] * R(2, 0), A[1] * Q[2][0] + A[2] * Q[1][0] + B[1] * Q[0][2] + B[2] * Q[0][1]);
+    ORC_EDGE(pp[2] * R(1, 1) - pp[1] * R(2, 1), A[1] * Q[2][1] + A[2] * Q[1][1] + B[0] * Q[0][2] + B[2] * Q[0][0]);
+    ORC_EDGE(pp[2] * R(1, 2) - pp[1] * R(2, 2), A[1] * Q[2][2] + A[2] * Q[1][2] + B[0] * Q[0][1] + B[1] * Q[0][0]);
+    ORC_EDGE(pp[0] * R(2, 0) - pp[2] * R(0, 0), A[0] * Q[2][0] + A[2] * Q[0][0] + B[1] * Q[1][2] + B[2] * Q[1][1]);
+    ORC_EDGE(pp[0] * R(2, 1) - pp[2] * R(0, 1), A[0] * Q[2][1] + A[2] * Q[0][1] + B[0] * Q[1][2] + B[2] * Q[1][0]);
+    ORC_EDGE(pp[0] * R(2, 2) - pp[2] * R(0, 2), A[0] * Q[2][2] + A[2] * Q[0][2] + B[0] * Q[1][1] + B[1] * Q[1][0]);
+    ORC_EDGE(pp[1] * R(0, 0) - pp[0] * R(1, 0), A[0] * Q[1][0] + A[1] * Q[0][0] + B[1] * Q[2][2] + B[2] * Q[2][1]);
+    ORC_EDGE(pp[1] * R(0, 1) - pp[0] * R(1, 1), A[0] * Q[1][1] + A[1] * Q[0][1] + B[0] * Q[2][2] + B[2] * Q[2][0]);
+    ORC_EDGE(pp[1] * R(0, 2) - pp[0] * R(1, 2), A[0] * Q[1][2] + A[1] * Q[0][2] + B[0] * Q[2][1] + B[1] * Q[2][0]);
+#undef ORC_EDGE
+    return false;
+  }
+
   // unit_world.cc:197-212 + geometry-inl.h:758-784
   void rel_tf(const double* q, M3& R, V3& T) const {
     M3 R1 = qtorot({perturb[3], perturb[4], perturb[5], perturb[6]});
@@ -746,6 +790,22 @@ struct World {
       int coplanar = 0;
       double p0[3] = {0, 0, 0}, p1[3] = {0, 0, 0};
       if (g_moller) g_moller(v[0], v[1], v[2], u[0], u[1], u[2], &coplanar, p0, p1);
+      // Moller97d.cc:671-672 ignores the "coplanar" return of the second interval computation: when
+      // all three snapped distances of U to V's plane are zero (but V is not in U's plane) the
+      // reference copies uninitialised stack memory into the end points.  That output is
+      // unspecified; oracle and engine both define it as the zero segment.
+      if (!coplanar) {
+        double e1[3], e2[3], n1[3];
+        for (int k = 0; k < 3; k++) { e1[k] = v[1][k] - v[0][k]; e2[k] = v[2][k] - v[0][k]; }
+        n1[0] = e1[1] * e2[2] - e1[2] * e2[1]; n1[1] = e1[2] * e2[0] - e1[0] * e2[2]; n1[2] = e1[0] * e2[1] - e1[1] * e2[0];
+        double d1 = -(n1[0] * v[0][0] + n1[1] * v[0][1] + n1[2] * v[0][2]);
+        bool allzero = true;
+        for (int k = 0; k < 3; k++) {
+          double du = (n1[0] * u[k][0] + n1[1] * u[k][1] + n1[2] * u[k][2]) + d1;
+          if (!((du >= 0 ? du : -du) < 0.000001)) allzero = false;
+        }
+        if (allzero) for (int k = 0; k < 3; k++) p0[k] = p1[k] = 0.0;
+      }
       for (int k = 0; k < 3; k++) segs.push_back(p0[k]);
       for (int k = 0; k < 3; k++) segs.push_back(p1[k]);
       cop.push_back((uint8_t)(coplanar != 0));
@@ -870,6 +930,10 @@ long long orc_intersecting_segments(void* h, const double* q, long long N, long 
     if (counters) { counters[2 * i] = c.bv; counters[2 * i + 1] = c.leaf; }
   }
   return total;
+}
+void orc_is_disentangled_states(void* h, const double* q, long long N, uint8_t* out) {
+  World* w = (World*)h;
+  for (long long i = 0; i < N; i++) out[i] = w->is_disentangled(q + 7 * i);
 }
 // state math
 void orc_interpolate(const double* a, const double* b, double tau, double* out) { orc::interpolate(a, b, tau, out); }

@@ -588,12 +588,12 @@ static void to_unit_one(const osr_world* w, const double* q, double* out) {  // 
   apply_perturbation(w->perturb, tmp, out);
 }
 int osr_translate_to_unit(const osr_world* w, const double* q, int64_t n, double* out) {
-  if (!w || !w->finalized) return fail(OSR_EINVAL, "not finalized");
+  if (!w || !w->host_ready) return fail(OSR_EINVAL, "geometry not built: call osr_finalize()");
   for (int64_t i = 0; i < n; i++) to_unit_one(w, q + 7 * i, out + 7 * i);
   return OSR_OK;
 }
 int osr_translate_from_unit(const osr_world* w, const double* q, int64_t n, double* out) {  // unit_world.cc:541-555
-  if (!w || !w->finalized) return fail(OSR_EINVAL, "not finalized");
+  if (!w || !w->host_ready) return fail(OSR_EINVAL, "geometry not built: call osr_finalize()");
   double inv = 1.0 / (double)w->scene_scale;
   for (int64_t i = 0; i < n; i++) {
     double tmp[7];
@@ -613,7 +613,7 @@ static void quat_rotate(const double* q, const double* v, double* o) {
   for (int k = 0; k < 3; k++) o[k] = v[k] + q[0] * uv[k] + c[k];
 }
 int osr_translate_ompl_to_unit(const osr_world* w, const double* qin, int64_t n, double* out) {  // unit_world.cc:689-711
-  if (!w || !w->finalized) return fail(OSR_EINVAL, "not finalized");
+  if (!w || !w->host_ready) return fail(OSR_EINVAL, "geometry not built: call osr_finalize()");
   double dc[3];
   for (int k = 0; k < 3; k++) dc[k] = (double)(w->ompl_centre[k] - w->centre[k]) * (double)w->scene_scale;
   for (int64_t i = 0; i < n; i++) {
@@ -630,7 +630,7 @@ int osr_translate_ompl_to_unit(const osr_world* w, const double* qin, int64_t n,
   return OSR_OK;
 }
 int osr_translate_unit_to_ompl(const osr_world* w, const double* qin, int64_t n, double* out) {  // unit_world.cc:557-591
-  if (!w || !w->finalized) return fail(OSR_EINVAL, "not finalized");
+  if (!w || !w->host_ready) return fail(OSR_EINVAL, "geometry not built: call osr_finalize()");
   double dc[3];
   for (int k = 0; k < 3; k++) dc[k] = (double)(w->ompl_centre[k] - w->centre[k]) * (double)w->scene_scale;
   for (int64_t i = 0; i < n; i++) {

@@ -846,7 +846,11 @@ __device__ __forceinline__ int moller_isectline(const double (*V)[3], const doub
   *coplanar = moller_interval(V[0], V[1], V[2], V[0][idx], V[1][idx], V[2][idx], dv0, dv1, dv2, dv0dv1, dv0dv2, A)
                   ? 1 : 0;
   if (*coplanar) return moller_coplanar(N1, V[0], V[1], V[2], U[0], U[1], U[2]);
-  moller_interval(U[0], U[1], U[2], U[0][idx], U[1][idx], U[2][idx], du0, du1, du2, du0du1, du0du2, B);
+  if (moller_interval(U[0], U[1], U[2], U[0][idx], U[1][idx], U[2][idx], du0, du1, du2, du0du1, du0du2, B)) {
+    // U snapped into V's plane while V is not in U's: the reference reads uninitialised memory
+    // here (Moller97d.cc:671-672 ignores this return value); defined as the zero segment.
+    return 1;
+  }
   bool swapA = A.s0 > A.s1, swapB = B.s0 > B.s1;
   double a0 = swapA ? A.s1 : A.s0, a1 = swapA ? A.s0 : A.s1;
   double b0 = swapB ? B.s1 : B.s0, b1 = swapB ? B.s0 : B.s1;
