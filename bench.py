@@ -1,0 +1,369 @@
+#!/usr/bin/env python
+"""bench.py -- throughput of the collision hot path on B200 (driver contract, see DESIGN.md "Measurement").
+
+A "step" is one pass of batched is_valid_state over one batch of 2^20 seeded uniform unit-SE(3) states on
+the alpha-1.2 puzzle (BASELINE.json configs[0], the configuration the metric's 1e9 configs/s target is
+quoted on).  Every rank owns one GPU, a replicated copy of the geometry and its own batches (weak scaling,
+no collective on the data path; torch.distributed is only used for the barrier and the max-over-ranks time).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--states S] [--no-touch]
+
+One JSON line is printed by rank 0.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "SE(3) configs/sec validity-checked (alpha-1.2, batched is_valid_state)"
+UNIT = "configs/s"
+NBATCH = 8                     # distinct resident batches rotated through: 8 x 56 MiB > 126 MB of L2
+VD_TOUCH = 0.0125 / 8          # /root/reference/src/GP/condor_touch_configuration.py:35,92
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--states", type=int, default=1 << 20)
+    ap.add_argument("--touch-segments", type=int, default=1 << 16)
+    ap.add_argument("--no-touch", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def env_rank():
+    return int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+
+
+def make_world(cls, **kw):
+    from puzzletunneldiscovery_b200 import workloads as W
+    A = W.assets_dir()
+    w = cls(**kw)
+    w.loadModelFromFile(os.path.join(A, "alpha_env-1.2.org.obj"))
+    w.loadRobotFromFile(os.path.join(A, "alpha-1.2.org.obj"))
+    w.scaleToUnit()
+    w.angleModel(0.0, 0.0)
+    return w
+
+
+def hbm_peak():
+    """Roofline denominator: the driver-measured copy bandwidth, else the profiling guide's fallback."""
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def physical_index(local_rank):
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    if vis:
+        try:
+            return int(vis.split(",")[local_rank])
+        except Exception:
+            return local_rank
+    return local_rank
+
+
+def workload_config(n):
+    return {"workload": "alpha-1.2 (G-org: 1008 x 1008 triangles) batched is_valid_state, %d seeded uniform "
+                        "unit-SE(3) states per step per GPU" % n,
+            "states_per_step_per_gpu": n, "sharding": "replicated geometry, disjoint seeded batches per rank",
+            "l2": "inputs larger than L2: %d resident batches of %.0f MiB rotated" % (NBATCH, n * 56 / 2**20)}
+
+
+def batch_seed(rank, b):
+    return 1000 * rank + b
+
+
+def algorithmic_bytes(n, rank, b):
+    """per validity check 57 B of I/O + 128 B per OBB-pair test + 72 B per triangle-pair
+    test, with the ORACLE's FCL-order DFS counts (tests/golden/counters_org.json, written by
+    tests/golden/make_counters.py).  Seeds without an own entry use the per-state mean."""
+    with open(os.path.join(ROOT, "tests", "golden", "counters_org.json")) as f:
+        cj = json.load(f)
+    key = str(batch_seed(rank, b))
+    if key in cj["per_seed"] and cj["per_seed"][key]["n"] == n:
+        e = cj["per_seed"][key]
+        return 57 * n + 128 * e["sum_bv"] + 72 * e["sum_leaf"]
+    return n * (57 + 128 * cj["mean_bv"] + 72 * cj["mean_leaf"])
+
+
+# ---- clocks sampled DURING the timed region (B200_PROFILING.md "clocks line") --------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows = []
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.perf_counter(), line.strip()))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for t, line in self.rows:
+            if t < t0 or t > t1 + 0.2:
+                continue
+            p = [x.strip() for x in line.split(",")]
+            try:
+                sm.append(float(p[0])); mx.append(float(p[1]))
+            except Exception:
+                continue
+            for nm, v in zip(names, p[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---- reference arm: the CPU implementation of the path on the host cores ------------------------------
+def run_reference(args):
+    """`--impl reference`: the reference's own CPU path.  pyosr/FCL cannot be compiled in this image (Eigen,
+    assimp, libccd absent -- DESIGN.md), so this times the oracle port of it (same algorithm: fp64 OBB-BVH
+    DFS + SAT-17 per state, OpenMP over states like calculateVisibilityPair) with every host thread, on
+    the same seeded batches."""
+    rank, _, world = env_rank()
+    if rank != 0:
+        return
+    from oracle import oracle as O
+    from puzzletunneldiscovery_b200 import workloads as W
+    ow = make_world(O.OracleWorld)
+    n = args.states
+    cores = O.lib().orc_max_threads()
+    qs = [W.random_states(n, batch_seed(0, b)) for b in range(min(NBATCH, args.steps + args.warmup))]
+    for i in range(args.warmup):
+        ow.is_valid_states(qs[i % len(qs)][: n // 8])
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        ow.is_valid_states(qs[i % len(qs)])
+    dt = time.perf_counter() - t0
+    val = n * args.steps / dt
+    sample = "%d steps x %d states (full batches), oracle port, %d OpenMP threads" % (args.steps, n, cores)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(n),
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+# ---- our arm ------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from puzzletunneldiscovery_b200 import pyosr, workloads as W
+    from puzzletunneldiscovery_b200._lib import check
+
+    rank, local_rank, world = env_rank()
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: the engine has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    dev = torch.device("cuda", local_rank)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    uw = make_world(pyosr.UnitWorld, devices=[local_rank])
+    L, h = uw._L, uw._h
+    stream = torch.cuda.ExternalStream(L.osr_stream(h), device=dev)
+    n, K, Wm = args.states, args.steps, args.warmup
+
+    # inputs: NBATCH distinct seeded batches, pinned on the host and resident in HBM
+    host_q = [torch.from_numpy(W.random_states(n, batch_seed(rank, b))).pin_memory() for b in range(NBATCH)]
+    dev_q = [q.to(dev) for q in host_q]
+    dev_out = torch.empty(n, dtype=torch.uint8, device=dev)
+    host_out = torch.empty(n, dtype=torch.uint8).pin_memory()
+    torch.cuda.synchronize()
+
+    def launch(b):
+        check(L.osr_is_valid_states_device(h, C.c_void_p(dev_q[b].data_ptr()), n, C.c_void_p(dev_out.data_ptr())))
+
+    # ---- device-resident throughput: W warm-up + K timed steps, events on the launching stream
+    for i in range(Wm):
+        launch(i % NBATCH)
+    check(L.osr_sync(h))
+    uw.counters(reset=True)
+    sampler = ClockSampler(physical_index(local_rank)) if rank == 0 else None
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    t0 = time.perf_counter()
+    e0.record(stream)
+    for i in range(K):
+        launch((Wm + i) % NBATCH)
+    e1.record(stream)
+    check(L.osr_sync(h))
+    barrier()
+    t1 = time.perf_counter()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_total = float(ms.item())
+    ctr = uw.counters(reset=True)
+    launches = ctr["kernel_launches"]
+    value = world * n * K / (ms_total * 1e-3)
+
+    # ---- per-launch kernel time (events recorded by the engine around the kernel itself) + roofline
+    kms = []
+    for i in range(K):
+        launch((Wm + i) % NBATCH)
+        f = C.c_float(0)
+        check(L.osr_last_kernel_ms(h, C.byref(f)))
+        kms.append(f.value)
+    kernel_ms = float(np.mean(kms))
+    alg = float(np.mean([algorithmic_bytes(n, rank, (Wm + i) % NBATCH) for i in range(K)]))
+    peak, peak_src = hbm_peak()
+    achieved = alg / (kernel_ms * 1e-3) / 1e9
+    gctr = uw.counters(reset=True)
+
+    # ---- end to end through the C ABI with HOST buffers (pinned): H2D + kernel + D2H inside the timed region
+    def e2e_call(b):
+        check(L.osr_is_valid_states(h, C.cast(host_q[b].data_ptr(), C.POINTER(C.c_double)), n,
+                                    C.cast(host_out.data_ptr(), C.POINTER(C.c_uint8))))
+    for i in range(Wm):
+        e2e_call(i % NBATCH)
+    barrier()
+    te0 = time.perf_counter()
+    for i in range(K):
+        e2e_call((Wm + i) % NBATCH)
+    barrier()
+    te = torch.tensor([time.perf_counter() - te0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_value = world * n * K / float(te.item())
+    valid_frac = float(host_out.numpy().mean())
+    clocks = sampler.stop(t0, t1) if sampler else None
+
+    # ---- second half of the metric: touch segments/s (config 2 semantics, bounded size)
+    touch = None
+    if not args.no_touch:
+        S = args.touch_segments
+        q0 = host_q[0].numpy()[: 1 << 16]
+        ok = uw.is_valid_states(q0) & ~uw.is_disentangled_states(q0)
+        fr, to = W.touch_rays(q0[ok][:1024], S, seed=1 + rank)
+        d_fr, d_to = torch.from_numpy(fr).to(dev), torch.from_numpy(to).to(dev)
+        d_lf = torch.empty((S, 7), dtype=torch.float64, device=dev); d_fh = torch.empty_like(d_lf)
+        d_free = torch.empty(S, dtype=torch.uint8, device=dev)
+        d_ft = torch.empty(S, dtype=torch.float64, device=dev); d_tt = torch.empty_like(d_ft)
+        d_st = torch.empty(S, dtype=torch.int64, device=dev)
+        p = lambda t: C.c_void_p(t.data_ptr())
+
+        def tlaunch():
+            check(L.osr_transit_states_device(h, p(d_fr), p(d_to), S, VD_TOUCH, p(d_lf), p(d_fh), p(d_free), p(d_ft),
+                                              p(d_tt), p(d_st)))
+        tlaunch(); check(L.osr_sync(h))
+        reps = 3
+        barrier()
+        e0.record(stream)
+        for _ in range(reps):
+            tlaunch()
+        e1.record(stream)
+        check(L.osr_sync(h))
+        barrier()
+        tms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        steps_sum = d_st.sum().to(torch.float64)
+        if world > 1:
+            dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+            dist.all_reduce(steps_sum, op=dist.ReduceOp.SUM)
+            steps_total = float(steps_sum.item())
+        else:
+            steps_total = float(steps_sum.item())
+        tsec = float(tms.item()) * 1e-3 / reps
+        touch = {"segments_per_s": world * S / tsec, "validity_checks_per_s": steps_total / tsec,
+                 "segments": world * S, "verify_delta": VD_TOUCH, "free_fraction": float(d_free.float().mean().item()),
+                 "mean_steps_per_segment": steps_total / (world * S)}
+
+    # ---- CPU baseline on the box's host cores (rank 0, N=1 only): the oracle port, bounded sample
+    cpu = None
+    match = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        from oracle import oracle as O
+        ow = make_world(O.OracleWorld)
+        cores = O.lib().orc_max_threads()
+        qs = host_q[0].numpy()
+        ow.is_valid_states(qs[:4096])
+        tc = time.perf_counter()
+        vo = ow.is_valid_states(qs)
+        dtc = time.perf_counter() - tc
+        cpu = {"value": n / dtc, "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": "one full batch of %d states (seed %d), oracle port, %d OpenMP threads, %.1f s" %
+                         (n, batch_seed(0, 0), cores, dtc)}
+        e2e_call(0)
+        match = bool(np.array_equal(host_out.numpy().astype(bool), vo.astype(bool)))
+
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank != 0:
+        return
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
+        "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32 box tests + f32-filtered/f64-exact triangle SAT", "data": "synthetic",
+        "config": workload_config(n),
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak if peak else None, "traffic": None, "peak_source": peak_src,
+                     "kernel": "k_is_valid", "kernel_ms": kernel_ms, "algorithmic_bytes_per_launch": alg,
+                     "note": "algorithmic bytes = 57 B/state + 128 B x oracle OBB tests + 72 B x oracle triangle "
+                             "tests (SURVEY 8(d) D8); the working set (0.33 MB) lives in L1/L2, so the HBM "
+                             "fraction is small by construction -- see DESIGN.md"},
+        "cpu_baseline": cpu,
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n * 56, "d2h_bytes_per_step": n},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "valid_fraction": valid_frac,
+        "engine_counters_per_state": {"bv_tests": gctr["bv_tests"] / max(1, gctr["poses"]),
+                                      "leaf_tests": gctr["leaf_tests"] / max(1, gctr["poses"]),
+                                      "fp64_rechecks": gctr["fp64_rechecks"] / max(1, gctr["poses"])},
+        "labels_match_oracle": match,
+        "touch": touch,
+    }
+    print(json.dumps(out))
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

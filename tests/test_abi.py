@@ -1,0 +1,134 @@
+"""CPU-only checks of the drop-in boundary: libosrgpu.so loads, exports every symbol include/osrgpu.h
+declares (and the ctypes table binds exactly those), the host-side geometry front end matches the
+oracle's unit-world frame, and -- without a CUDA device -- every query fails loudly (no CPU fallback)."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import ASSETS, ROOT, _has_cuda, make_world
+from puzzletunneldiscovery_b200 import _lib, pyosr, workloads as W
+
+
+def _header_symbols():
+    src = open(os.path.join(ROOT, "include", "osrgpu.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(osr_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    names = _header_symbols()
+    assert len(names) >= 35
+    L = C.CDLL(_lib.library_path())
+    for n in names:
+        assert hasattr(L, n), "libosrgpu.so does not export " + n
+    assert sorted(_lib.SIGNATURES) == names  # the Python binding covers the header, nothing more
+
+
+def test_no_torch_types_in_the_abi():
+    src = open(os.path.join(ROOT, "include", "osrgpu.h")).read()
+    assert "torch" not in src and "at::" not in src and 'extern "C"' in src
+
+
+def test_module_level_state_functions_match_oracle(oracle_mod):
+    rs = np.random.RandomState(0)
+    qs = W.random_states(64, 5)
+    for i in range(0, 64, 2):
+        a, b = qs[i], qs[i + 1]
+        assert pyosr.distance(a, b) == oracle_mod.distance(a, b)
+        tau = rs.rand()
+        assert np.array_equal(pyosr.interpolate(a, b, tau), oracle_mod.interpolate(a, b, tau))
+        tr, aa = rs.randn(3), rs.randn(3)
+        assert np.array_equal(pyosr.apply(a, tr, aa), oracle_mod.apply(a, tr, aa))
+    assert np.array_equal(pyosr.multi_distance(qs[0], qs[1:5]),
+                          np.array([oracle_mod.distance(qs[0], q) for q in qs[1:5]]))
+    assert pyosr.STATE_DIMENSION == 7
+    assert np.array_equal(pyosr.get_identity_state_vector(), [0, 0, 0, 1, 0, 0, 0])
+
+
+def _host_world(which, centre=None):
+    """Geometry front end only: osr_finalize builds the unit meshes + BVH on the host and, on a box
+    without a GPU, returns OSR_ENODEV after doing so."""
+    try:
+        return make_world(pyosr.UnitWorld, which, centre), True
+    except _lib.OsrError as e:
+        assert "no CUDA device" in str(e)
+    envf, robf = W.REF_ALPHA_FILES[which]
+    w = pyosr.UnitWorld()
+    w.loadModelFromFile(os.path.join(ASSETS, envf))
+    w.loadRobotFromFile(os.path.join(ASSETS, robf))
+    if centre is not None:
+        w.enforceRobotCenter(centre)
+    with pytest.raises(_lib.OsrError):
+        w.angleModel(0.0, 0.0)
+    return w, False
+
+
+@pytest.mark.parametrize("which,centre", [("org", None), ("wt2", W.ROB_OMPL_CENTER)])
+def test_unit_world_frame_equals_oracle(which, centre, oracle_mod):
+    w, _ = _host_world(which, centre)
+    ow = make_world(oracle_mod.OracleWorld, which, centre)
+    assert w.scene_scale == ow.scene_scale
+    assert np.array_equal(w.robot_center, ow.robot_center)
+    for g in (0, 1):
+        V, F = w._geometry(g)
+        Vo, Fo = ow.unit_geometry(g)
+        # same triangle soup, bit for bit (vertex numbering may differ: the engine drops unreferenced v rows)
+        assert np.array_equal(V[F], Vo[Fo])
+        nv, nf, nn, depth = w.mesh_sizes(g)
+        assert nn == 2 * nf - 1 and depth < 40
+
+
+def test_bvh_is_conservative_on_host():
+    w, _ = _host_world("org")
+    for g in (0, 1):
+        V, F = w._geometry(g)
+        nodes = w.bvh_nodes(g)
+        link = nodes[:, 15].copy().view(np.int32)
+        nd = nodes.astype(np.float64)
+        leaves = np.nonzero(link < 0)[0]
+        assert len(leaves) == len(F)
+        assert sorted(-(link[leaves] + 1)) == list(range(len(F)))
+        for i in leaves:
+            A = nd[i, :12].reshape(3, 4)
+            P = V[F[-(link[i] + 1)]] - A[:, 3]
+            assert (np.abs(P @ A[:, :3].T) <= nd[i, 12:15] + 1e-12).all()
+
+
+def test_errors_are_runtime_errors_like_the_reference():
+    w = pyosr.UnitWorld()
+    with pytest.raises(RuntimeError):  # unit_world.cc:140-142
+        w.angleModel(0.1, 0.0)
+    with pytest.raises(RuntimeError):
+        w.loadModelFromFile("/nonexistent/mesh.obj")
+    with pytest.raises(RuntimeError):  # query before scaleToUnit/angleModel
+        w.is_valid_states(np.zeros((1, 7)))
+    with pytest.raises(RuntimeError):  # robot missing
+        w.loadModelFromFile(os.path.join(ASSETS, "alpha_env-1.2.org.obj"))
+        w.angleModel(0.0, 0.0)
+
+
+@pytest.mark.skipif(_has_cuda(), reason="checks the behaviour on a box without a GPU")
+def test_no_cpu_fallback_without_a_device():
+    w, on_gpu = _host_world("org")
+    assert not on_gpu
+    q = W.random_states(8, 0)
+    for call in (lambda: w.is_valid_states(q), lambda: w.is_disentangled_states(q),
+                 lambda: w.transit_states_to_with_contact(q[:4], q[4:], 0.01),
+                 lambda: w.is_valid_transitions(q[:4], q[4:], 0.01),
+                 lambda: w.intersecting_segments_batch(q, cap=16)):
+        with pytest.raises(_lib.OsrError):
+            call()
+
+
+def test_product_package_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "puzzletunneldiscovery_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cc", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert "oracle" not in src.replace("test oracle", "").replace("the oracle", "") or f == "workloads.py" \
+                    or "import oracle" not in src and "from oracle" not in src
+                assert "from oracle" not in src and "import oracle" not in src and "libosr_oracle" not in src

@@ -1,0 +1,310 @@
+"""GPU parity tests: libosrgpu.so (through its C ABI, via the pyosr-compatible front end) against the CPU
+oracle on identical seeded inputs, against the committed golden fixtures, and -- at BASELINE.json's full
+sizes -- through size-independent properties.  Integer / boolean / index results must be bit-exact; fp64
+outputs (states, taus, Moeller segments) are produced with the same operation order as the oracle and are
+compared bit-exactly as well unless a tolerance is written in the test."""
+import numpy as np
+import pytest
+
+from conftest import golden, make_world
+from puzzletunneldiscovery_b200 import workloads as W
+
+pytestmark = pytest.mark.gpu
+
+VD_TOUCH = 0.0125 / 8  # src/GP/condor_touch_configuration.py:35,92
+TOL = 1e-14            # absolute tolerance on fp64 outputs that pass through libm (see _close)
+
+
+def _close(a, b):
+    return np.abs(np.asarray(a, float) - np.asarray(b, float)).max() <= TOL
+
+
+# ---- config 1: batched is_valid_state --------------------------------------------------------------
+def test_validity_golden_fixtures(uw_org, uw_wt2):
+    g = golden("validity_org_seed0.npz")
+    assert np.array_equal(uw_org.is_valid_states(g["q"]), g["valid"].astype(bool))
+    assert np.array_equal(uw_org.is_disentangled_states(g["q"]), g["disentangled"].astype(bool))
+    g2 = golden("validity_wt2_seed5.npz")
+    assert np.array_equal(uw_wt2.is_valid_states(g2["q"]), g2["valid"].astype(bool))
+    assert abs(uw_org.scene_scale - float(g["scene_scale"])) == 0.0
+    assert abs(uw_wt2.scene_scale - float(g2["scene_scale"])) == 0.0
+
+
+@pytest.mark.parametrize("which,n,seed", [("org", 1 << 16, 11), ("wt2", 1 << 15, 12)])
+def test_validity_matches_oracle_bit_exact(which, n, seed, uw_org, uw_wt2, ow_org, ow_wt2):
+    uw, ow = (uw_org, ow_org) if which == "org" else (uw_wt2, ow_wt2)
+    q = W.random_states(n, seed)
+    uw.counters(reset=True)
+    v = uw.is_valid_states(q)
+    c = uw.counters()
+    vo = ow.is_valid_states(q).astype(bool)
+    assert np.array_equal(v, vo)  # ambiguity set is empty: the fp64 re-test decides every uncertain pair
+    assert c["poses"] == n and c["bv_tests"] > 0 and c["spills"] == 0
+
+
+def test_validity_near_contact_states_match_oracle(uw_org, ow_org):
+    """States inside the contact band: the two end states of blocked touch rays (last free / first hit)
+    and their midpoints -- where the fp32 filter is most often undecided."""
+    g = golden("segments_org_seed1.npz")
+    blocked = g["is_free"] == 0
+    lf, fh = g["last_free"][blocked], g["first_hit"][blocked]
+    mid = 0.5 * (lf + fh)
+    q = np.concatenate([lf, fh, mid])
+    assert np.array_equal(uw_org.is_valid_states(q), ow_org.is_valid_states(q).astype(bool))
+    assert uw_org.is_valid_states(lf).all() and not uw_org.is_valid_states(fh).any()
+
+
+def test_validity_edge_cases(uw_org, ow_org):
+    assert uw_org.is_valid_states(np.zeros((0, 7))).shape == (0,)           # empty batch
+    q = W.random_states(97, 3)                                               # ragged: 3 tiles + 1 state
+    vo = ow_org.is_valid_states(q).astype(bool)
+    assert np.array_equal(uw_org.is_valid_states(q), vo)
+    for n in (1, 31, 32, 33):
+        assert np.array_equal(uw_org.is_valid_states(q[:n]), vo[:n])
+    assert uw_org.is_valid_state(q[0]) == bool(vo[0])
+    # float32 input widens like pybind11 does (uw_random.py:15-17)
+    assert np.array_equal(uw_org.is_valid_states(q.astype(np.float32)), vo)
+    # the quaternion is NOT renormalised (osr_state.cc:16-25): a scaled quaternion scales the robot
+    q2 = q.copy()
+    q2[:, 3:] *= 1.25
+    assert np.array_equal(uw_org.is_valid_states(q2), ow_org.is_valid_states(q2).astype(bool))
+    # far away: everything separated at the root
+    far = q.copy()
+    far[:, 0] += 10.0
+    assert uw_org.is_valid_states(far).all()
+    with pytest.raises(RuntimeError):
+        uw_org.is_valid_states(np.zeros((4, 6)))
+
+
+def test_validity_with_perturbation(oracle_mod):
+    from puzzletunneldiscovery_b200 import pyosr
+    pert = np.array([0.01, -0.02, 0.015, 0.9980, 0.0366, -0.0366, 0.0329])
+    uw = make_world(pyosr.UnitWorld, "org", perturb=pert)
+    ow = make_world(oracle_mod.OracleWorld, "org", perturb=pert)
+    q = W.random_states(8192, 21)
+    assert np.array_equal(uw.is_valid_states(q), ow.is_valid_states(q).astype(bool))
+
+
+def test_validity_full_size_properties(uw_org, ow_org):
+    """BASELINE config 1 at full size (2^20 states): determinism, batch-split invariance, quaternion sign
+    invariance (R(q) == R(-q) bit for bit), and the oracle on a 32 Ki random subset."""
+    n = 1 << 20
+    q = W.random_states(n, 0)
+    v = uw_org.is_valid_states(q)
+    assert np.array_equal(v, uw_org.is_valid_states(q))
+    parts = np.concatenate([uw_org.is_valid_states(q[a:b]) for a, b in ((0, 333333), (333333, 700001), (700001, n))])
+    assert np.array_equal(v, parts)
+    qn = q.copy()
+    qn[:, 3:] = -qn[:, 3:]
+    assert np.array_equal(v, uw_org.is_valid_states(qn))
+    idx = np.random.RandomState(5).choice(n, 1 << 15, replace=False)
+    assert np.array_equal(v[idx], ow_org.is_valid_states(q[idx]).astype(bool))
+    g = golden("validity_org_seed0.npz")
+    assert np.array_equal(v[:4096], g["valid"].astype(bool))
+    assert 0.76 < v.mean() < 0.775
+
+
+def test_bvh_boxes_contain_their_triangles(uw_org):
+    """Conservativeness of the engine's own fp32 OBB tree (labels only equal FCL's if no box prunes a
+    triangle it should contain): every leaf box contains its triangle, every parent box its children's
+    triangles, evaluated in fp64 on the fp32 node data."""
+    for which in (0, 1):
+        V, F = uw_org._geometry(which)
+        nodes = uw_org.bvh_nodes(which).astype(np.float64)
+        link = uw_org.bvh_nodes(which)[:, 15].copy().view(np.int32)
+        tris = [None] * len(nodes)
+        for i in range(len(nodes) - 1, -1, -1):  # breadth-first numbering: children after parents
+            if link[i] < 0:
+                tris[i] = [-(int(link[i]) + 1)]
+            else:
+                tris[i] = tris[link[i]] + tris[link[i] + 1]
+        assert sorted(tris[0]) == list(range(len(F)))
+        for i in range(len(nodes)):
+            A = nodes[i, :12].reshape(3, 4)
+            P = V[F[tris[i]].reshape(-1)] - A[:, 3]
+            proj = np.abs(P @ A[:, :3].T)
+            assert (proj <= nodes[i, 12:15] + 1e-12).all()
+
+
+# ---- config 2: segment walk / first contact ------------------------------------------------------------
+def test_segments_golden_fixture(uw_org):
+    g = golden("segments_org_seed1.npz")
+    lf, fh, isf, ft, tt, st = uw_org.transit_states_to_with_contact(g["fr"], g["to"], float(g["vd"]), with_steps=True)
+    assert np.array_equal(isf, g["is_free"].astype(bool))
+    assert np.array_equal(st, g["steps"])                      # first contact at the very same step
+    # fp64 outputs: same formulas and operation order; the device libm (atan2/acos/sin) may differ from
+    # glibc in the last bit, hence 1e-14 absolute instead of bit equality
+    assert _close(tt, g["touch_tau"]) and _close(ft, g["free_tau"])
+    assert _close(lf, g["last_free"]) and _close(fh, g["first_hit"])
+    vt = uw_org.is_valid_transitions(g["fr"], g["to"], 0.01)
+    assert np.array_equal(vt, g["valid_transition_0p01"].astype(bool))
+
+
+def test_segments_match_oracle_wt2_tunnel(uw_wt2, ow_wt2):
+    """D3: from-states = TUNNEL_V on G-wt2 (the reference's alpha-1.2 touch sampling set-up)."""
+    import os
+    tv = np.load(os.path.join(W.assets_dir(), "alpha-1.2.org.tunnel.npz"))["TUNNEL_V"]
+    free = np.concatenate([tv[:, :3] * uw_wt2.scene_scale, tv[:, 3:]], axis=1)
+    assert uw_wt2.is_valid_states(free).all()
+    fr, to = W.touch_rays(free, 768, seed=31)
+    lf, fh, isf, ft, tt, st = uw_wt2.transit_states_to_with_contact(fr, to, VD_TOUCH, with_steps=True)
+    olf, ofh, oisf, oft, ott, oc = ow_wt2.transit_states_to_with_contact(fr, to, VD_TOUCH, counters=True)
+    assert np.array_equal(isf, oisf.astype(bool)) and np.array_equal(st, oc[:, 0])
+    assert _close(tt, ott) and _close(ft, oft) and _close(lf, olf) and _close(fh, ofh)
+    # runtime invariant unit_world.cc:325-326
+    assert uw_wt2.is_valid_states(lf).all()
+    assert not uw_wt2.is_valid_states(fh[~isf]).any()
+
+
+def test_segments_per_segment_verify_delta_and_degenerate(uw_org, ow_org):
+    g = golden("segments_org_seed1.npz")
+    fr, to = g["fr"][:128], g["to"][:128]
+    vd = np.linspace(0.001, 0.05, 128)
+    vd[5] = 100.0  # vd >= dist -> (from, to, false, 0, 1)   unit_world.cc:445-447
+    r = uw_org.transit_states_to_with_contact(fr, to, vd, with_steps=True)
+    o = ow_org.transit_states_to_with_contact(fr, to, vd, counters=True)
+    assert np.array_equal(r[2], o[2].astype(bool)) and np.array_equal(r[5], o[5][:, 0])
+    assert _close(r[3], o[3]) and _close(r[4], o[4])
+    assert np.array_equal(r[0][5], fr[5]) and np.array_equal(r[1][5], to[5]) and not r[2][5]
+    assert r[3][5] == 0.0 and r[4][5] == 1.0 and r[5][5] == 0
+    # from == to: dist = 0 <= vd
+    assert not uw_org.is_valid_transition(fr[0], fr[0], 0.01)
+    # single-state wrappers return the reference's tuple shapes (taus narrowed to C float)
+    t = uw_org.transit_state_to_with_contact(fr[0], to[0], VD_TOUCH)
+    assert len(t) == 5 and t[0].shape == (7,) and isinstance(t[2], bool)
+    t3 = uw_org.transit_state_to(fr[0], to[0], VD_TOUCH)
+    assert np.array_equal(t3[0], t[0]) and t3[1] == t[2] and t3[2] == t[3]
+    assert uw_org.transit_states_to_with_contact(np.zeros((0, 7)), np.zeros((0, 7)), 0.1)[2].shape == (0,)
+
+
+def test_segments_fine_verify_delta_long_walks(uw_org, ow_org):
+    """recommended_cres-sized steps (D3 ii): tens of thousands of steps per segment."""
+    g = golden("segments_org_seed1.npz")
+    fr, to = g["fr"][:24], g["to"][:24]
+    vd = uw_org.scene_scale * 0.001
+    r = uw_org.transit_states_to_with_contact(fr, to, vd, with_steps=True)
+    o = ow_org.transit_states_to_with_contact(fr, to, vd, counters=True)
+    assert np.array_equal(r[5], o[5][:, 0]) and np.array_equal(r[2], o[2].astype(bool))
+    assert _close(r[4], o[4]) and r[5].max() > 10000
+
+
+# ---- config 3: edge validation -----------------------------------------------------------------------
+def test_edge_validation_knn_edges_match_oracle(uw_org, ow_org):
+    ms = W.random_states(4096, 2)
+    fr, to = W.knn_edges(ms, k=4, window=1024)
+    vd = uw_org.scene_scale * 0.001 * 8
+    v = uw_org.is_valid_transitions(fr, to, vd)
+    assert np.array_equal(v, ow_org.is_valid_transitions(fr, to, vd).astype(bool))
+    assert 0 < v.mean() < 1
+
+
+def test_visibility_matrices(uw_org, ow_org):
+    q0 = W.random_states(24, 41)
+    q1 = W.random_states(17, 42)
+    vd = 0.02
+    m2 = uw_org.calculate_visibility_matrix2(q0, True, q1, True, vd)
+    assert m2.dtype == np.int8 and m2.shape == (24, 17)
+    fr = np.repeat(q0, 17, axis=0)
+    to = np.tile(q1, (24, 1))
+    assert np.array_equal(m2.reshape(-1), ow_org.is_valid_transitions(fr, to, vd).astype(np.int8))
+    vp = uw_org.calculate_visibility_pair(q0, True, q1, True, vd)
+    assert vp.shape == (24, 1)
+    idx = np.arange(24)
+    assert np.array_equal(vp[:, 0], ow_org.is_valid_transitions(q0[idx % 24], q1[idx % 17], vd).astype(np.int8))
+    ms = uw_org.calculate_visibility_matrix(q0, True, vd)
+    assert np.array_equal(ms, ms.T) and (np.diag(ms) == 0).all()
+    # non-unit rows go through translate_to_unit_state first (unit_world.cc:810-817)
+    big = q0.copy()
+    big[:, :3] /= uw_org.scene_scale
+    assert np.array_equal(uw_org.calculate_visibility_matrix2(big, False, q1, True, vd), m2)
+
+
+# ---- config 5: contacts -> surface ----------------------------------------------------------------------
+def _canon(off, faces, seg, cop):
+    rows = []
+    for i in range(len(off) - 1):
+        for k in range(off[i], off[i + 1]):
+            rows.append((i, int(faces[k][0]), int(faces[k][1])) + tuple(seg[k]) + (int(cop[k]),))
+    return np.array(sorted(rows))
+
+
+def test_contacts_golden_fixture(uw_org):
+    g = golden("contacts_org.npz")
+    r = uw_org.intersecting_segments_batch(g["q"], cap=1 << 16, with_bary=True)
+    assert r["total"] == int(g["total"]) and np.array_equal(r["offsets"], g["offsets"])
+    a = _canon(r["offsets"], r["faces"], r["seg"], r["coplanar"])
+    b = _canon(g["offsets"], g["faces"], g["segs"], g["coplanar"])
+    assert a.shape == b.shape
+    assert np.array_equal(a[:, :3], b[:, :3])          # (state, env triangle, robot triangle) rows
+    assert np.array_equal(a[:, 9], b[:, 9])            # coplanar flags
+    assert np.array_equal(a[:, 3:9], b[:, 3:9])        # Moeller segment end points, same operation order
+    # surface points: barycentric coordinates of each segment's mid point sum to 1 on both triangles
+    seg = r["seg"]
+    nz = np.abs(seg).sum(axis=1) > 0
+    bary = r["bary"][nz]
+    assert np.allclose(bary[:, :3].sum(axis=1), 1.0, atol=1e-9) and np.allclose(bary[:, 3:].sum(axis=1), 1.0, atol=1e-9)
+    # the mid point reconstructed from the env-triangle barycentrics lies on the segment
+    V0, F0 = uw_org._geometry(0)
+    mid = 0.5 * (seg[nz, :3] + seg[nz, 3:])
+    tri = V0[F0[r["faces"][nz, 0]]]
+    rec = (bary[:, :3, None] * tri).sum(axis=1)
+    assert np.abs(rec - mid).max() < 1e-6
+    p0, p1, mag, faces = uw_org.intersecting_segments(g["q"][0])
+    assert p0.shape[1] == 3 and mag.shape == (len(p0), 1) and faces.shape == (len(p0), 2)
+
+
+def test_contacts_capacity_overflow_flag(uw_org):
+    g = golden("contacts_org.npz")
+    full = uw_org.intersecting_segments_batch(g["q"], cap=1 << 16)
+    cap = int(full["offsets"][5]) + 1
+    r = uw_org.intersecting_segments_batch(g["q"], cap=cap)
+    assert r["total"] == full["total"] and r["offsets"][-1] == cap
+    assert r["overflow"][5] and r["overflow"][6:].all() and not r["overflow"][:5].any()
+    free = golden("validity_org_seed0.npz")
+    fq = free["q"][free["valid"] == 1][:64]
+    e = uw_org.intersecting_segments_batch(fq, cap=16)
+    assert e["total"] == 0 and (e["offsets"] == 0).all()
+
+
+# ---- other hot-path entry points -------------------------------------------------------------------------
+def test_enum_free_configurations_labels_are_validity(uw_org):
+    V0, F0 = uw_org._geometry(0)
+    V1, F1 = uw_org._geometry(1)
+    rs = np.random.RandomState(9)
+
+    def sample(V, F, n):
+        f = F[rs.randint(0, len(F), n)]
+        a, b, c = V[f[:, 0]], V[f[:, 1]], V[f[:, 2]]
+        nrm = np.cross(b - a, c - a)
+        return (a + b + c) / 3.0, nrm / np.linalg.norm(nrm, axis=1, keepdims=True)
+
+    rp, rn = sample(V1, F1, 16)
+    ep, en = sample(V0, F0, 16)
+    pts = np.stack([rp, rn, ep, en], axis=1)
+    q, valid, counts = uw_org.enum_free_configurations(pts, 1e-4, 64)
+    assert q.shape == (16, 64, 7) and np.array_equal(counts, valid.sum(axis=1))
+    assert np.array_equal(valid.reshape(-1), uw_org.is_valid_states(q.reshape(-1, 7)))
+    # contact construction: R * (rob point + margin * n) lands on env point + margin * n
+    from puzzletunneldiscovery_b200.pyosr import _rotate_points
+    for b in range(4):
+        for i in (0, 17):
+            p = _rotate_points(q[b, i], (rp[b] + 1e-4 * rn[b])[None])[0]
+            assert np.abs(p - (ep[b] + 1e-4 * en[b])).max() < 1e-9
+    _, vm, cm = uw_org.enum_free_configurations(pts, 1e-4, 64, only_median=True)
+    assert (cm <= counts).all() and (vm & ~valid).sum() == 0
+
+
+def test_state_frame_maps_round_trip(uw_wt2):
+    q = W.random_states(64, 77)
+    back = uw_wt2._map(uw_wt2._L.osr_translate_from_unit, uw_wt2.translate_to_unit_states(q))
+    assert np.abs(back - q).max() < 1e-12
+    o = uw_wt2.translate_unit_to_ompl(q)
+    assert np.abs(uw_wt2.translate_ompl_to_unit(o) - q).max() < 1e-12
+    assert np.allclose(o[:, 6], q[:, 3]) and np.allclose(o[:, 3:6], q[:, 4:7])  # w-last <-> w-first
+
+
+def test_no_cpu_fallback_counters_show_gpu_work(uw_org):
+    uw_org.counters(reset=True)
+    uw_org.is_valid_states(W.random_states(1024, 1))
+    c = uw_org.counters()
+    assert c["kernel_launches"] == 1 and c["poses"] == 1024 and c["bv_tests"] >= 1024
