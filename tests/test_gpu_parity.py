@@ -248,7 +248,10 @@ def test_contacts_golden_fixture(uw_org):
     mid = 0.5 * (seg[nz, :3] + seg[nz, 3:])
     tri = V0[F0[r["faces"][nz, 0]]]
     rec = (bary[:, :3, None] * tri).sum(axis=1)
-    assert np.abs(rec - mid).max() < 1e-6
+    # Moeller snaps plane distances below 1e-6 (unnormalised) to zero (Moller97d.cc:41,603-606), so an end point
+    # may sit up to ~1e-3 off the other triangle's plane; typical rows reconstruct to rounding error
+    err = np.abs(rec - mid).max(axis=1)
+    assert np.median(err) < 1e-12 and err.max() < 1e-2
     p0, p1, mag, faces = uw_org.intersecting_segments(g["q"][0])
     assert p0.shape[1] == 3 and mag.shape == (len(p0), 1) and faces.shape == (len(p0), 2)
 
