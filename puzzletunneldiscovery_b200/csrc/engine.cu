@@ -15,6 +15,7 @@
 #include "../../include/osrgpu.h"
 #include "geometry.h"
 #include "kernels.cuh"
+#include "kernels_dfs.cuh"
 
 namespace {
 
@@ -52,6 +53,11 @@ struct Slot {  // one GPU
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   float4* env_nodes = nullptr; double* env_tris = nullptr;
   float4* rob_nodes = nullptr; double* rob_tris = nullptr;
+  uint4* env_qnodes = nullptr; uint4* rob_qnodes = nullptr;  // 32-byte QNodes (qnode.h)
+  int dfs_variant = -1;        // 0: <u32,32>  1: <u32,64>  2: <u64,64>  -1: trees too deep, tile kernel only
+  int dfs_env_smem = 0, dfs_rob_smem = 0;
+  size_t dfs_smem_bytes = 0;
+  int num_sms = 0;
   osr::DevCounters* counters = nullptr;
   unsigned long long* work = nullptr;   // [0] tile queue, [1] contact record count
   unsigned long long* spill = nullptr;
@@ -77,6 +83,7 @@ struct osr_world {
   osr::UnitModel env, rob;
   std::vector<Slot> slots;
   osr_counters host_counters = {0, 0, 0, 0, 0, 0};
+  bool force_tile_kernel = false;  // OSR_VALID_KERNEL=tile: first-generation kernel, kept for A/B measurements
 
   osr::KParams params(const Slot& s) const {
     osr::KParams P;
@@ -102,6 +109,7 @@ void free_slot(Slot& s) {
   cudaSetDevice(s.dev);
   if (s.stream) cudaStreamSynchronize(s.stream);
   cudaFree(s.env_nodes); cudaFree(s.env_tris); cudaFree(s.rob_nodes); cudaFree(s.rob_tris);
+  cudaFree(s.env_qnodes); cudaFree(s.rob_qnodes);
   cudaFree(s.counters); cudaFree(s.work); cudaFree(s.spill); cudaFree(s.err);
   s.in0.release(); s.in1.release(); s.vd.release();
   for (auto& b : s.out) b.release();
@@ -127,6 +135,8 @@ int init_slot(osr_world* w, Slot& s, int dev) {
   CU(up((void**)&s.env_tris, w->env.tris.data(), w->env.tris.size() * 8));
   CU(up((void**)&s.rob_nodes, w->rob.bvh.nodes.data(), w->rob.bvh.nodes.size() * 4));
   CU(up((void**)&s.rob_tris, w->rob.tris.data(), w->rob.tris.size() * 8));
+  CU(up((void**)&s.env_qnodes, w->env.bvh.qnodes.data(), w->env.bvh.qnodes.size() * 4));
+  CU(up((void**)&s.rob_qnodes, w->rob.bvh.qnodes.data(), w->rob.bvh.qnodes.size() * 4));
   CU(cudaMalloc((void**)&s.counters, sizeof(osr::DevCounters)));
   CU(cudaMemset(s.counters, 0, sizeof(osr::DevCounters)));
   CU(cudaMalloc((void**)&s.work, 2 * sizeof(unsigned long long)));
@@ -144,6 +154,34 @@ int init_slot(osr_world* w, Slot& s, int dev) {
   s.grid_valid = nsm * std::max(1, bpsm);
   s.grid_transit = nsm * std::max(1, b2);
   s.grid_contacts = nsm * std::max(1, b3);
+  s.num_sms = nsm;
+  {  // lane-owned DFS kernel: pick the task width / stack depth variant and the shared-memory node budget
+    int need = w->env.bvh.depth + w->rob.bvh.depth + 2;
+    bool small = w->env.bvh.num_nodes < 32768 && w->rob.bvh.num_nodes < 32768;
+    size_t wm = 0;
+    if (small && need <= 32) { s.dfs_variant = 0; wm = sizeof(osr::DfsWarpMem<uint32_t, 32>); }
+    else if (small && need <= 64) { s.dfs_variant = 1; wm = sizeof(osr::DfsWarpMem<uint32_t, 64>); }
+    else if (need <= 64) { s.dfs_variant = 2; wm = sizeof(osr::DfsWarpMem<unsigned long long, 64>); }
+    else s.dfs_variant = -1;
+    if (s.dfs_variant >= 0) {
+      int max_smem = 0;
+      CU(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+      size_t fixed = wm * osr::DFS_WARPS;
+      long long budget = ((long long)max_smem - (long long)fixed) / 32;  // nodes
+      if (budget < 2) s.dfs_variant = -1;
+      else {
+        long long ne = w->env.bvh.num_nodes, nr = w->rob.bvh.num_nodes;
+        long long se = std::min(ne, budget / 2), sr = std::min(nr, budget / 2);
+        se = std::min(ne, budget - sr);
+        sr = std::min(nr, budget - se);
+        s.dfs_env_smem = (int)se; s.dfs_rob_smem = (int)sr;
+        s.dfs_smem_bytes = (size_t)(se + sr) * 32 + fixed;
+        CU(cudaFuncSetAttribute(osr::k_valid_dfs<uint32_t, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+        CU(cudaFuncSetAttribute(osr::k_valid_dfs<uint32_t, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+        CU(cudaFuncSetAttribute(osr::k_valid_dfs<unsigned long long, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+      }
+    }
+  }
   s.spill_cap = 8192;
   size_t warps = (size_t)std::max(s.grid_valid, std::max(s.grid_transit, s.grid_contacts)) * osr::WARPS_PER_BLOCK;
   CU(cudaMalloc((void**)&s.spill, warps * s.spill_cap * sizeof(unsigned long long)));
@@ -187,6 +225,8 @@ const char* osr_last_error(void) { return g_err.c_str(); }
 int osr_create(osr_world** out) {
   if (!out) return fail(OSR_EINVAL, "null out");
   *out = new osr_world();
+  const char* k = getenv("OSR_VALID_KERNEL");
+  (*out)->force_tile_kernel = k && strcmp(k, "tile") == 0;
   return OSR_OK;
 }
 
@@ -333,8 +373,38 @@ int osr_get_counters(osr_world* w, osr_counters* out, int reset) {
 }
 
 // ---- launch helpers ---------------------------------------------------------------------------
+static osr::DfsParams dfs_params(const osr_world* w, const Slot& s) {
+  osr::DfsParams P;
+  P.env_q = s.env_qnodes; P.rob_q = s.rob_qnodes;
+  P.env_tris = s.env_tris; P.rob_tris = s.rob_tris;
+  P.env_nodes = w->env.bvh.num_nodes; P.rob_nodes = w->rob.bvh.num_nodes;
+  P.env_smem_nodes = s.dfs_env_smem; P.rob_smem_nodes = s.dfs_rob_smem;
+  osr::state_to_rigid(w->perturb, P.env_tf);
+  for (int k = 0; k < 4; k++) P.env_quat[k] = w->perturb[3 + k];
+  P.r_rob = w->rob.bvh.max_radius;
+  P.counters = s.counters;
+  P.work_counter = s.work;
+  P.error_flag = s.err;
+  return P;
+}
+
 static int launch_valid(osr_world* w, Slot& s, const double* d_q, int64_t n, uint8_t* d_out) {
   CU(cudaMemsetAsync(s.work, 0, 2 * sizeof(unsigned long long), s.stream));
+  if (s.dfs_variant >= 0 && !w->force_tile_kernel) {
+    if (n > 0x7fffffffLL) return fail(OSR_EINVAL, "more than 2^31-1 states in one launch");
+    osr::DfsParams D = dfs_params(w, s);
+    CU(cudaEventRecord(s.ev0, s.stream));
+    if (s.dfs_variant == 0)
+      osr::k_valid_dfs<uint32_t, 32><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, s.stream>>>(D, d_q, (long long)n, d_out);
+    else if (s.dfs_variant == 1)
+      osr::k_valid_dfs<uint32_t, 64><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, s.stream>>>(D, d_q, (long long)n, d_out);
+    else
+      osr::k_valid_dfs<unsigned long long, 64><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, s.stream>>>(D, d_q, (long long)n, d_out);
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(s.ev1, s.stream));
+    w->host_counters.kernel_launches++;
+    return OSR_OK;
+  }
   osr::KParams P = w->params(s);
   CU(cudaEventRecord(s.ev0, s.stream));
   osr::k_is_valid<<<s.grid_valid, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK, s.stream>>>(P, d_q, (long long)n, d_out);

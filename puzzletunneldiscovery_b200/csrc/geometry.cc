@@ -1,6 +1,7 @@
 // geometry.cc -- OBJ reader, unit-world transform and the GPU-oriented OBB-BVH builder.
 // See geometry.h for the reference functions this replaces.
 #include "geometry.h"
+#include "qnode.h"
 
 #include <algorithm>
 #include <cmath>
@@ -134,6 +135,8 @@ struct BuildNode {
   int left = -1;   // child build-node ids, or -1
   int right = -1;
   int tri = -1;
+  uint16_t qh[4];  // QNode: orientation quaternion (fp16 bits) ...
+  uint16_t eh[3];  // ... and extents fitted to the exact rotation of that quaternion, rounded up to fp16
 };
 
 struct Builder {
@@ -229,6 +232,49 @@ struct Builder {
     }
   }
 
+  // QNode: quaternion of the (near-orthonormal) frame above, rounded to fp16.  The box of the node is DEFINED
+  // by the exact rotation of the normalised rounded quaternion; extents are re-fitted to it in fp64 about the
+  // same fp32 centre.  The relative slack covers the kernel's first-order renormalisation and fp32 products
+  // (frame error < 2e-6 rad); the absolute one the same error times the lever arm to the centre.
+  void fit_q(int first, int n, BuildNode& nd) {
+    double m[3][3];  // columns = axes
+    for (int k = 0; k < 3; k++) { m[0][k] = nd.axis[3 * k]; m[1][k] = nd.axis[3 * k + 1]; m[2][k] = nd.axis[3 * k + 2]; }
+    double q[4];
+    double tr = m[0][0] + m[1][1] + m[2][2];
+    if (tr > 0) {
+      double s = std::sqrt(tr + 1.0) * 2;
+      q[0] = 0.25 * s; q[1] = (m[2][1] - m[1][2]) / s; q[2] = (m[0][2] - m[2][0]) / s; q[3] = (m[1][0] - m[0][1]) / s;
+    } else if (m[0][0] > m[1][1] && m[0][0] > m[2][2]) {
+      double s = std::sqrt(1.0 + m[0][0] - m[1][1] - m[2][2]) * 2;
+      q[0] = (m[2][1] - m[1][2]) / s; q[1] = 0.25 * s; q[2] = (m[0][1] + m[1][0]) / s; q[3] = (m[0][2] + m[2][0]) / s;
+    } else if (m[1][1] > m[2][2]) {
+      double s = std::sqrt(1.0 + m[1][1] - m[0][0] - m[2][2]) * 2;
+      q[0] = (m[0][2] - m[2][0]) / s; q[1] = (m[0][1] + m[1][0]) / s; q[2] = 0.25 * s; q[3] = (m[1][2] + m[2][1]) / s;
+    } else {
+      double s = std::sqrt(1.0 + m[2][2] - m[0][0] - m[1][1]) * 2;
+      q[0] = (m[1][0] - m[0][1]) / s; q[1] = (m[0][2] + m[2][0]) / s; q[2] = (m[1][2] + m[2][1]) / s; q[3] = 0.25 * s;
+    }
+    double qn = std::sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+    double qd[4];
+    for (int k = 0; k < 4; k++) {
+      nd.qh[k] = float_to_half_bits_rn((float)(q[k] / qn));
+      qd[k] = (double)half_bits_to_float(nd.qh[k]);
+    }
+    qn = std::sqrt(qd[0] * qd[0] + qd[1] * qd[1] + qd[2] * qd[2] + qd[3] * qd[3]);
+    double R[9];
+    quat_to_rot(qd[0] / qn, qd[1] / qn, qd[2] / qn, qd[3] / qn, R);  // columns = exact box axes
+    Vec3 cf = {(double)nd.centre[0], (double)nd.centre[1], (double)nd.centre[2]};
+    double ext[3] = {0, 0, 0}, lever = 0;
+    for (int i = 0; i < n; i++)
+      for (int k = 0; k < 3; k++) {
+        Vec3 d = vert(prims[first + i], k) - cf;
+        lever = std::max(lever, std::sqrt(dot(d, d)));
+        for (int a = 0; a < 3; a++)
+          ext[a] = std::max(ext[a], std::fabs(R[a] * d.x + R[3 + a] * d.y + R[6 + a] * d.z));
+      }
+    for (int a = 0; a < 3; a++) nd.eh[a] = float_to_half_bits_up(ext[a] * (1.0 + 1e-5) + 4e-6 * lever + 1e-9);
+  }
+
   int build(int first, int n, int lvl) {
     depth = std::max(depth, lvl);
     int id = (int)nodes.size();
@@ -236,6 +282,7 @@ struct Builder {
     {
       BuildNode nd;
       fit(first, n, nd);
+      fit_q(first, n, nd);
       nodes[id] = nd;
     }
     if (n == 1) { nodes[id].tri = prims[first]; return id; }
@@ -295,6 +342,7 @@ void build_gpu_bvh(UnitModel& m) {
   m.bvh.num_nodes = N;
   m.bvh.depth = b.depth;
   m.bvh.nodes.assign((size_t)16 * N, 0.f);
+  m.bvh.qnodes.assign((size_t)8 * N, 0u);
   for (int i = 0; i < N; i++) {
     const BuildNode& nd = b.nodes[order[i]];
     float* o = &m.bvh.nodes[(size_t)16 * i];
@@ -305,7 +353,18 @@ void build_gpu_bvh(UnitModel& m) {
     o[12] = nd.ext[0]; o[13] = nd.ext[1]; o[14] = nd.ext[2];
     int32_t link = nd.left >= 0 ? newid[nd.left] : -(nd.tri + 1);
     std::memcpy(&o[15], &link, 4);
+    QNode qn;
+    for (int k = 0; k < 3; k++) qn.c[k] = nd.centre[k];
+    qn.link = link;
+    qn.q01 = (uint32_t)nd.qh[0] | ((uint32_t)nd.qh[1] << 16);
+    qn.q23 = (uint32_t)nd.qh[2] | ((uint32_t)nd.qh[3] << 16);
+    qn.e01 = (uint32_t)nd.eh[0] | ((uint32_t)nd.eh[1] << 16);
+    qn.e2x = (uint32_t)nd.eh[2];
+    std::memcpy(&m.bvh.qnodes[(size_t)8 * i], &qn, 32);
   }
+  double r2 = 0;
+  for (size_t i = 0; i < m.V.size(); i += 3) r2 = std::max(r2, m.V[i] * m.V[i] + m.V[i + 1] * m.V[i + 1] + m.V[i + 2] * m.V[i + 2]);
+  m.bvh.max_radius = std::nextafterf((float)std::sqrt(r2), std::numeric_limits<float>::infinity());
 }
 
 }  // namespace osr

@@ -31,9 +31,11 @@ bool load_obj(const std::string& path, TriMesh& out, std::string& err);
 //   [12..14] half extents (already inflated to cover fp32 rounding of axes/centre)
 //   [15] int32 bit pattern: >=0 index of left child (right = left+1); <0 leaf, triangle = -(v+1)
 struct GpuBvh {
-  std::vector<float> nodes;
+  std::vector<float> nodes;       // 16 floats per node (layout above)
+  std::vector<uint32_t> qnodes;   // 8 words per node: the 32-byte QNode of qnode.h (same numbering)
   int num_nodes = 0;
   int depth = 0;
+  float max_radius = 0.f;         // largest |vertex| of the model (bounds |p| in the pose slack, qnode.h)
 };
 
 struct UnitModel {

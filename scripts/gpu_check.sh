@@ -21,6 +21,6 @@ if [[ $what == all || $what == ncu ]]; then
   echo "ncu launches rc=$?"
   CMD2="python bench.py --steps 3 --warmup 1 --no-cpu-baseline --no-touch"
   timeout 600 $CMD2 > gpurun_out/ncu_plain2.log 2>&1 &&
-  timeout 1500 ncu --set full --clock-control none --import-source on -k regex:k_is_valid -s 2 -c 2 -f -o gpurun_out/prof_valid $CMD2 > gpurun_out/ncu_full.log 2>&1
+  timeout 1500 ncu --set full --clock-control none --import-source on -k regex:k_valid_dfs -s 2 -c 1 -f -o gpurun_out/prof_valid $CMD2 > gpurun_out/ncu_full.log 2>&1
   echo "ncu full rc=$?"; tail -3 gpurun_out/ncu_full.log
 fi

@@ -64,10 +64,16 @@ def test_validity_edge_cases(uw_org, ow_org):
     assert uw_org.is_valid_state(q[0]) == bool(vo[0])
     # float32 input widens like pybind11 does (uw_random.py:15-17)
     assert np.array_equal(uw_org.is_valid_states(q.astype(np.float32)), vo)
-    # the quaternion is NOT renormalised (osr_state.cc:16-25): a scaled quaternion scales the robot
+    # the quaternion is NOT renormalised (osr_state.cc:16-25): a non-unit quaternion gives a non-rigid map
+    # 1 + |q|^2 (Rot - 1).  FCL's OBB pruning is not conservative for such maps (its result then depends on
+    # its tree), so outside the unit-quaternion domain the engine is held to the tree-independent truth:
+    # the all-pairs SAT-17 of the oracle's brute-force mode.
     q2 = q.copy()
     q2[:, 3:] *= 1.25
-    assert np.array_equal(uw_org.is_valid_states(q2), ow_org.is_valid_states(q2).astype(bool))
+    assert np.array_equal(uw_org.is_valid_states(q2), ow_org.is_valid_states(q2, mode="brute").astype(bool))
+    q3 = q.copy()
+    q3[:, 3:] *= 1.0 + 1e-4
+    assert np.array_equal(uw_org.is_valid_states(q3), ow_org.is_valid_states(q3, mode="brute").astype(bool))
     # far away: everything separated at the root
     far = q.copy()
     far[:, 0] += 10.0
@@ -300,10 +306,13 @@ def test_enum_free_configurations_labels_are_validity(uw_org):
 def test_state_frame_maps_round_trip(uw_wt2):
     q = W.random_states(64, 77)
     back = uw_wt2._map(uw_wt2._L.osr_translate_from_unit, uw_wt2.translate_to_unit_states(q))
-    assert np.abs(back - q).max() < 1e-12
+    # both maps renormalise the quaternion (unit_world.cc:713-738); the seeded states are float32-rounded
+    qn = q.copy()
+    qn[:, 3:] /= np.linalg.norm(qn[:, 3:], axis=1, keepdims=True)
+    assert np.abs(back - qn).max() < 1e-12
     o = uw_wt2.translate_unit_to_ompl(q)
-    assert np.abs(uw_wt2.translate_ompl_to_unit(o) - q).max() < 1e-12
-    assert np.allclose(o[:, 6], q[:, 3]) and np.allclose(o[:, 3:6], q[:, 4:7])  # w-last <-> w-first
+    assert np.abs(uw_wt2.translate_ompl_to_unit(o) - qn).max() < 1e-12
+    assert np.allclose(o[:, 6], qn[:, 3]) and np.allclose(o[:, 3:6], qn[:, 4:7])  # w-last <-> w-first
 
 
 def test_no_cpu_fallback_counters_show_gpu_work(uw_org):
