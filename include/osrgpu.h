@@ -79,6 +79,10 @@ typedef struct osr_counters {
   uint64_t poses;         /* validity checks (configs or segment steps)      */
   uint64_t spills;        /* stack spill events to global memory             */
   uint64_t kernel_launches;
+  /* lane occupancy of the depth-first traversal kernels: per warp iteration 32 lanes can each run one box
+   * test; lanes_active did, lanes_waiting held a pose whose queued triangle tests were pending,
+   * lanes_idle had no pose (input exhausted).  warp efficiency = lanes_active / (32 * warp_iters). */
+  uint64_t warp_iters, lanes_active, lanes_waiting, lanes_idle;
 } osr_counters;
 int osr_get_counters(osr_world* w, osr_counters* out, int reset);
 

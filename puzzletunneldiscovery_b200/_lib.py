@@ -17,7 +17,9 @@ c_fp = C.POINTER(C.c_float)
 
 class Counters(C.Structure):
     _fields_ = [("bv_tests", C.c_uint64), ("leaf_tests", C.c_uint64), ("fp64_rechecks", C.c_uint64),
-                ("poses", C.c_uint64), ("spills", C.c_uint64), ("kernel_launches", C.c_uint64)]
+                ("poses", C.c_uint64), ("spills", C.c_uint64), ("kernel_launches", C.c_uint64),
+                ("warp_iters", C.c_uint64), ("lanes_active", C.c_uint64), ("lanes_waiting", C.c_uint64),
+                ("lanes_idle", C.c_uint64)]
 
 
 # name -> (restype, argtypes): exactly the symbols include/osrgpu.h declares

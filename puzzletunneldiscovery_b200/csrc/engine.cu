@@ -82,7 +82,7 @@ struct osr_world {
   double perturb[7] = {0, 0, 0, 1, 0, 0, 0};
   osr::UnitModel env, rob;
   std::vector<Slot> slots;
-  osr_counters host_counters = {0, 0, 0, 0, 0, 0};
+  osr_counters host_counters = {};
   bool force_tile_kernel = false;  // OSR_VALID_KERNEL=tile: first-generation kernel, kept for A/B measurements
 
   osr::KParams params(const Slot& s) const {
@@ -365,10 +365,12 @@ int osr_get_counters(osr_world* w, osr_counters* out, int reset) {
     CU(cudaStreamSynchronize(s.stream));
     tot.bv_tests += c.bv; tot.leaf_tests += c.leaf; tot.fp64_rechecks += c.fp64; tot.poses += c.poses;
     tot.spills += c.spills;
+    tot.warp_iters += c.warp_iters; tot.lanes_active += c.lanes_active; tot.lanes_waiting += c.lanes_waiting;
+    tot.lanes_idle += c.lanes_idle;
     if (reset) CU(cudaMemsetAsync(s.counters, 0, sizeof(c), s.stream));
   }
   if (out) *out = tot;
-  if (reset) w->host_counters = osr_counters{0, 0, 0, 0, 0, 0};
+  if (reset) w->host_counters = osr_counters{};
   return OSR_OK;
 }
 

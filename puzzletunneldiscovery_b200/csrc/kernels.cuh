@@ -33,6 +33,8 @@ struct DevModel {
 
 struct DevCounters {
   unsigned long long bv, leaf, fp64, poses, spills;
+  // lane occupancy of the depth-first kernels, in lane-iterations (one iteration = one box test slot)
+  unsigned long long warp_iters, lanes_active, lanes_waiting, lanes_idle;
 };
 
 struct KParams {

@@ -67,6 +67,8 @@ struct __align__(16) DfsWarpMem {
   unsigned long long req[REQ_CAP];
   float pend[17][32];  // BoxPose of prepared poses: q[4] R[9] t[3] eta
   int pend_idx[32];
+  int parts[32];       // work sharing at the end of the input: lanes still working on the pose of home lane i
+  int hitf[32];        // ... and whether one of them has found an intersecting pair
 };
 
 // leaf-queue entry: owner lane:5 | epoch:11 | env triangle:24 | robot triangle:24
@@ -172,20 +174,31 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
   unsigned epoch = 0;
   bool has_pose = false, hit = false, pl = false, pr = false, lf_root = false;
   E cur = 0;
-  int sp = 0;
+  int sp = 0, sb = 0;   // the lane's stack is stack[sb .. sp-1][lane]
+  int home = lane;      // lane that pulled the pose this lane works on (differs after a steal)
   // warp state (uniform)
   int pend_n = 0, nleaf = 0, nre = 0, since_flush = 0, re_age = 0;
-  bool exhausted = false, draining_leaf = false, draining_re = false;
+  bool exhausted = false, draining_leaf = false, draining_re = false, steal_mode = false;
   unsigned n_bv = 0, n_leaf = 0, n_fp64 = 0;
   unsigned long long nposes = 0;
+  unsigned st_iters = 0, st_active = 0, st_wait = 0, st_idle = 0;
 
   // One drain step = one chunk of up to 32 queued entries.  Both drains appear exactly once in the code
   // (the kernel is instruction-cache sensitive: 12 warps at different places of a long loop).
   while (true) {
-    // (1) completed poses
-    if (has_pose && (hit || (cur == 0 && !pl && !pr && !lf_root))) {
-      src.result(tag, hit);
-      has_pose = false; hit = false; pl = false; pr = false; cur = 0; sp = 0;
+    // (1) completed poses.  Once lanes share poses (steal_mode) a pose is finished by the last of its parts.
+    {
+      bool done = has_pose && (hit || (cur == 0 && !pl && !pr && !lf_root));
+      if (!steal_mode) {
+        if (done) src.result(tag, hit);
+      } else {
+        if (has_pose && M.hitf[home] != 0) { hit = true; done = true; }
+        if (done && hit) M.hitf[home] = 1;
+        __syncwarp();
+        if (done && atomicSub(&M.parts[home], 1) == 1) src.result(tag, M.hitf[home] != 0);
+        __syncwarp();
+      }
+      if (done) { has_pose = false; hit = false; pl = false; pr = false; cur = 0; sp = 0; sb = 0; }
     }
     // (2) hand new poses to idle lanes
     unsigned idle = __ballot_sync(FULL, !has_pose);
@@ -237,7 +250,7 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
           for (int j = 0; j < 3; j++) bp.t[j] = M.pend[13 + j][slot];
           bp.eta = M.pend[16][slot];
           tag = M.pend_idx[slot];
-          has_pose = true; hit = false; pl = false; pr = false; sp = 0;
+          has_pose = true; hit = false; pl = false; pr = false; sp = 0; sb = 0;
           epoch = (epoch + 1) & 0x7ffu;
           cur = root_t0;
           if (root_t1 != 0) { M.stack[0][lane] = root_t1; sp = 1; }
@@ -248,12 +261,61 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
         any_cur = __any_sync(FULL, cur != 0 || lf_root);
       }
     }
+    // (2b) input exhausted and lanes idle: idle lanes take the OLDEST stack entry (the largest pending subtree)
+    // of lanes that still have one.  Without this the kernel cannot end before its longest single pose does
+    // (up to ~2000 box tests in sequence on alpha-1.2), and every warp idles through its own longest pose.
+    if (exhausted && pend_n == 0) {
+      unsigned thieves = __ballot_sync(FULL, !has_pose);
+      if (thieves != 0) {
+        if (!steal_mode) {
+          M.parts[lane] = has_pose ? 1 : 0;
+          M.hitf[lane] = 0;
+          home = lane;
+          steal_mode = true;
+          __syncwarp();
+        }
+        unsigned victims = __ballot_sync(FULL, has_pose && sp > sb);
+        int ns = min(__popc(thieves), __popc(victims));
+        if (ns > 0) {
+          int r = __popc(thieves & ltmask);
+          bool thief = !has_pose && r < ns;
+          int v = thief ? (int)__fns(victims, 0, r + 1) : lane;
+          BoxPose vb;
+#pragma unroll
+          for (int k = 0; k < 4; k++) vb.q[k] = __shfl_sync(FULL, bp.q[k], v);
+#pragma unroll
+          for (int k = 0; k < 9; k++) vb.R[k] = __shfl_sync(FULL, bp.R[k], v);
+#pragma unroll
+          for (int k = 0; k < 3; k++) vb.t[k] = __shfl_sync(FULL, bp.t[k], v);
+          vb.eta = __shfl_sync(FULL, bp.eta, v);
+          int vtag = __shfl_sync(FULL, tag, v), vhome = __shfl_sync(FULL, home, v), vsb = __shfl_sync(FULL, sb, v);
+          bool robbed = has_pose && sp > sb && __popc(victims & ltmask) < ns;
+          E stolen = 0;
+          if (thief) stolen = M.stack[vsb][v];
+          __syncwarp();
+          if (robbed) sb++;
+          if (thief) {
+            bp = vb; tag = vtag; home = vhome;
+            cur = stolen; sp = 0; sb = 0;
+            has_pose = true; hit = false; pl = false; pr = false; lf_root = false;
+            epoch = (epoch + 1) & 0x7ffu;
+            atomicAdd(&M.parts[home], 1);
+          }
+          __syncwarp();
+          any_cur = true;
+        }
+      }
+    }
     // (3) one box test per lane: the pair on top of the lane's stack; an overlapping pair is replaced by its
     // two child pairs (not while a queue is being drained: the queues' capacity assumes at most one iteration
     // of new triangle pairs on top)
     if (any_cur && !draining_leaf && !draining_re) {
       bool lf0 = false;
       unsigned ta0 = 0, tb0 = 0;
+      st_iters++;
+      st_active += __popc(__ballot_sync(FULL, cur != 0));
+      st_wait += __popc(__ballot_sync(FULL, has_pose && cur == 0));
+      st_idle += __popc(__ballot_sync(FULL, !has_pose));
       if (cur != 0) {
         unsigned n1 = TC::env(cur), n2 = TC::rob(cur);
         QNode A = load_qnode(sm_env, P.env_q, P.env_smem_nodes, n1);
@@ -274,7 +336,7 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
             sp++;
           }
         }
-        if (nxt == 0 && sp > 0) { sp--; nxt = M.stack[sp][lane]; }
+        if (nxt == 0 && sp > sb) { sp--; nxt = M.stack[sp][lane]; }
         cur = nxt;
       }
       // queue the triangle pairs found
@@ -368,6 +430,10 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
     atomicAdd(&P.counters->leaf, (unsigned long long)lf);
     atomicAdd(&P.counters->fp64, (unsigned long long)f64);
     atomicAdd(&P.counters->poses, nposes);
+    atomicAdd(&P.counters->warp_iters, (unsigned long long)st_iters);
+    atomicAdd(&P.counters->lanes_active, (unsigned long long)st_active);
+    atomicAdd(&P.counters->lanes_waiting, (unsigned long long)st_wait);
+    atomicAdd(&P.counters->lanes_idle, (unsigned long long)st_idle);
   }
 }
 
