@@ -56,6 +56,7 @@ struct Slot {  // one GPU
   uint4* env_qnodes = nullptr; uint4* rob_qnodes = nullptr;  // 32-byte QNodes (qnode.h)
   int dfs_variant = -1;        // 0: <u32,32>  1: <u32,64>  2: <u64,64>  -1: trees too deep, tile kernel only
   int dfs_env_smem = 0, dfs_rob_smem = 0;
+  bool dfs_all_smem = false;   // both trees fit into shared memory entirely
   size_t dfs_smem_bytes = 0;
   int num_sms = 0;
   osr::DevCounters* counters = nullptr;
@@ -176,9 +177,11 @@ int init_slot(osr_world* w, Slot& s, int dev) {
         sr = std::min(nr, budget - se);
         s.dfs_env_smem = (int)se; s.dfs_rob_smem = (int)sr;
         s.dfs_smem_bytes = (size_t)(se + sr) * 32 + fixed;
-        CU(cudaFuncSetAttribute(osr::k_valid_dfs<uint32_t, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
-        CU(cudaFuncSetAttribute(osr::k_valid_dfs<uint32_t, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
-        CU(cudaFuncSetAttribute(osr::k_valid_dfs<unsigned long long, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+        s.dfs_all_smem = se == ne && sr == nr;
+        CU(cudaFuncSetAttribute(osr::k_valid_dfs<uint32_t, 32, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+        CU(cudaFuncSetAttribute(osr::k_valid_dfs<uint32_t, 32, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+        CU(cudaFuncSetAttribute(osr::k_valid_dfs<uint32_t, 64, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+        CU(cudaFuncSetAttribute(osr::k_valid_dfs<unsigned long long, 64, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
       }
     }
   }
@@ -396,12 +399,14 @@ static int launch_valid(osr_world* w, Slot& s, const double* d_q, int64_t n, uin
     if (n > 0x7fffffffLL) return fail(OSR_EINVAL, "more than 2^31-1 states in one launch");
     osr::DfsParams D = dfs_params(w, s);
     CU(cudaEventRecord(s.ev0, s.stream));
-    if (s.dfs_variant == 0)
-      osr::k_valid_dfs<uint32_t, 32><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, s.stream>>>(D, d_q, (long long)n, d_out);
+    if (s.dfs_variant == 0 && s.dfs_all_smem)
+      osr::k_valid_dfs<uint32_t, 32, true><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, s.stream>>>(D, d_q, (long long)n, d_out);
+    else if (s.dfs_variant == 0)
+      osr::k_valid_dfs<uint32_t, 32, false><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, s.stream>>>(D, d_q, (long long)n, d_out);
     else if (s.dfs_variant == 1)
-      osr::k_valid_dfs<uint32_t, 64><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, s.stream>>>(D, d_q, (long long)n, d_out);
+      osr::k_valid_dfs<uint32_t, 64, false><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, s.stream>>>(D, d_q, (long long)n, d_out);
     else
-      osr::k_valid_dfs<unsigned long long, 64><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, s.stream>>>(D, d_q, (long long)n, d_out);
+      osr::k_valid_dfs<unsigned long long, 64, false><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, s.stream>>>(D, d_q, (long long)n, d_out);
     CU(cudaGetLastError());
     CU(cudaEventRecord(s.ev1, s.stream));
     w->host_counters.kernel_launches++;

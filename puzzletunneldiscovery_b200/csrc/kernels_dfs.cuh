@@ -17,6 +17,7 @@
 #pragma once
 #include "kernels.cuh"
 #include "qnode.h"
+#include "sat17.h"
 
 namespace osr {
 
@@ -77,9 +78,10 @@ __device__ __forceinline__ unsigned long long leaf_entry(unsigned lane, unsigned
          ((unsigned long long)tb << 40);
 }
 
+template <bool ALL_SMEM>
 __device__ __forceinline__ QNode load_qnode(const uint4* sm, const uint4* gl, int nsm, unsigned idx) {
   uint4 a, b;
-  if ((int)idx < nsm) { a = sm[2 * idx]; b = sm[2 * idx + 1]; }
+  if (ALL_SMEM || (int)idx < nsm) { a = sm[2 * idx]; b = sm[2 * idx + 1]; }
   else { a = __ldg(gl + 2 * (size_t)idx); b = __ldg(gl + 2 * (size_t)idx + 1); }
   QNode n;
   n.c[0] = __uint_as_float(a.x); n.c[1] = __uint_as_float(a.y); n.c[2] = __uint_as_float(a.z);
@@ -91,7 +93,7 @@ __device__ __forceinline__ QNode load_qnode(const uint4* sm, const uint4* gl, in
 // Robot triangle into the environment frame with the reference's operation order
 // (intersect-inl.h:598-617: Q' = R*Q + T; then :738-743 everything minus P1); transform in registers.
 __device__ __forceinline__ void load_pair_exact_r(const double* __restrict__ Pt, const double* __restrict__ Qt,
-                                                  const Rigid& rel, Tri6<double>& t) {
+                                                  const Rigid& rel, TriPair<double>& t) {
   double p1[3] = {__ldg(Pt), __ldg(Pt + 1), __ldg(Pt + 2)};
 #pragma unroll
   for (int k = 0; k < 3; k++) {
@@ -132,11 +134,19 @@ struct ValiditySource {
 
 namespace osr {
 
+// lane flags
+constexpr unsigned F_HAS = 1u;  // the lane works on a pose
+constexpr unsigned F_HIT = 2u;  // an intersecting triangle pair of that pose is known
+constexpr unsigned F_PL = 4u;   // triangle pairs of the pose are waiting in the pair queue
+constexpr unsigned F_PR = 8u;   // ... in the exact-recheck queue
+
 // ---------------------------------------------------------------------------------------------------
 // K1 (second generation): batched validity, out[i] = 1 iff state i is collision free
 // (UnitWorld::isValid, /root/reference/lib/osr/unit_world.cc:215-247).  One persistent block per SM.
+// The loop body is kept small on purpose: its instruction working set (box test + stack step + the two
+// drains) has to stay inside the 32 KB L1.5 instruction cache shared by the 12 warps.
 // ---------------------------------------------------------------------------------------------------
-template <typename E, int DEPTH>
+template <typename E, int DEPTH, bool ALL_SMEM>
 __global__ void __launch_bounds__(DFS_THREADS, 1)
     k_valid_dfs(DfsParams P, const double* __restrict__ q, long long n, uint8_t* __restrict__ out) {
   typedef TaskCodec<E> TC;
@@ -152,27 +162,12 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
   const int lane = threadIdx.x & 31;
   const unsigned ltmask = (1u << lane) - 1u;
   ValiditySource src = {q, n, out};
-
-  // every pose that passes the root box test starts with the root pair already expanded (same descent rule
-  // as everywhere else: bvh_collision_traversal_node-inl.h:78-89)
-  E root_t0 = 0, root_t1 = 0;
-  bool root_leafpair = false;
-  {
-    QNode a = load_qnode(sm_env, P.env_q, P.env_smem_nodes, 0), b = load_qnode(sm_rob, P.rob_q, P.rob_smem_nodes, 0);
-    float ea0, ea1, ea2, eb0, eb1, eb2, sp_;
-    unpack_half2(a.e01, ea0, ea1); unpack_half2(a.e2x, ea2, sp_);
-    unpack_half2(b.e01, eb0, eb1); unpack_half2(b.e2x, eb2, sp_);
-    float sa = fmaf(ea0, ea0, fmaf(ea1, ea1, ea2 * ea2)), sb = fmaf(eb0, eb0, fmaf(eb1, eb1, eb2 * eb2));
-    if (a.link < 0 && b.link < 0) root_leafpair = true;
-    else if (b.link < 0 || (a.link >= 0 && sa > sb)) { root_t0 = TC::make((unsigned)a.link, 0); root_t1 = TC::make((unsigned)a.link + 1u, 0); }
-    else { root_t0 = TC::make(0, (unsigned)b.link); root_t1 = TC::make(0, (unsigned)b.link + 1u); }
-  }
+  const bool root_leafpair = ((int)sm_env[0].w < 0) && ((int)sm_rob[0].w < 0);  // two single-triangle meshes
 
   // lane state
   BoxPose bp;
   int tag = 0;
-  unsigned epoch = 0;
-  bool has_pose = false, hit = false, pl = false, pr = false, lf_root = false;
+  unsigned epoch = 0, fl = 0;
   E cur = 0;
   int sp = 0, sb = 0;   // the lane's stack is stack[sb .. sp-1][lane]
   int home = lane;      // lane that pulled the pose this lane works on (differs after a steal)
@@ -181,66 +176,60 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
   bool exhausted = false, draining_leaf = false, draining_re = false, steal_mode = false;
   unsigned n_bv = 0, n_leaf = 0, n_fp64 = 0;
   unsigned long long nposes = 0;
+#ifdef OSR_DFS_STATS
   unsigned st_iters = 0, st_active = 0, st_wait = 0, st_idle = 0;
+#endif
 
-  // One drain step = one chunk of up to 32 queued entries.  Both drains appear exactly once in the code
-  // (the kernel is instruction-cache sensitive: 12 warps at different places of a long loop).
   while (true) {
     // (1) completed poses.  Once lanes share poses (steal_mode) a pose is finished by the last of its parts.
     {
-      bool done = has_pose && (hit || (cur == 0 && !pl && !pr && !lf_root));
+      bool done = (fl & F_HAS) && ((fl & F_HIT) || (cur == 0 && !(fl & (F_PL | F_PR))));
       if (!steal_mode) {
-        if (done) src.result(tag, hit);
+        if (done) src.result(tag, (fl & F_HIT) != 0);
       } else {
-        if (has_pose && M.hitf[home] != 0) { hit = true; done = true; }
-        if (done && hit) M.hitf[home] = 1;
+        if ((fl & F_HAS) && M.hitf[home] != 0) { fl |= F_HIT; done = true; }
+        if (done && (fl & F_HIT)) M.hitf[home] = 1;
         __syncwarp();
         if (done && atomicSub(&M.parts[home], 1) == 1) src.result(tag, M.hitf[home] != 0);
         __syncwarp();
       }
-      if (done) { has_pose = false; hit = false; pl = false; pr = false; cur = 0; sp = 0; sb = 0; }
+      if (done) { fl = 0; cur = 0; sp = 0; sb = 0; }
     }
-    // (2) hand new poses to idle lanes
-    unsigned idle = __ballot_sync(FULL, !has_pose);
-    bool any_cur = __any_sync(FULL, cur != 0 || lf_root);
-    if (idle != 0 && (__popc(idle) >= REFILL_MIN || !any_cur)) {
-      while (pend_n == 0 && !exhausted) {  // prepare the next 32 states with the whole warp
+    // (2) idle lanes: new poses, or (input exhausted) a share of another lane's pose
+    unsigned idle = __ballot_sync(FULL, !(fl & F_HAS));
+    if (idle != 0) {
+      if (pend_n == 0 && !exhausted) {  // prepare the next 32 states with the whole warp
         unsigned long long base = 0;
         if (lane == 0) base = atomicAdd(P.work_counter, 32ull);
         base = __shfl_sync(FULL, base, 0);
-        if ((long long)base >= n) { exhausted = true; break; }
-        long long i = (long long)base + lane;
-        bool have = i < n, ov = false;
-        BoxPose np;
-        if (have) {
-          Rigid rel; double qd[4];
-          src.exact_pose(P, (int)i, rel, qd);
-          make_box_pose(rel, P.env_quat, qd, P.r_rob, np);
-          QNode a = load_qnode(sm_env, P.env_q, P.env_smem_nodes, 0), b = load_qnode(sm_rob, P.rob_q, P.rob_smem_nodes, 0);
-          float s1, s2;
-          ov = obb_overlap_q(a, b, np, s1, s2);
-          n_bv++;
-          if (!ov) src.result((int)i, false);
+        if ((long long)base >= n) exhausted = true;
+        else {
+          long long i = (long long)base + lane;
+          bool have = i < n;
+          unsigned hm = __ballot_sync(FULL, have);
+          if (have) {
+            Rigid rel; double qd[4];
+            src.exact_pose(P, (int)i, rel, qd);
+            BoxPose np;
+            make_box_pose(rel, P.env_quat, qd, P.r_rob, np);
+#pragma unroll
+            for (int k = 0; k < 4; k++) M.pend[k][lane] = np.q[k];
+#pragma unroll
+            for (int k = 0; k < 9; k++) M.pend[4 + k][lane] = np.R[k];
+#pragma unroll
+            for (int k = 0; k < 3; k++) M.pend[13 + k][lane] = np.t[k];
+            M.pend[16][lane] = np.eta;
+            M.pend_idx[lane] = (int)i;
+          }
+          pend_n = __popc(hm);
+          nposes += pend_n;
+          __syncwarp();
         }
-        nposes += __popc(__ballot_sync(FULL, have));
-        unsigned sm = __ballot_sync(FULL, ov);
-        if (ov) {
-          int slot = pend_n + __popc(sm & ltmask);
-#pragma unroll
-          for (int k = 0; k < 4; k++) M.pend[k][slot] = np.q[k];
-#pragma unroll
-          for (int k = 0; k < 9; k++) M.pend[4 + k][slot] = np.R[k];
-#pragma unroll
-          for (int k = 0; k < 3; k++) M.pend[13 + k][slot] = np.t[k];
-          M.pend[16][slot] = np.eta;
-          M.pend_idx[slot] = (int)i;
-        }
-        pend_n += __popc(sm);
-        __syncwarp();
       }
       if (pend_n > 0) {
         int k = __popc(idle & ltmask);
-        if (!has_pose && k < pend_n) {
+        bool pulled = !(fl & F_HAS) && k < pend_n;
+        if (pulled) {
           int slot = pend_n - 1 - k;
 #pragma unroll
           for (int j = 0; j < 4; j++) bp.q[j] = M.pend[j][slot];
@@ -250,35 +239,33 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
           for (int j = 0; j < 3; j++) bp.t[j] = M.pend[13 + j][slot];
           bp.eta = M.pend[16][slot];
           tag = M.pend_idx[slot];
-          has_pose = true; hit = false; pl = false; pr = false; sp = 0; sb = 0;
+          fl = F_HAS; sp = 0; sb = 0;
           epoch = (epoch + 1) & 0x7ffu;
-          cur = root_t0;
-          if (root_t1 != 0) { M.stack[0][lane] = root_t1; sp = 1; }
-          lf_root = root_leafpair;
+          cur = root_leafpair ? 0 : TC::make(0, 0);
         }
         pend_n -= min(pend_n, __popc(idle));
+        if (root_leafpair) {  // degenerate meshes: the only pair goes straight to the pair queue
+          unsigned m2 = __ballot_sync(FULL, pulled);
+          if (pulled) { M.leafq[nleaf + __popc(m2 & ltmask)] = leaf_entry(lane, epoch, 0, 0); fl |= F_PL; }
+          nleaf += __popc(m2);
+        }
         __syncwarp();
-        any_cur = __any_sync(FULL, cur != 0 || lf_root);
-      }
-    }
-    // (2b) input exhausted and lanes idle: idle lanes take the OLDEST stack entry (the largest pending subtree)
-    // of lanes that still have one.  Without this the kernel cannot end before its longest single pose does
-    // (up to ~2000 box tests in sequence on alpha-1.2), and every warp idles through its own longest pose.
-    if (exhausted && pend_n == 0) {
-      unsigned thieves = __ballot_sync(FULL, !has_pose);
-      if (thieves != 0) {
+      } else if (exhausted) {
+        // idle lanes take the OLDEST stack entry (the largest pending subtree) of lanes that still have one.
+        // Without this the kernel cannot end before its longest single pose does (up to ~2000 box tests in
+        // sequence on alpha-1.2) and every warp idles through its own longest pose.
         if (!steal_mode) {
-          M.parts[lane] = has_pose ? 1 : 0;
+          M.parts[lane] = (fl & F_HAS) ? 1 : 0;
           M.hitf[lane] = 0;
           home = lane;
           steal_mode = true;
           __syncwarp();
         }
-        unsigned victims = __ballot_sync(FULL, has_pose && sp > sb);
-        int ns = min(__popc(thieves), __popc(victims));
+        unsigned victims = __ballot_sync(FULL, (fl & F_HAS) && sp > sb);
+        int ns = min(__popc(idle), __popc(victims));
         if (ns > 0) {
-          int r = __popc(thieves & ltmask);
-          bool thief = !has_pose && r < ns;
+          int r = __popc(idle & ltmask);
+          bool thief = !(fl & F_HAS) && r < ns;
           int v = thief ? (int)__fns(victims, 0, r + 1) : lane;
           BoxPose vb;
 #pragma unroll
@@ -289,7 +276,7 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
           for (int k = 0; k < 3; k++) vb.t[k] = __shfl_sync(FULL, bp.t[k], v);
           vb.eta = __shfl_sync(FULL, bp.eta, v);
           int vtag = __shfl_sync(FULL, tag, v), vhome = __shfl_sync(FULL, home, v), vsb = __shfl_sync(FULL, sb, v);
-          bool robbed = has_pose && sp > sb && __popc(victims & ltmask) < ns;
+          bool robbed = (fl & F_HAS) && sp > sb && __popc(victims & ltmask) < ns;
           E stolen = 0;
           if (thief) stolen = M.stack[vsb][v];
           __syncwarp();
@@ -297,36 +284,38 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
           if (thief) {
             bp = vb; tag = vtag; home = vhome;
             cur = stolen; sp = 0; sb = 0;
-            has_pose = true; hit = false; pl = false; pr = false; lf_root = false;
+            fl = F_HAS;
             epoch = (epoch + 1) & 0x7ffu;
             atomicAdd(&M.parts[home], 1);
           }
           __syncwarp();
-          any_cur = true;
         }
       }
     }
     // (3) one box test per lane: the pair on top of the lane's stack; an overlapping pair is replaced by its
     // two child pairs (not while a queue is being drained: the queues' capacity assumes at most one iteration
     // of new triangle pairs on top)
+    const bool any_cur = __any_sync(FULL, cur != 0);
     if (any_cur && !draining_leaf && !draining_re) {
       bool lf0 = false;
       unsigned ta0 = 0, tb0 = 0;
+#ifdef OSR_DFS_STATS
       st_iters++;
       st_active += __popc(__ballot_sync(FULL, cur != 0));
-      st_wait += __popc(__ballot_sync(FULL, has_pose && cur == 0));
-      st_idle += __popc(__ballot_sync(FULL, !has_pose));
+      st_wait += __popc(__ballot_sync(FULL, (fl & F_HAS) && cur == 0));
+      st_idle += __popc(__ballot_sync(FULL, !(fl & F_HAS)));
+#endif
       if (cur != 0) {
         unsigned n1 = TC::env(cur), n2 = TC::rob(cur);
-        QNode A = load_qnode(sm_env, P.env_q, P.env_smem_nodes, n1);
-        QNode B = load_qnode(sm_rob, P.rob_q, P.rob_smem_nodes, n2);
-        float sa, sb;
-        bool ov = obb_overlap_q(A, B, bp, sa, sb);
+        QNode A = load_qnode<ALL_SMEM>(sm_env, P.env_q, P.env_smem_nodes, n1);
+        QNode B = load_qnode<ALL_SMEM>(sm_rob, P.rob_q, P.rob_smem_nodes, n2);
+        float sa, sb_;
+        bool ov = obb_overlap_q(A, B, bp, sa, sb_);
         n_bv++;
         E nxt = 0;
         if (ov) {
           if (A.link < 0 && B.link < 0) { lf0 = true; ta0 = (unsigned)(-(A.link + 1)); tb0 = (unsigned)(-(B.link + 1)); }
-          else if (B.link < 0 || (A.link >= 0 && sa > sb)) {
+          else if (B.link < 0 || (A.link >= 0 && sa > sb_)) {  // descend the environment node
             nxt = TC::make((unsigned)A.link, n2);
             M.stack[sp][lane] = TC::make((unsigned)A.link + 1u, n2);
             sp++;
@@ -339,41 +328,36 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
         if (nxt == 0 && sp > sb) { sp--; nxt = M.stack[sp][lane]; }
         cur = nxt;
       }
-      // queue the triangle pairs found
-      unsigned m0 = __ballot_sync(FULL, lf0), m2 = __ballot_sync(FULL, lf_root);
-      if (m0 | m2) {
-        if (lf0) M.leafq[nleaf + __popc(m0 & ltmask)] = leaf_entry(lane, epoch, ta0, tb0);
-        if (lf_root) M.leafq[nleaf + __popc(m0) + __popc(m2 & ltmask)] = leaf_entry(lane, epoch, 0, 0);
-        nleaf += __popc(m0) + __popc(m2);
-        pl = pl || lf0 || lf_root;
-        lf_root = false;
+      unsigned m0 = __ballot_sync(FULL, lf0);
+      if (m0) {  // queue the triangle pairs found
+        if (lf0) { M.leafq[nleaf + __popc(m0 & ltmask)] = leaf_entry(lane, epoch, ta0, tb0); fl |= F_PL; }
+        nleaf += __popc(m0);
         __syncwarp();
       }
       since_flush++;
       re_age = nre > 0 ? re_age + 1 : 0;
     }
-    // (4) drain policy: which queue (if any) gets one chunk processed now
+    // (4) drain policy: which queue (if any) gets one chunk of up to 32 entries processed now
     bool do_leaf = false, do_re = false;
     if (draining_leaf) do_leaf = true;
     else if (draining_re) do_re = true;
     else if (!any_cur) {
       if (nleaf > 0) do_leaf = true;
       else if (nre > 0) do_re = true;
-      else if (!__any_sync(FULL, has_pose) && exhausted && pend_n == 0) break;
+      else if (!__any_sync(FULL, (fl & F_HAS) != 0) && exhausted && pend_n == 0) break;
     } else {
       if (nleaf > 0) {
-        unsigned waiting = __ballot_sync(FULL, has_pose && cur == 0 && pl);
+        unsigned waiting = __ballot_sync(FULL, (fl & (F_HAS | F_PL)) == (F_HAS | F_PL) && cur == 0);
         do_leaf = nleaf >= LEAF_FLUSH || __popc(waiting) >= WAIT_FLUSH || since_flush > 1024;
       }
       if (!do_leaf && nre > 0) {
-        unsigned waiting = __ballot_sync(FULL, has_pose && cur == 0 && !pl && pr);
+        unsigned waiting = __ballot_sync(FULL, (fl & (F_HAS | F_PL | F_PR)) == (F_HAS | F_PR) && cur == 0);
         do_re = nre >= RE_FLUSH || __popc(waiting) >= WAIT_FLUSH || re_age > 1024;
       }
     }
     if (do_leaf && nre > REQ_CAP - 32) { do_leaf = false; do_re = true; draining_leaf = true; }  // make room first
     if (do_leaf | do_re) {
-      // one chunk of the chosen queue: the fp32-filtered SAT-17 for queued pairs, the exact fp64 SAT-17 for
-      // the pairs the filter could not decide
+      // the fp32-filtered SAT-17 for queued pairs / the exact fp64 SAT-17 for the pairs the filter left open
       unsigned long long* Q = do_leaf ? M.leafq : M.req;
       int& cntq = do_leaf ? nleaf : nre;
       int cnt = min(32, cntq);
@@ -381,44 +365,43 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
       unsigned long long e = act ? Q[cntq - 1 - lane] : 0ull;
       cntq -= cnt;
       unsigned owner = (unsigned)e & 31u, ep = (unsigned)(e >> 5) & 0x7ffu;
-      unsigned oep = __shfl_sync(FULL, epoch, owner);
-      int ohit = __shfl_sync(FULL, (int)hit, owner), ohas = __shfl_sync(FULL, (int)has_pose, owner);
+      unsigned oep = __shfl_sync(FULL, epoch, owner), ofl = __shfl_sync(FULL, fl, owner);
       int otag = __shfl_sync(FULL, tag, owner);
-      act = act && ohas && oep == ep && !ohit;
+      act = act && (ofl & (F_HAS | F_HIT)) == F_HAS && oep == ep;
       int r = 0;
       if (act) {
         Rigid rel; double qd[4];
         src.exact_pose(P, otag, rel, qd);
-        Tri6<double> td;
+        TriPair<double> td;
         load_pair_exact_r(P.env_tris + (size_t)9 * ((unsigned)(e >> 16) & 0xffffffu),
                           P.rob_tris + (size_t)9 * (unsigned)(e >> 40), rel, td);
         if (do_leaf) {
-          Tri6<float> tf;
+          TriPair<float> tf;
 #pragma unroll
           for (int k = 0; k < 3; k++) {
             tf.p2[k] = (float)td.p2[k]; tf.p3[k] = (float)td.p3[k];
             tf.q1[k] = (float)td.q1[k]; tf.q2[k] = (float)td.q2[k]; tf.q3[k] = (float)td.q3[k];
           }
-          r = sat17_filter(tf);
+          r = sat17_filter_c(tf);
           n_leaf++;
         } else {
-          r = sat17_exact(td) ? 1 : 0;
+          r = sat17_exact_c(td) ? 1 : 0;
           n_fp64++;
         }
       }
       unsigned hm = __reduce_or_sync(FULL, r == 1 ? (1u << owner) : 0u);
-      if (hm >> lane & 1u) hit = true;
+      if (hm >> lane & 1u) fl |= F_HIT;
       if (do_leaf) {
         unsigned um = __ballot_sync(FULL, r == 2);
         unsigned uo = __reduce_or_sync(FULL, r == 2 ? (1u << owner) : 0u);
         if (r == 2) M.req[nre + __popc(um & ltmask)] = e;
         nre += __popc(um);
-        if (uo >> lane & 1u) pr = true;
+        if (uo >> lane & 1u) fl |= F_PR;
         draining_leaf = nleaf > 0;
-        if (nleaf == 0) { pl = false; since_flush = 0; }
+        if (nleaf == 0) { fl &= ~F_PL; since_flush = 0; }
       } else {
         draining_re = nre > 0;
-        if (nre == 0) pr = false;
+        if (nre == 0) fl &= ~F_PR;
       }
       __syncwarp();
     }
@@ -430,10 +413,12 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
     atomicAdd(&P.counters->leaf, (unsigned long long)lf);
     atomicAdd(&P.counters->fp64, (unsigned long long)f64);
     atomicAdd(&P.counters->poses, nposes);
+#ifdef OSR_DFS_STATS
     atomicAdd(&P.counters->warp_iters, (unsigned long long)st_iters);
     atomicAdd(&P.counters->lanes_active, (unsigned long long)st_active);
     atomicAdd(&P.counters->lanes_waiting, (unsigned long long)st_wait);
     atomicAdd(&P.counters->lanes_idle, (unsigned long long)st_idle);
+#endif
   }
 }
 

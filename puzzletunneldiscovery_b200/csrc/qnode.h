@@ -182,13 +182,24 @@ OSR_HD bool obb_overlap_q(const QNode& A, const QNode& B, const BoxPose& P, floa
 // fp32 box pose from the fp64 relative transform `rel` (reference semantics) and the two quaternions it
 // was built from (environment perturbation, robot state; neither normalised).  r_rob = largest |vertex| of
 // the robot in its own frame.
+OSR_HD void quat_normalize_f(const double* q, float* o) {
+  float w = (float)q[0], x = (float)q[1], y = (float)q[2], z = (float)q[3];
+  float n2 = fmaf(w, w, fmaf(x, x, fmaf(y, y, z * z)));
+  if (!(n2 > 0.f)) { o[0] = 1.f; o[1] = 0.f; o[2] = 0.f; o[3] = 0.f; return; }
+#if defined(__CUDA_ARCH__)
+  float s = rsqrtf(n2);
+#else
+  float s = 1.0f / sqrtf(n2);
+#endif
+  o[0] = w * s; o[1] = x * s; o[2] = y * s; o[3] = z * s;
+}
 OSR_HD void make_box_pose(const Rigid& rel, const double* q_env, const double* q_rob, float r_rob, BoxPose& P) {
-  double e[4] = {q_env[0], q_env[1], q_env[2], q_env[3]}, r[4] = {q_rob[0], q_rob[1], q_rob[2], q_rob[3]};
-  quat_normalize(e[0], e[1], e[2], e[3]);
-  quat_normalize(r[0], r[1], r[2], r[3]);
-  double ec[4] = {e[0], -e[1], -e[2], -e[3]}, qr[4];
-  quat_mul(ec, r, qr);
-  for (int k = 0; k < 4; k++) P.q[k] = (float)qr[k];
+  // fp32 throughout: whatever rotation comes out, its distance to the reference's matrix goes into eta
+  float e[4], r[4];
+  quat_normalize_f(q_env, e);
+  quat_normalize_f(q_rob, r);
+  float ec[4] = {e[0], -e[1], -e[2], -e[3]};
+  quat_mul_f(ec, r, P.q);
   quat_to_rot_f(P.q, P.R);
   float dev = 0.f;
   for (int k = 0; k < 9; k++) {
@@ -196,7 +207,6 @@ OSR_HD void make_box_pose(const Rigid& rel, const double* q_env, const double* q
     dev = fmaf(d, d, dev);
   }
   for (int k = 0; k < 3; k++) P.t[k] = (float)rel.t[k];
-  // sqrt(dev) <= 1.0001 * (dev + 1) / 2 is avoided: use the exact sqrt, it is computed once per pose
   P.eta = 2e-5f * (1.0f + fabsf(P.t[0]) + fabsf(P.t[1]) + fabsf(P.t[2])) + 1.0001f * sqrtf(dev) * r_rob;
 }
 
