@@ -36,9 +36,9 @@ struct DfsParams {
   int* error_flag;
 };
 
-constexpr int DFS_WARPS = 12;
+constexpr int DFS_WARPS = 12;   // 3 per scheduler: 4 would need <= 128 registers (16 K registers per SM sub-partition)
 constexpr int DFS_THREADS = DFS_WARPS * 32;
-constexpr int LEAFQ_CAP = 128;   // >= LEAF_FLUSH - 1 + 96 (up to three pairs per lane and iteration)
+constexpr int LEAFQ_CAP = 64;    // >= LEAF_FLUSH - 1 + 32 (at most one new pair per lane and iteration)
 constexpr int REQ_CAP = 64;
 constexpr int LEAF_FLUSH = 16;   // drain the triangle-pair queue once it holds this many pairs
 constexpr int RE_FLUSH = 8;      // same for the queue of pairs awaiting the exact fp64 predicate
