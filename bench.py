@@ -339,7 +339,7 @@ def run_ours(args):
         "config": workload_config(n),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak if peak else None, "traffic": None, "peak_source": peak_src,
-                     "kernel": "k_is_valid", "kernel_ms": kernel_ms, "algorithmic_bytes_per_launch": alg,
+                     "kernel": "k_valid_dfs", "kernel_ms": kernel_ms, "algorithmic_bytes_per_launch": alg,
                      "note": "algorithmic bytes = 57 B/state + 128 B x oracle OBB tests + 72 B x oracle triangle "
                              "tests (SURVEY 8(d) D8); the working set (0.33 MB) lives in L1/L2, so the HBM "
                              "fraction is small by construction -- see DESIGN.md"},

@@ -7,7 +7,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libosrgpu.so")
 SOURCES = ["engine.cu", "geometry.cc"]
-DEPS = SOURCES + ["kernels.cuh", "se3.h", "geometry.h", os.path.join("..", "..", "include", "osrgpu.h")]
+DEPS = SOURCES + ["kernels.cuh", "kernels_dfs.cuh", "qnode.h", "sat17.h", "se3.h", "geometry.h",
+                  os.path.join("..", "..", "include", "osrgpu.h")]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

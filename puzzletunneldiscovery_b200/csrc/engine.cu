@@ -50,17 +50,18 @@ struct DevBuf {  // grow-only device buffer
 struct Slot {  // one GPU
   int dev = 0;
   cudaStream_t stream = nullptr;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaStream_t stream2 = nullptr;       // second lane of the host-call pipeline (H2D of chunk i+1 under kernel i)
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, evp = nullptr;
   float4* env_nodes = nullptr; double* env_tris = nullptr;
   float4* rob_nodes = nullptr; double* rob_tris = nullptr;
   uint4* env_qnodes = nullptr; uint4* rob_qnodes = nullptr;  // 32-byte QNodes (qnode.h)
-  int dfs_variant = -1;        // 0: <u32,32>  1: <u32,64>  2: <u64,64>  -1: trees too deep, tile kernel only
+  int dfs_variant = -1;        // 0: <u32,32>  1: <u32,64>  2: <u64,48>  -1: trees too deep, tile kernel only
   int dfs_env_smem = 0, dfs_rob_smem = 0;
   bool dfs_all_smem = false;   // both trees fit into shared memory entirely
   size_t dfs_smem_bytes = 0;
   int num_sms = 0;
   osr::DevCounters* counters = nullptr;
-  unsigned long long* work = nullptr;   // [0] tile queue, [1] contact record count
+  unsigned long long* work = nullptr;   // [0] tile queue, [1] contact record count, [2..] queues of pipelined chunks
   unsigned long long* spill = nullptr;
   int* err = nullptr;
   int grid_valid = 0, grid_transit = 0, grid_contacts = 0;
@@ -104,6 +105,7 @@ struct osr_world {
 
 namespace {
 
+constexpr int WORK_SLOTS = 4;  // [0],[1] see Slot::work; [2],[3] the two pipeline lanes of host calls
 constexpr size_t SMEM_PER_BLOCK = sizeof(osr::WarpShared) * osr::WARPS_PER_BLOCK;
 
 void free_slot(Slot& s) {
@@ -117,6 +119,8 @@ void free_slot(Slot& s) {
   s.recs.release(); s.rowrec.release(); s.seg.release(); s.faces.release(); s.cop.release(); s.bary.release();
   if (s.ev0) cudaEventDestroy(s.ev0);
   if (s.ev1) cudaEventDestroy(s.ev1);
+  if (s.evp) cudaEventDestroy(s.evp);
+  if (s.stream2) cudaStreamDestroy(s.stream2);
   if (s.stream) cudaStreamDestroy(s.stream);
   s = Slot();
 }
@@ -125,8 +129,10 @@ int init_slot(osr_world* w, Slot& s, int dev) {
   s.dev = dev;
   CU(cudaSetDevice(dev));
   CU(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+  CU(cudaStreamCreateWithFlags(&s.stream2, cudaStreamNonBlocking));
   CU(cudaEventCreate(&s.ev0));
   CU(cudaEventCreate(&s.ev1));
+  CU(cudaEventCreateWithFlags(&s.evp, cudaEventDisableTiming));
   auto up = [&](void** d, const void* h, size_t bytes) -> cudaError_t {
     cudaError_t e = cudaMalloc(d, bytes);
     if (e != cudaSuccess) return e;
@@ -140,7 +146,7 @@ int init_slot(osr_world* w, Slot& s, int dev) {
   CU(up((void**)&s.rob_qnodes, w->rob.bvh.qnodes.data(), w->rob.bvh.qnodes.size() * 4));
   CU(cudaMalloc((void**)&s.counters, sizeof(osr::DevCounters)));
   CU(cudaMemset(s.counters, 0, sizeof(osr::DevCounters)));
-  CU(cudaMalloc((void**)&s.work, 2 * sizeof(unsigned long long)));
+  CU(cudaMalloc((void**)&s.work, WORK_SLOTS * sizeof(unsigned long long)));
   CU(cudaMalloc((void**)&s.err, sizeof(int)));
   CU(cudaMemset(s.err, 0, sizeof(int)));
   // persistent grid: as many blocks as fit, on every SM
@@ -162,7 +168,7 @@ int init_slot(osr_world* w, Slot& s, int dev) {
     size_t wm = 0;
     if (small && need <= 32) { s.dfs_variant = 0; wm = sizeof(osr::DfsWarpMem<uint32_t, 32>); }
     else if (small && need <= 64) { s.dfs_variant = 1; wm = sizeof(osr::DfsWarpMem<uint32_t, 64>); }
-    else if (need <= 64) { s.dfs_variant = 2; wm = sizeof(osr::DfsWarpMem<unsigned long long, 64>); }
+    else if (need <= 48) { s.dfs_variant = 2; wm = sizeof(osr::DfsWarpMem<unsigned long long, 48>); }
     else s.dfs_variant = -1;
     if (s.dfs_variant >= 0) {
       int max_smem = 0;
@@ -181,7 +187,7 @@ int init_slot(osr_world* w, Slot& s, int dev) {
         CU(cudaFuncSetAttribute(osr::k_valid_dfs<uint32_t, 32, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
         CU(cudaFuncSetAttribute(osr::k_valid_dfs<uint32_t, 32, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
         CU(cudaFuncSetAttribute(osr::k_valid_dfs<uint32_t, 64, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
-        CU(cudaFuncSetAttribute(osr::k_valid_dfs<unsigned long long, 64, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+        CU(cudaFuncSetAttribute(osr::k_valid_dfs<unsigned long long, 48, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
       }
     }
   }
@@ -393,11 +399,29 @@ static osr::DfsParams dfs_params(const osr_world* w, const Slot& s) {
   return P;
 }
 
-static int launch_valid(osr_world* w, Slot& s, const double* d_q, int64_t n, uint8_t* d_out) {
-  CU(cudaMemsetAsync(s.work, 0, 2 * sizeof(unsigned long long), s.stream));
+// `lane` 0: the handle's main stream with events around the kernel; 1 / 2: the two pipeline lanes of a host
+// call (main stream / stream2), each with its own work queue word so that consecutive chunks may overlap
+static int launch_valid(osr_world* w, Slot& s, const double* d_q, int64_t n, uint8_t* d_out, int lane = 0) {
+  cudaStream_t st = lane == 2 ? s.stream2 : s.stream;
+  unsigned long long* work = lane == 0 ? s.work : s.work + 1 + lane;
+  CU(cudaMemsetAsync(work, 0, (lane == 0 ? 2 : 1) * sizeof(unsigned long long), st));
   if (s.dfs_variant >= 0 && !w->force_tile_kernel) {
     if (n > 0x7fffffffLL) return fail(OSR_EINVAL, "more than 2^31-1 states in one launch");
     osr::DfsParams D = dfs_params(w, s);
+    D.work_counter = work;
+    if (lane != 0) {
+      if (s.dfs_variant == 0 && s.dfs_all_smem)
+        osr::k_valid_dfs<uint32_t, 32, true><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, st>>>(D, d_q, (long long)n, d_out);
+      else if (s.dfs_variant == 0)
+        osr::k_valid_dfs<uint32_t, 32, false><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, st>>>(D, d_q, (long long)n, d_out);
+      else if (s.dfs_variant == 1)
+        osr::k_valid_dfs<uint32_t, 64, false><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, st>>>(D, d_q, (long long)n, d_out);
+      else
+        osr::k_valid_dfs<unsigned long long, 48, false><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, st>>>(D, d_q, (long long)n, d_out);
+      CU(cudaGetLastError());
+      w->host_counters.kernel_launches++;
+      return OSR_OK;
+    }
     CU(cudaEventRecord(s.ev0, s.stream));
     if (s.dfs_variant == 0 && s.dfs_all_smem)
       osr::k_valid_dfs<uint32_t, 32, true><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, s.stream>>>(D, d_q, (long long)n, d_out);
@@ -406,17 +430,18 @@ static int launch_valid(osr_world* w, Slot& s, const double* d_q, int64_t n, uin
     else if (s.dfs_variant == 1)
       osr::k_valid_dfs<uint32_t, 64, false><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, s.stream>>>(D, d_q, (long long)n, d_out);
     else
-      osr::k_valid_dfs<unsigned long long, 64, false><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, s.stream>>>(D, d_q, (long long)n, d_out);
+      osr::k_valid_dfs<unsigned long long, 48, false><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, s.stream>>>(D, d_q, (long long)n, d_out);
     CU(cudaGetLastError());
     CU(cudaEventRecord(s.ev1, s.stream));
     w->host_counters.kernel_launches++;
     return OSR_OK;
   }
   osr::KParams P = w->params(s);
-  CU(cudaEventRecord(s.ev0, s.stream));
-  osr::k_is_valid<<<s.grid_valid, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK, s.stream>>>(P, d_q, (long long)n, d_out);
+  P.work_counter = work;
+  if (lane == 0) CU(cudaEventRecord(s.ev0, s.stream));
+  osr::k_is_valid<<<s.grid_valid, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK, st>>>(P, d_q, (long long)n, d_out);
   CU(cudaGetLastError());
-  CU(cudaEventRecord(s.ev1, s.stream));
+  if (lane == 0) CU(cudaEventRecord(s.ev1, s.stream));
   w->host_counters.kernel_launches++;
   return OSR_OK;
 }
@@ -435,6 +460,19 @@ static int launch_transit(osr_world* w, Slot& s, const double* d_from, const dou
 }
 
 // ---- validity ---------------------------------------------------------------------------------
+// Host buffers in, host buffers out.  Every device gets a contiguous index range (shard()); inside a range the
+// states move in chunks through a two-lane pipeline (main stream / stream2), so that the PCIe upload of chunk
+// i+1 and the download of chunk i-1 run under the kernel of chunk i -- the call costs max(copy, kernel), not
+// their sum, when the caller's buffers are pinned.
+static int64_t host_chunk_states() {
+  static int64_t v = [] {
+    const char* e = getenv("OSR_HOST_CHUNK");
+    long long x = e ? atoll(e) : 0;
+    return (int64_t)(x > 0 ? x : (1 << 18));
+  }();
+  return v;
+}
+
 int osr_is_valid_states(osr_world* w, const double* q, int64_t n, uint8_t* out) {
   int rc = check_ready(w);
   if (rc) return rc;
@@ -442,6 +480,7 @@ int osr_is_valid_states(osr_world* w, const double* q, int64_t n, uint8_t* out) 
   if (n == 0) return OSR_OK;
   std::lock_guard<std::mutex> lk(w->mu);
   int parts = (int)w->slots.size();
+  const int64_t chunk = host_chunk_states();
   for (int i = 0; i < parts; i++) {
     Slot& s = w->slots[i];
     int64_t lo, hi;
@@ -450,10 +489,26 @@ int osr_is_valid_states(osr_world* w, const double* q, int64_t n, uint8_t* out) 
     CU(cudaSetDevice(s.dev));
     CU(s.in0.need((size_t)(hi - lo) * 56));
     CU(s.out[0].need((size_t)(hi - lo)));
-    CU(cudaMemcpyAsync(s.in0.p, q + 7 * lo, (size_t)(hi - lo) * 56, cudaMemcpyHostToDevice, s.stream));
-    rc = launch_valid(w, s, (const double*)s.in0.p, hi - lo, (uint8_t*)s.out[0].p);
-    if (rc) return rc;
-    CU(cudaMemcpyAsync(out + lo, s.out[0].p, (size_t)(hi - lo), cudaMemcpyDeviceToHost, s.stream));
+    int64_t nchunks = (hi - lo + chunk - 1) / chunk;
+    if (nchunks > 1) {  // stream2 joins after whatever the main stream still has queued
+      CU(cudaEventRecord(s.evp, s.stream));
+      CU(cudaStreamWaitEvent(s.stream2, s.evp, 0));
+    }
+    for (int64_t c = 0; c < nchunks; c++) {
+      int64_t c0 = c * chunk, m = std::min(chunk, hi - lo - c0);
+      int lane = nchunks == 1 ? 1 : 1 + (int)(c & 1);
+      cudaStream_t st = lane == 2 ? s.stream2 : s.stream;
+      double* d_in = (double*)s.in0.p + 7 * c0;
+      uint8_t* d_out = (uint8_t*)s.out[0].p + c0;
+      CU(cudaMemcpyAsync(d_in, q + 7 * (lo + c0), (size_t)m * 56, cudaMemcpyHostToDevice, st));
+      rc = launch_valid(w, s, d_in, m, d_out, lane);
+      if (rc) return rc;
+      CU(cudaMemcpyAsync(out + lo + c0, d_out, (size_t)m, cudaMemcpyDeviceToHost, st));
+    }
+    if (nchunks > 1) {
+      CU(cudaEventRecord(s.evp, s.stream2));
+      CU(cudaStreamWaitEvent(s.stream, s.evp, 0));
+    }
   }
   for (int i = 0; i < parts; i++) {
     Slot& s = w->slots[i];

@@ -1,0 +1,182 @@
+#!/usr/bin/env python
+"""Bounded runs of BASELINE.json configs 2-5 on one B200 (bench.py measures config 1, the headline).
+
+Every leg goes through the C ABI (`libosrgpu.so`) with HOST buffers, is timed by wall clock around the call
+(copies included), and a prefix of its output is compared with the CPU oracle (test infrastructure, used here
+only as the checker and as the timed CPU baseline).  One JSON line per leg; keep the output under profiles/.
+
+    python scripts/bench_configs.py [--legs touch,touch_fine,edges,hipoly,contacts] [--scale 1.0]
+"""
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from puzzletunneldiscovery_b200 import pyosr, workloads as W  # noqa: E402
+
+A = W.assets_dir()
+VD_TOUCH = 0.0125 / 8   # /root/reference/src/GP/condor_touch_configuration.py:35,92
+
+
+def world(cls, which="org", centre=None, meshes=None):
+    w = cls()
+    if meshes is not None:
+        w.set_meshes(*meshes)
+    else:
+        envf, robf = W.REF_ALPHA_FILES[which]
+        w.loadModelFromFile(os.path.join(A, envf))
+        w.loadRobotFromFile(os.path.join(A, robf))
+    if centre is not None:
+        w.enforceRobotCenter(centre)
+    w.scaleToUnit()
+    w.angleModel(0.0, 0.0)
+    return w
+
+
+def timed(fn, reps=1):
+    fn()  # warm-up (buffers, clocks)
+    t = time.perf_counter()
+    for _ in range(reps):
+        r = fn()
+    return r, (time.perf_counter() - t) / reps
+
+
+def leg_touch(O, scale, fine=False):
+    """Config 2: touch segments from the tunnel vertices on G-wt2, verify_delta 0.0125/8 (or the
+    pipeline's recommended_cres on a small subset when fine=True)."""
+    uw = world(pyosr.UnitWorld, "wt2", W.ROB_OMPL_CENTER)
+    ow = world(O.OracleWorld, "wt2", W.ROB_OMPL_CENTER)
+    tv = np.concatenate([np.load(os.path.join(A, "alpha-1.2.org.tunnel.npz"))["TUNNEL_V"],
+                         np.load(os.path.join(A, "alpha-1.2.org.tunnel-more.npz"))["TUNNEL_V"]])
+    fr0 = uw.translate_to_unit_states(tv)
+    vd = 1.5164e-5 if fine else VD_TOUCH
+    n = int((1 << 12 if fine else 1 << 18) * scale)
+    fr, to = W.touch_rays(fr0, n, seed=1)
+    (lf, fh, isf, ft, tt, st), dt = timed(lambda: uw.transit_states_to_with_contact(fr, to, vd, with_steps=True))
+    m = min(n, 64 if fine else 2048)
+    tc = time.perf_counter()
+    olf, ofh, oisf, oft, ott, ocnt = ow.transit_states_to_with_contact(fr[:m], to[:m], vd, counters=True)
+    dtc = time.perf_counter() - tc
+    # first contact at the very same step; taus to 1e-12 (device libm vs glibc may differ in the last bit of dist)
+    same = bool((isf[:m] == oisf.astype(bool)).all() and (st[:m] == ocnt[:, 0]).all() and
+                np.abs(tt[:m] - ott).max() < 1e-12 and np.abs(ft[:m] - oft).max() < 1e-12 and
+                np.abs(fh[:m] - ofh).max() < 1e-12)
+    return {"leg": "touch_fine" if fine else "touch", "geometry": "G-wt2", "segments": n, "verify_delta": vd,
+            "segments_per_s": n / dt, "validity_checks_per_s": float(st.sum()) / dt,
+            "mean_steps_per_segment": float(st.mean()), "free_fraction": float(isf.mean()), "seconds": dt,
+            "oracle_prefix": m, "same_first_contact_step_as_oracle_on_prefix": same,
+            "cpu_port": {"segments_per_s": m / dtc, "validity_checks_per_s": float(ocnt[:, 0].sum()) / dtc,
+                         "threads": O.lib().orc_max_threads()}}
+
+
+def leg_edges(O, scale):
+    """Config 3: is_valid_transition on windowed k-NN edges among valid milestones, G-org."""
+    uw = world(pyosr.UnitWorld)
+    ow = world(O.OracleWorld)
+    nm = int((1 << 16) * scale)
+    q = W.random_states(2 * nm, seed=2)
+    q = q[uw.is_valid_states(q)][:nm]
+    t = time.perf_counter()
+    fr, to = W.knn_edges(q, k=8, window=4096)
+    t_knn = time.perf_counter() - t
+    vd = 1.51641e-5
+    res, dt = timed(lambda: uw.is_valid_transitions(fr, to, vd))
+    m = 256
+    tc = time.perf_counter()
+    ores, ocnt = ow.is_valid_transitions(fr[:m], to[:m], vd, counters=True)
+    dtc = time.perf_counter() - tc
+    c = uw.counters(reset=True)
+    return {"leg": "edges", "geometry": "G-org", "milestones": len(q), "edges": len(fr), "verify_delta": vd,
+            "edges_per_s": len(fr) / dt, "seconds": dt, "valid_edge_fraction": float(res.mean()),
+            "host_knn_seconds": t_knn, "oracle_prefix": m,
+            "labels_equal_oracle_on_prefix": bool(np.array_equal(res[:m], ores.astype(bool))),
+            "cpu_port": {"edges_per_s": m / dtc, "validity_checks_per_s": float(ocnt[:, 0].sum()) / dtc,
+                         "threads": O.lib().orc_max_threads()}}
+
+
+def leg_hipoly(O, scale):
+    """Config 4: validity on the subdivided alpha puzzle (robot 100 800 x env 487 872 triangles)."""
+    eV, eF = W.load_obj_vf(os.path.join(A, "alpha_env-1.2.org.obj"))
+    rV, rF = W.load_obj_vf(os.path.join(A, "alpha-1.2.org.obj"))
+    EV, EF = W.subdivide(eV, eF, 22)
+    RV, RF = W.subdivide(rV, rF, 10)
+    t = time.perf_counter()
+    uw = world(pyosr.UnitWorld, meshes=(EV, EF, RV, RF))
+    t_build = time.perf_counter() - t
+    n = int((1 << 22) * scale)
+    q = W.random_states(n, seed=3)
+    v, dt = timed(lambda: uw.is_valid_states(q))
+    c = uw.counters(reset=True)
+    ow = world(O.OracleWorld, meshes=(EV, EF, RV, RF))
+    m = 1 << 16
+    tc = time.perf_counter()
+    vo = ow.is_valid_states(q[:m])
+    dtc = time.perf_counter() - tc
+    return {"leg": "hipoly", "geometry": "G-hi (env %d, robot %d triangles)" % (len(EF), len(RF)), "states": n,
+            "configs_per_s": n / dt, "seconds": dt, "valid_fraction": float(v.mean()),
+            "finalize_seconds (host BVH build + upload)": t_build, "oracle_prefix": m,
+            "labels_equal_oracle_on_prefix": bool(np.array_equal(v[:m], vo.astype(bool))),
+            "cpu_port": {"configs_per_s": m / dtc, "threads": O.lib().orc_max_threads()}}
+
+
+def leg_contacts(O, scale):
+    """Config 5: first-hit states of the touch search -> every touching triangle pair, its Moeller
+    segment, coplanar flag and the barycentric coordinates of the segment midpoint on both triangles."""
+    uw = world(pyosr.UnitWorld, "wt2", W.ROB_OMPL_CENTER)
+    ow = world(O.OracleWorld, "wt2", W.ROB_OMPL_CENTER)
+    tv = np.load(os.path.join(A, "alpha-1.2.org.tunnel-more.npz"))["TUNNEL_V"]
+    fr0 = uw.translate_to_unit_states(tv)
+    ns = int((1 << 16) * scale)
+    fr, to = W.touch_rays(fr0, ns, seed=4)
+    lf, fh, isf, ft, tt = uw.transit_states_to_with_contact(fr, to, VD_TOUCH)
+    hit = fh[~isf]
+    cap = 1 << 21
+    r, dt = timed(lambda: uw.intersecting_segments_batch(hit, cap=cap, with_bary=True))
+    m = min(len(hit), 1024)
+    tc = time.perf_counter()
+    off, segs, faces, cop, total = ow.intersecting_segments_batch(hit[:m])
+    dtc = time.perf_counter() - tc
+    k = int(off[-1])
+
+    def canon(off_, faces_, seg_, cop_):  # the oracle lists a state's rows in FCL's DFS order, the engine sorted
+        rows = [(i, int(faces_[j][0]), int(faces_[j][1])) + tuple(seg_[j]) + (int(cop_[j]),)
+                for i in range(m) for j in range(off_[i], off_[i + 1])]
+        return np.array(sorted(rows)).reshape(-1, 10)
+    a = canon(r["offsets"], r["faces"], r["seg"], r["coplanar"])
+    b = canon(off, faces, segs, cop)
+    same_faces = bool(a.shape == b.shape and np.array_equal(a[:, :3], b[:, :3]) and np.array_equal(a[:, 9], b[:, 9]))
+    err = float(np.abs(a[:, 3:9] - b[:, 3:9]).max()) if same_faces and k else None
+    return {"leg": "contacts", "geometry": "G-wt2", "states": int(len(hit)), "contact_rows": int(r["total"]),
+            "contacts_per_s": r["total"] / dt, "states_per_s": len(hit) / dt, "seconds": dt,
+            "rows_per_state": r["total"] / max(1, len(hit)), "oracle_prefix_states": m,
+            "rows_equal_oracle_on_prefix": same_faces, "max_abs_segment_error_on_prefix": err,
+            "cpu_port": {"states_per_s": m / dtc, "contacts_per_s": k / dtc, "threads": 1}}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--legs", default="touch,touch_fine,edges,hipoly,contacts")
+    ap.add_argument("--scale", type=float, default=1.0)
+    args = ap.parse_args()
+    from oracle import oracle as O
+    legs = {"touch": lambda: leg_touch(O, args.scale), "touch_fine": lambda: leg_touch(O, args.scale, fine=True),
+            "edges": lambda: leg_edges(O, args.scale), "hipoly": lambda: leg_hipoly(O, args.scale),
+            "contacts": lambda: leg_contacts(O, args.scale)}
+    for name in args.legs.split(","):
+        t = time.perf_counter()
+        try:
+            out = legs[name]()
+        except Exception as e:  # keep the other legs running; the failure is part of the record
+            out = {"leg": name, "error": repr(e)}
+        out["leg_wall_seconds"] = time.perf_counter() - t
+        print(json.dumps(out), flush=True)
+
+
+if __name__ == "__main__":
+    main()
