@@ -50,8 +50,12 @@ struct DevBuf {  // grow-only device buffer
 struct Slot {  // one GPU
   int dev = 0;
   cudaStream_t stream = nullptr;
-  cudaStream_t stream2 = nullptr;       // second lane of the host-call pipeline (H2D of chunk i+1 under kernel i)
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr, evp = nullptr;
+  cudaStream_t stream2 = nullptr;       // copy stream of host calls (second lane of the chunked pipeline)
+  cudaStream_t stream3 = nullptr;       // stream-fed launches: advances `ready` behind every uploaded chunk
+  cudaEvent_t feed_ev[64] = {};         // one per upload chunk (created on first use)
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, evp = nullptr, evq = nullptr;
+  long long* ready = nullptr;           // device word: states uploaded so far (stream-fed validity launches)
+  long long* h_ready = nullptr;         // pinned source values of the copies that advance it
   float4* env_nodes = nullptr; double* env_tris = nullptr;
   float4* rob_nodes = nullptr; double* rob_tris = nullptr;
   uint4* env_qnodes = nullptr; uint4* rob_qnodes = nullptr;  // 32-byte QNodes (qnode.h)
@@ -105,6 +109,32 @@ struct osr_world {
 
 namespace {
 
+constexpr int MAX_FEED_CHUNKS = 64;
+
+// cuStreamWriteValue64 (driver API stream memory operation) through the runtime's entry-point lookup, so the
+// library does not link libcuda: a stream-ordered 8-byte write costs ~1 us where a tiny cudaMemcpyAsync costs
+// a DMA round trip.  Null when the driver does not offer it (then the small copy is used).
+typedef int (*StreamWriteValue64)(cudaStream_t, unsigned long long, unsigned long long, unsigned int);
+StreamWriteValue64 stream_write_value64() {
+  static StreamWriteValue64 fn = [] {
+    void* p = nullptr;
+    if (getenv("OSR_NO_STREAM_MEMOPS")) return (StreamWriteValue64) nullptr;
+#if CUDART_VERSION >= 12050
+    cudaDriverEntryPointQueryResult st;
+    if (cudaGetDriverEntryPointByVersion("cuStreamWriteValue64", &p, 12000, cudaEnableDefault, &st) != cudaSuccess ||
+        st != cudaDriverEntryPointSuccess)
+      p = nullptr;
+#else
+    cudaDriverEntryPointQueryResult st;
+    if (cudaGetDriverEntryPoint("cuStreamWriteValue64", &p, cudaEnableDefault, &st) != cudaSuccess ||
+        st != cudaDriverEntryPointSuccess)
+      p = nullptr;
+#endif
+    cudaGetLastError();
+    return (StreamWriteValue64)p;
+  }();
+  return fn;
+}
 constexpr int WORK_SLOTS = 4;  // [0],[1] see Slot::work; [2],[3] the two pipeline lanes of host calls
 constexpr size_t SMEM_PER_BLOCK = sizeof(osr::WarpShared) * osr::WARPS_PER_BLOCK;
 
@@ -120,6 +150,11 @@ void free_slot(Slot& s) {
   if (s.ev0) cudaEventDestroy(s.ev0);
   if (s.ev1) cudaEventDestroy(s.ev1);
   if (s.evp) cudaEventDestroy(s.evp);
+  if (s.evq) cudaEventDestroy(s.evq);
+  cudaFree(s.ready);
+  if (s.h_ready) cudaFreeHost(s.h_ready);
+  for (auto& e : s.feed_ev) if (e) cudaEventDestroy(e);
+  if (s.stream3) cudaStreamDestroy(s.stream3);
   if (s.stream2) cudaStreamDestroy(s.stream2);
   if (s.stream) cudaStreamDestroy(s.stream);
   s = Slot();
@@ -130,9 +165,13 @@ int init_slot(osr_world* w, Slot& s, int dev) {
   CU(cudaSetDevice(dev));
   CU(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
   CU(cudaStreamCreateWithFlags(&s.stream2, cudaStreamNonBlocking));
+  CU(cudaStreamCreateWithFlags(&s.stream3, cudaStreamNonBlocking));
   CU(cudaEventCreate(&s.ev0));
   CU(cudaEventCreate(&s.ev1));
   CU(cudaEventCreateWithFlags(&s.evp, cudaEventDisableTiming));
+  CU(cudaEventCreateWithFlags(&s.evq, cudaEventDisableTiming));
+  CU(cudaMalloc((void**)&s.ready, sizeof(long long)));
+  CU(cudaHostAlloc((void**)&s.h_ready, MAX_FEED_CHUNKS * sizeof(long long), cudaHostAllocDefault));
   auto up = [&](void** d, const void* h, size_t bytes) -> cudaError_t {
     cudaError_t e = cudaMalloc(d, bytes);
     if (e != cudaSuccess) return e;
@@ -184,10 +223,14 @@ int init_slot(osr_world* w, Slot& s, int dev) {
         s.dfs_env_smem = (int)se; s.dfs_rob_smem = (int)sr;
         s.dfs_smem_bytes = (size_t)(se + sr) * 32 + fixed;
         s.dfs_all_smem = se == ne && sr == nr;
-        CU(cudaFuncSetAttribute(osr::k_valid_dfs<uint32_t, 32, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
-        CU(cudaFuncSetAttribute(osr::k_valid_dfs<uint32_t, 32, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
-        CU(cudaFuncSetAttribute(osr::k_valid_dfs<uint32_t, 64, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
-        CU(cudaFuncSetAttribute(osr::k_valid_dfs<unsigned long long, 48, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+#define OSR_DFS_ATTR(...)                                                                                         \
+  CU(cudaFuncSetAttribute(osr::k_valid_dfs<__VA_ARGS__, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem)); \
+  CU(cudaFuncSetAttribute(osr::k_valid_dfs<__VA_ARGS__, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem))
+        OSR_DFS_ATTR(uint32_t, 32, true);
+        OSR_DFS_ATTR(uint32_t, 32, false);
+        OSR_DFS_ATTR(uint32_t, 64, false);
+        OSR_DFS_ATTR(unsigned long long, 48, false);
+#undef OSR_DFS_ATTR
       }
     }
   }
@@ -216,10 +259,28 @@ int check_device_error(osr_world* w, Slot& s) {
   CU(cudaStreamSynchronize(s.stream));
   if (flag) {
     cudaMemsetAsync(s.err, 0, sizeof(int), s.stream);
+    if (flag == 2) return fail(OSR_ECUDA, "validity kernel timed out waiting for its input upload");
     return fail(OSR_EOVERFLOW, "device traversal stack spill area exhausted");
   }
   (void)w;
   return OSR_OK;
+}
+
+}  // namespace
+
+namespace {
+// the four tree-size variants of K1 x {resident input, stream-fed input}
+template <bool FEED>
+void launch_dfs_variant(const Slot& s, const osr::DfsParams& D, const double* d_q, long long n, uint8_t* d_out,
+                               cudaStream_t st) {
+  if (s.dfs_variant == 0 && s.dfs_all_smem)
+    osr::k_valid_dfs<uint32_t, 32, true, FEED><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, st>>>(D, d_q, n, d_out);
+  else if (s.dfs_variant == 0)
+    osr::k_valid_dfs<uint32_t, 32, false, FEED><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, st>>>(D, d_q, n, d_out);
+  else if (s.dfs_variant == 1)
+    osr::k_valid_dfs<uint32_t, 64, false, FEED><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, st>>>(D, d_q, n, d_out);
+  else
+    osr::k_valid_dfs<unsigned long long, 48, false, FEED><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, st>>>(D, d_q, n, d_out);
 }
 
 }  // namespace
@@ -396,12 +457,14 @@ static osr::DfsParams dfs_params(const osr_world* w, const Slot& s) {
   P.counters = s.counters;
   P.work_counter = s.work;
   P.error_flag = s.err;
+  P.ready = nullptr;
   return P;
 }
 
 // `lane` 0: the handle's main stream with events around the kernel; 1 / 2: the two pipeline lanes of a host
 // call (main stream / stream2), each with its own work queue word so that consecutive chunks may overlap
-static int launch_valid(osr_world* w, Slot& s, const double* d_q, int64_t n, uint8_t* d_out, int lane = 0) {
+static int launch_valid(osr_world* w, Slot& s, const double* d_q, int64_t n, uint8_t* d_out, int lane = 0,
+                        const long long* ready = nullptr) {
   cudaStream_t st = lane == 2 ? s.stream2 : s.stream;
   unsigned long long* work = lane == 0 ? s.work : s.work + 1 + lane;
   CU(cudaMemsetAsync(work, 0, (lane == 0 ? 2 : 1) * sizeof(unsigned long long), st));
@@ -409,28 +472,19 @@ static int launch_valid(osr_world* w, Slot& s, const double* d_q, int64_t n, uin
     if (n > 0x7fffffffLL) return fail(OSR_EINVAL, "more than 2^31-1 states in one launch");
     osr::DfsParams D = dfs_params(w, s);
     D.work_counter = work;
+    D.ready = ready;
     if (lane != 0) {
-      if (s.dfs_variant == 0 && s.dfs_all_smem)
-        osr::k_valid_dfs<uint32_t, 32, true><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, st>>>(D, d_q, (long long)n, d_out);
-      else if (s.dfs_variant == 0)
-        osr::k_valid_dfs<uint32_t, 32, false><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, st>>>(D, d_q, (long long)n, d_out);
-      else if (s.dfs_variant == 1)
-        osr::k_valid_dfs<uint32_t, 64, false><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, st>>>(D, d_q, (long long)n, d_out);
-      else
-        osr::k_valid_dfs<unsigned long long, 48, false><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, st>>>(D, d_q, (long long)n, d_out);
+      if (ready) {
+        CU(cudaEventRecord(s.ev0, st));
+        launch_dfs_variant<true>(s, D, d_q, (long long)n, d_out, st);
+      } else launch_dfs_variant<false>(s, D, d_q, (long long)n, d_out, st);
       CU(cudaGetLastError());
+      if (ready) CU(cudaEventRecord(s.ev1, st));
       w->host_counters.kernel_launches++;
       return OSR_OK;
     }
     CU(cudaEventRecord(s.ev0, s.stream));
-    if (s.dfs_variant == 0 && s.dfs_all_smem)
-      osr::k_valid_dfs<uint32_t, 32, true><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, s.stream>>>(D, d_q, (long long)n, d_out);
-    else if (s.dfs_variant == 0)
-      osr::k_valid_dfs<uint32_t, 32, false><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, s.stream>>>(D, d_q, (long long)n, d_out);
-    else if (s.dfs_variant == 1)
-      osr::k_valid_dfs<uint32_t, 64, false><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, s.stream>>>(D, d_q, (long long)n, d_out);
-    else
-      osr::k_valid_dfs<unsigned long long, 48, false><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, s.stream>>>(D, d_q, (long long)n, d_out);
+    launch_dfs_variant<false>(s, D, d_q, (long long)n, d_out, s.stream);
     CU(cudaGetLastError());
     CU(cudaEventRecord(s.ev1, s.stream));
     w->host_counters.kernel_launches++;
@@ -468,7 +522,7 @@ static int64_t host_chunk_states() {
   static int64_t v = [] {
     const char* e = getenv("OSR_HOST_CHUNK");
     long long x = e ? atoll(e) : 0;
-    return (int64_t)(x > 0 ? x : (1 << 18));
+    return (int64_t)(x > 0 ? x : (1 << 16));
   }();
   return v;
 }
@@ -481,6 +535,7 @@ int osr_is_valid_states(osr_world* w, const double* q, int64_t n, uint8_t* out) 
   std::lock_guard<std::mutex> lk(w->mu);
   int parts = (int)w->slots.size();
   const int64_t chunk = host_chunk_states();
+  static const bool no_feed = getenv("OSR_NO_STREAM_FEED") != nullptr;  // A/B: chunked two-lane pipeline instead
   for (int i = 0; i < parts; i++) {
     Slot& s = w->slots[i];
     int64_t lo, hi;
@@ -490,6 +545,41 @@ int osr_is_valid_states(osr_world* w, const double* q, int64_t n, uint8_t* out) 
     CU(s.in0.need((size_t)(hi - lo) * 56));
     CU(s.out[0].need((size_t)(hi - lo)));
     int64_t nchunks = (hi - lo + chunk - 1) / chunk;
+    if (nchunks > 1 && s.dfs_variant >= 0 && !w->force_tile_kernel && !no_feed) {
+      // Stream-fed launch: ONE persistent kernel over the whole range.  The upload is queued chunk by chunk on
+      // the copy stream, each chunk followed by an 8-byte copy that advances the device word `ready`; the
+      // kernel's warps pull states in index order and wait on that word, so compute runs under the PCIe
+      // transfer and pays the kernel's ramp-up and tail once.  All copies are enqueued BEFORE the launch, so a
+      // tool that serialises launches (ncu) cannot starve the kernel of its input.
+      int64_t m = hi - lo;
+      int64_t ck = std::max(chunk, (m + MAX_FEED_CHUNKS - 1) / MAX_FEED_CHUNKS);
+      ck = (ck + 1023) / 1024 * 1024;
+      // The word is advanced from a third stream that waits on an event behind each chunk: a write queued on
+      // the copy stream itself would drain the copy engine's pipeline between chunks (~20 us per chunk).
+      CU(cudaEventRecord(s.evp, s.stream));
+      CU(cudaStreamWaitEvent(s.stream2, s.evp, 0));
+      CU(cudaStreamWaitEvent(s.stream3, s.evp, 0));
+      CU(cudaMemsetAsync(s.ready, 0, sizeof(long long), s.stream3));
+      StreamWriteValue64 wv = stream_write_value64();
+      int c = 0;
+      for (int64_t c0 = 0; c0 < m; c0 += ck, c++) {
+        int64_t len = std::min(ck, m - c0);
+        if (!s.feed_ev[c]) CU(cudaEventCreateWithFlags(&s.feed_ev[c], cudaEventDisableTiming));
+        CU(cudaMemcpyAsync((double*)s.in0.p + 7 * c0, q + 7 * (lo + c0), (size_t)len * 56, cudaMemcpyHostToDevice, s.stream2));
+        CU(cudaEventRecord(s.feed_ev[c], s.stream2));
+        CU(cudaStreamWaitEvent(s.stream3, s.feed_ev[c], 0));
+        s.h_ready[c] = c0 + len;
+        if (!wv || wv(s.stream3, (unsigned long long)(uintptr_t)s.ready, (unsigned long long)(c0 + len), 0) != 0)
+          CU(cudaMemcpyAsync(s.ready, s.h_ready + c, sizeof(long long), cudaMemcpyHostToDevice, s.stream3));
+      }
+      CU(cudaStreamWaitEvent(s.stream, s.feed_ev[0], 0));
+      rc = launch_valid(w, s, (const double*)s.in0.p, m, (uint8_t*)s.out[0].p, 1, s.ready);
+      if (rc) return rc;
+      CU(cudaMemcpyAsync(out + lo, s.out[0].p, (size_t)m, cudaMemcpyDeviceToHost, s.stream));
+      CU(cudaEventRecord(s.evq, s.stream3));
+      CU(cudaStreamWaitEvent(s.stream, s.evq, 0));
+      continue;
+    }
     if (nchunks > 1) {  // stream2 joins after whatever the main stream still has queued
       CU(cudaEventRecord(s.evp, s.stream));
       CU(cudaStreamWaitEvent(s.stream2, s.evp, 0));

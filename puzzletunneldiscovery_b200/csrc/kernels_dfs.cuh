@@ -34,7 +34,29 @@ struct DfsParams {
   DevCounters* counters;
   unsigned long long* work_counter;
   int* error_flag;
+  // stream-fed launches (FEED): number of leading states whose upload has completed, advanced by small H2D
+  // copies queued behind each chunk of the input on the copy stream (engine.cu: osr_is_valid_states)
+  const long long* ready;
 };
+
+// Wait (one lane polls, with back-off) until at least `need` states are resident; returns the count observed.
+// Gives up after ~4 s of GPU time: raises the error flag and returns a short count instead of hanging the device
+// if the copies never arrive.
+__device__ __noinline__ long long wait_for_states(const long long* ready, int* error_flag, long long need, int lane) {
+  long long seen = 0;
+  if (lane == 0) {
+    unsigned long long t0, t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    while (true) {
+      asm volatile("ld.acquire.sys.global.s64 %0, [%1];" : "=l"(seen) : "l"(ready) : "memory");
+      if (seen >= need) break;
+      __nanosleep(500);
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+      if (t1 - t0 > 4000000000ull) { atomicExch(error_flag, 2); break; }
+    }
+  }
+  return __shfl_sync(0xffffffffu, seen, 0);
+}
 
 constexpr int DFS_WARPS = 12;   // 3 per scheduler: 4 would need <= 128 registers (16 K registers per SM sub-partition)
 constexpr int DFS_THREADS = DFS_WARPS * 32;
@@ -146,7 +168,7 @@ constexpr unsigned F_PR = 8u;   // ... in the exact-recheck queue
 // The loop body is kept small on purpose: its instruction working set (box test + stack step + the two
 // drains) has to stay inside the 32 KB L1.5 instruction cache shared by the 12 warps.
 // ---------------------------------------------------------------------------------------------------
-template <typename E, int DEPTH, bool ALL_SMEM>
+template <typename E, int DEPTH, bool ALL_SMEM, bool FEED>
 __global__ void __launch_bounds__(DFS_THREADS, 1)
     k_valid_dfs(DfsParams P, const double* __restrict__ q, long long n, uint8_t* __restrict__ out) {
   typedef TaskCodec<E> TC;
@@ -176,6 +198,7 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
   bool exhausted = false, draining_leaf = false, draining_re = false, steal_mode = false;
   unsigned n_bv = 0, n_leaf = 0, n_fp64 = 0;
   unsigned long long nposes = 0;
+  long long ready_seen = 0;  // FEED: states known to be resident (the device word is polled only past this)
 #ifdef OSR_DFS_STATS
   unsigned st_iters = 0, st_active = 0, st_wait = 0, st_idle = 0;
 #endif
@@ -203,6 +226,10 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
         if (lane == 0) base = atomicAdd(P.work_counter, 32ull);
         base = __shfl_sync(FULL, base, 0);
         if ((long long)base >= n) exhausted = true;
+        else if (FEED && min((long long)base + 32, n) > ready_seen &&
+                 (ready_seen = wait_for_states(P.ready, P.error_flag, min((long long)base + 32, n), lane)) <
+                     min((long long)base + 32, n))
+          exhausted = true;
         else {
           long long i = (long long)base + lane;
           bool have = i < n;
