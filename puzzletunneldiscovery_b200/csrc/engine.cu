@@ -16,6 +16,7 @@
 #include "geometry.h"
 #include "kernels.cuh"
 #include "kernels_dfs.cuh"
+#include "kernels_seg.cuh"
 
 namespace {
 
@@ -63,6 +64,10 @@ struct Slot {  // one GPU
   int dfs_env_smem = 0, dfs_rob_smem = 0;
   bool dfs_all_smem = false;   // both trees fit into shared memory entirely
   size_t dfs_smem_bytes = 0;
+  int seg_warps = 0;           // K2 on the depth-first traversal: warps per block (0: tile kernel only)
+  int seg_env_smem = 0, seg_rob_smem = 0;
+  bool seg_all_smem = false;
+  size_t seg_smem_bytes = 0;
   int num_sms = 0;
   osr::DevCounters* counters = nullptr;
   unsigned long long* work = nullptr;   // [0] tile queue, [1] contact record count, [2..] queues of pipelined chunks
@@ -89,6 +94,7 @@ struct osr_world {
   osr::UnitModel env, rob;
   std::vector<Slot> slots;
   osr_counters host_counters = {};
+  bool seg_dfs = false;            // OSR_SEG_KERNEL=dfs: K2 on the lane-owned depth-first traversal
   bool force_tile_kernel = false;  // OSR_VALID_KERNEL=tile: first-generation kernel, kept for A/B measurements
 
   osr::KParams params(const Slot& s) const {
@@ -234,6 +240,35 @@ int init_slot(osr_world* w, Slot& s, int dev) {
       }
     }
   }
+  if (s.dfs_variant >= 0) {  // K2 (kernels_seg.cuh): same tree variants, its own per-warp shared memory
+    int max_smem = 0;
+    CU(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+    const char* e = getenv("OSR_SEG_WARPS");
+    int sw = (s.dfs_variant == 0) ? ((e && atoi(e) == 8) ? 8 : 12) : 8;
+    size_t wm = s.dfs_variant == 0 ? sizeof(osr::SegWarpMem<uint32_t, 32>)
+              : s.dfs_variant == 1 ? sizeof(osr::SegWarpMem<uint32_t, 64>)
+                                   : sizeof(osr::SegWarpMem<unsigned long long, 48>);
+    size_t fixed = wm * sw;
+    long long budget = ((long long)max_smem - (long long)fixed) / 32;
+    if (budget >= 2) {
+      long long ne = w->env.bvh.num_nodes, nr = w->rob.bvh.num_nodes;
+      long long se = std::min(ne, budget / 2), sr = std::min(nr, budget / 2);
+      se = std::min(ne, budget - sr);
+      sr = std::min(nr, budget - se);
+      s.seg_warps = sw;
+      s.seg_env_smem = (int)se; s.seg_rob_smem = (int)sr;
+      s.seg_all_smem = se == ne && sr == nr;
+      s.seg_smem_bytes = (size_t)(se + sr) * 32 + fixed;
+#define OSR_SEG_ATTR(...) CU(cudaFuncSetAttribute(osr::k_transit_dfs<__VA_ARGS__>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem))
+      OSR_SEG_ATTR(uint32_t, 32, true, 8);
+      OSR_SEG_ATTR(uint32_t, 32, false, 8);
+      OSR_SEG_ATTR(uint32_t, 32, true, 12);
+      OSR_SEG_ATTR(uint32_t, 32, false, 12);
+      OSR_SEG_ATTR(uint32_t, 64, false, 8);
+      OSR_SEG_ATTR(unsigned long long, 48, false, 8);
+#undef OSR_SEG_ATTR
+    }
+  }
   s.spill_cap = 8192;
   size_t warps = (size_t)std::max(s.grid_valid, std::max(s.grid_transit, s.grid_contacts)) * osr::WARPS_PER_BLOCK;
   CU(cudaMalloc((void**)&s.spill, warps * s.spill_cap * sizeof(unsigned long long)));
@@ -297,6 +332,8 @@ int osr_create(osr_world** out) {
   *out = new osr_world();
   const char* k = getenv("OSR_VALID_KERNEL");
   (*out)->force_tile_kernel = k && strcmp(k, "tile") == 0;
+  const char* k2 = getenv("OSR_SEG_KERNEL");
+  (*out)->seg_dfs = k2 && strcmp(k2, "dfs") == 0;
   return OSR_OK;
 }
 
@@ -503,6 +540,27 @@ static int launch_transit(osr_world* w, Slot& s, const double* d_from, const dou
                           const double* d_vd, int64_t vd_count, double vd_scalar, int transition_mode,
                           osr::SegOut O) {
   CU(cudaMemsetAsync(s.work, 0, 2 * sizeof(unsigned long long), s.stream));
+  // K2 default = the tile kernel: on every measured segment workload (profiles/r01/README.md) the warp-shared
+  // frontier keeps all 32 lanes busy on the mostly FREE steps of a walk, where depth-first early exit buys nothing.
+  // OSR_SEG_KERNEL=dfs selects the lane-owned depth-first variant (kernels_seg.cuh) for A/B runs.
+  if (s.seg_warps > 0 && w->seg_dfs) {
+    osr::DfsParams D = dfs_params(w, s);
+    D.env_smem_nodes = s.seg_env_smem; D.rob_smem_nodes = s.seg_rob_smem;
+    osr::SegArgs A = {d_from, d_to, (long long)n, d_vd, (long long)vd_count, vd_scalar, transition_mode, O};
+    CU(cudaEventRecord(s.ev0, s.stream));
+    const int nb = s.num_sms, nt = s.seg_warps * 32;
+    const size_t sm = s.seg_smem_bytes;
+    if (s.dfs_variant == 0 && s.seg_warps == 8 && s.seg_all_smem) osr::k_transit_dfs<uint32_t, 32, true, 8><<<nb, nt, sm, s.stream>>>(D, A);
+    else if (s.dfs_variant == 0 && s.seg_warps == 8) osr::k_transit_dfs<uint32_t, 32, false, 8><<<nb, nt, sm, s.stream>>>(D, A);
+    else if (s.dfs_variant == 0 && s.seg_all_smem) osr::k_transit_dfs<uint32_t, 32, true, 12><<<nb, nt, sm, s.stream>>>(D, A);
+    else if (s.dfs_variant == 0) osr::k_transit_dfs<uint32_t, 32, false, 12><<<nb, nt, sm, s.stream>>>(D, A);
+    else if (s.dfs_variant == 1) osr::k_transit_dfs<uint32_t, 64, false, 8><<<nb, nt, sm, s.stream>>>(D, A);
+    else osr::k_transit_dfs<unsigned long long, 48, false, 8><<<nb, nt, sm, s.stream>>>(D, A);
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(s.ev1, s.stream));
+    w->host_counters.kernel_launches++;
+    return OSR_OK;
+  }
   osr::KParams P = w->params(s);
   CU(cudaEventRecord(s.ev0, s.stream));
   osr::k_transit<<<s.grid_transit, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK, s.stream>>>(
