@@ -63,6 +63,8 @@ double osr_scene_scale(const osr_world* w);
 double osr_get_recommended_cres(const osr_world* w);
 int osr_set_recommended_cres(osr_world* w, double v);
 int osr_get_robot_center(const osr_world* w, double c[3]);
+/* UnitWorld::getOMPLCenter(geo) (unit_world.cc:1562-1565): mean of the mesh's vertices, which=0 env, 1 robot */
+int osr_get_ompl_center(const osr_world* w, int which, double c[3]);
 int osr_num_devices(const osr_world* w);
 /* geometry read-back (CDModel::vertices()/faces(), cdmodel.cc:232-246): which 0=env 1=robot */
 int osr_mesh_sizes(const osr_world* w, int which, int* nV, int* nF, int* nNodes, int* depth);
@@ -137,6 +139,17 @@ int osr_translate_unit_to_ompl(const osr_world* w, const double* q, int64_t n, d
 double osr_distance(const double a[7], const double b[7]);
 void osr_interpolate(const double a[7], const double b[7], double tau, double out[7]);
 void osr_apply(const double from[7], const double tr[3], const double aa[3], double out[7]);
+
+/* UnitWorld::intersectingToModelSurface (which=0) / intersectingToRobotSurface (which=1)
+ * (unit_world.cc:928-957 -> intersectingToSurface :1092-1176): every (surface face i, mesh face j) pair that
+ * Moeller97 reports as intersecting AND coplanar, in the reference's order (j outer, i inner).  Row r gets
+ * out_faces[r][3] = vertex ids of surface face i and out_bary[3r+v][3] = barycentric coordinates (libigl
+ * formula) of vertex v of mesh face j w.r.t. the world-space surface triangle.  `q` is the UNIT state of the
+ * robot (ignored for which=0, where the environment transform is the perturbation).  *total = rows found;
+ * at most `cap` rows are written. */
+int osr_intersecting_to_surface(osr_world* w, int which, const double* q, const double* V, int64_t nV,
+                                const int32_t* F, int64_t nF, int64_t cap, int32_t* out_faces,
+                                double* out_bary, int64_t* total);
 
 /* Device-resident variants (pointers on the handle's first device).  Launch only; the caller
  * synchronises with osr_sync() (or its own stream wait on osr_stream()). */

@@ -71,6 +71,8 @@ def lib():
     L.orc_apply.argtypes = [_dp, _dp, _dp, _dp]
     L.orc_sat17.argtypes = [_dp]
     L.orc_contact_multiplicity.argtypes = [_dp]
+    L.orc_surface_map.argtypes = [_dp, _ip, C.c_longlong, _dp, _ip, C.c_longlong, C.c_longlong, _ip, _dp]
+    L.orc_surface_map.restype = C.c_longlong
     ref = os.path.join(_HERE, "_ref", "libmoller97d.so")
     if os.path.exists(ref):
         _MOLLER = C.CDLL(ref)
@@ -117,6 +119,19 @@ def sat17(P, Q):
 def contact_multiplicity(P, Q):
     t = np.ascontiguousarray(np.concatenate([np.asarray(P, float).reshape(9), np.asarray(Q, float).reshape(9)]))
     return int(lib().orc_contact_multiplicity(_ptr(t, _dp)))
+
+
+def surface_map(TV, TF, V, F, cap=1 << 16):
+    """unit_world.cc:1092-1176 on world-space target vertices TV -> (faces[K,3], barycentrics[3K,3])."""
+    TV = np.ascontiguousarray(TV, dtype=np.float64); TF = np.ascontiguousarray(TF, dtype=np.int32)
+    V = np.ascontiguousarray(V, dtype=np.float64); F = np.ascontiguousarray(F, dtype=np.int32)
+    of = np.zeros((cap, 3), np.int32); ol = np.zeros((3 * cap, 3))
+    k = lib().orc_surface_map(_ptr(TV, _dp), _ptr(TF, _ip), len(TF), _ptr(V, _dp), _ptr(F, _ip), len(F), cap,
+                              _ptr(of, _ip), _ptr(ol, _dp))
+    if k < 0:
+        raise RuntimeError("oracle/_ref/libmoller97d.so (the reference's Moeller routine) is not built")
+    assert k <= cap
+    return of[:k].copy(), ol[:3 * k].copy()
 
 
 def interpolate(a, b, tau):

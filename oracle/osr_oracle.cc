@@ -950,4 +950,42 @@ int orc_contact_multiplicity(const double* t) {
   for (int i = 0; i < 6; i++) v[i] = {t[3 * i], t[3 * i + 1], t[3 * i + 2]};
   return (int)orc::contact_multiplicity(v[0], v[1], v[2], v[3], v[4], v[5]);
 }
+// UnitWorld::intersectingToSurface (unit_world.cc:1092-1176): TriTriCopIsect (lib/tritri/tritri_cop.hh:115-151)
+// over every (target face i, mesh face j) pair with the REFERENCE's Moeller routine (oracle/_ref), kept when
+// it intersects and is coplanar; rows in Eigen's column-major SparseMatrix order (j outer, i inner); libigl
+// barycentric_coordinates (third-party/libigl/include/igl/barycentric_coordinates.cpp) per vertex of face j.
+// TV = world-space target vertices.  Returns the number of rows found; writes at most `cap`.
+long long orc_surface_map(const double* TV, const int* TF, long long nTF, const double* V, const int* F,
+                          long long nF, long long cap, int* outF, double* outL) {
+  if (!orc::g_moller) return -1;
+  long long rows = 0;
+  for (long long j = 0; j < nF; j++) {
+    const double* u[3] = {V + 3 * F[3 * j], V + 3 * F[3 * j + 1], V + 3 * F[3 * j + 2]};
+    for (long long i = 0; i < nTF; i++) {
+      const double* v[3] = {TV + 3 * TF[3 * i], TV + 3 * TF[3 * i + 1], TV + 3 * TF[3 * i + 2]};
+      int cop = 0;
+      double p0[3], p1[3];
+      int isect = orc::g_moller(v[0], v[1], v[2], u[0], u[1], u[2], &cop, p0, p1);
+      if (!(isect && cop)) continue;
+      if (rows < cap) {
+        for (int k = 0; k < 3; k++) outF[3 * rows + k] = TF[3 * i + k];
+        for (int p = 0; p < 3; p++) {
+          double v0[3], v1[3], v2[3];
+          for (int k = 0; k < 3; k++) { v0[k] = v[1][k] - v[0][k]; v1[k] = v[2][k] - v[0][k]; v2[k] = u[p][k] - v[0][k]; }
+          double d00 = v0[0] * v0[0] + v0[1] * v0[1] + v0[2] * v0[2], d01 = v0[0] * v1[0] + v0[1] * v1[1] + v0[2] * v1[2];
+          double d11 = v1[0] * v1[0] + v1[1] * v1[1] + v1[2] * v1[2], d20 = v2[0] * v0[0] + v2[1] * v0[1] + v2[2] * v0[2];
+          double d21 = v2[0] * v1[0] + v2[1] * v1[1] + v2[2] * v1[2];
+          double den = d00 * d11 - d01 * d01;
+          double* L = outL + 9 * rows + 3 * p;
+          L[1] = (d11 * d20 - d01 * d21) / den;
+          L[2] = (d00 * d21 - d01 * d20) / den;
+          L[0] = 1.0 - (L[1] + L[2]);
+        }
+      }
+      rows++;
+    }
+  }
+  return rows;
+}
+
 }  // extern "C"

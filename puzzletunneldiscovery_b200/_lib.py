@@ -38,6 +38,7 @@ SIGNATURES = {
     "osr_get_recommended_cres": (C.c_double, [C.c_void_p]),
     "osr_set_recommended_cres": (C.c_int, [C.c_void_p, C.c_double]),
     "osr_get_robot_center": (C.c_int, [C.c_void_p, c_dp]),
+    "osr_get_ompl_center": (C.c_int, [C.c_void_p, C.c_int, c_dp]),
     "osr_num_devices": (C.c_int, [C.c_void_p]),
     "osr_mesh_sizes": (C.c_int, [C.c_void_p, C.c_int] + [C.POINTER(C.c_int)] * 4),
     "osr_get_unit_mesh": (C.c_int, [C.c_void_p, C.c_int, c_dp, c_i32p]),
@@ -54,6 +55,8 @@ SIGNATURES = {
                                       c_i8p]),
     "osr_intersecting_segments": (C.c_int, [C.c_void_p, c_dp, C.c_int64, C.c_int64, c_i64p, c_dp, c_i32p, c_u8p, c_dp,
                                             c_u8p, c_i64p]),
+    "osr_intersecting_to_surface": (C.c_int, [C.c_void_p, C.c_int, c_dp, c_dp, C.c_int64, c_i32p, C.c_int64, C.c_int64,
+                                              c_i32p, c_dp, c_i64p]),
     "osr_enum_free_configurations": (C.c_int, [C.c_void_p, c_dp, C.c_int64, C.c_double, C.c_int, C.c_int, c_dp, c_u8p,
                                                c_i32p]),
     "osr_translate_to_unit": (C.c_int, [C.c_void_p, c_dp, C.c_int64, c_dp]),

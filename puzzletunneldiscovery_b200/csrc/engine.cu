@@ -17,6 +17,7 @@
 #include "kernels.cuh"
 #include "kernels_dfs.cuh"
 #include "kernels_seg.cuh"
+#include "kernels_surface.cuh"
 
 namespace {
 
@@ -76,6 +77,7 @@ struct Slot {  // one GPU
   int grid_valid = 0, grid_transit = 0, grid_contacts = 0;
   int spill_cap = 0;
   DevBuf in0, in1, vd, out[6], recs, rowrec, seg, faces, cop, bary;
+  DevBuf surf_v, surf_f, surf_flags, surf_cnt, surf_off, surf_face, surf_l;  // K5 (kernels_surface.cuh)
 };
 
 }  // namespace
@@ -152,6 +154,8 @@ void free_slot(Slot& s) {
   cudaFree(s.counters); cudaFree(s.work); cudaFree(s.spill); cudaFree(s.err);
   s.in0.release(); s.in1.release(); s.vd.release();
   for (auto& b : s.out) b.release();
+  s.surf_v.release(); s.surf_f.release(); s.surf_flags.release(); s.surf_cnt.release(); s.surf_off.release();
+  s.surf_face.release(); s.surf_l.release();
   s.recs.release(); s.rowrec.release(); s.seg.release(); s.faces.release(); s.cop.release(); s.bary.release();
   if (s.ev0) cudaEventDestroy(s.ev0);
   if (s.ev1) cudaEventDestroy(s.ev1);
@@ -440,6 +444,14 @@ int osr_set_recommended_cres(osr_world* w, double v) {
 int osr_get_robot_center(const osr_world* w, double c[3]) {
   if (!w || !c) return fail(OSR_EINVAL, "bad arguments");
   for (int k = 0; k < 3; k++) c[k] = w->centre[k];
+  return OSR_OK;
+}
+int osr_get_ompl_center(const osr_world* w, int which, double c[3]) {  // Scene::getOMPLCenter = mean of vertices
+  if (!w || !c || !w->host_ready) return fail(OSR_EINVAL, "geometry not built: call osr_finalize()");
+  float m[3];
+  if (which) for (int k = 0; k < 3; k++) m[k] = w->ompl_centre[k];
+  else osr::mean_of_vertices(w->env_mesh, m);
+  for (int k = 0; k < 3; k++) c[k] = m[k];
   return OSR_OK;
 }
 int osr_num_devices(const osr_world* w) { return w ? (int)w->slots.size() : 0; }
@@ -1093,6 +1105,68 @@ int osr_intersecting_segments(osr_world* w, const double* q, int64_t n, int64_t 
     CU(cudaSetDevice(s.dev));
     CU(cudaStreamSynchronize(s.stream));
   }
+  return OSR_OK;
+}
+
+// ---- surface mapping of an intersection mesh (unit_world.cc:928-957, 1092-1176) -------------------
+int osr_intersecting_to_surface(osr_world* w, int which, const double* q, const double* V, int64_t nV,
+                                const int32_t* F, int64_t nF, int64_t cap, int32_t* out_faces, double* out_bary,
+                                int64_t* total) {
+  int rc = check_ready(w);
+  if (rc) return rc;
+  if ((which != 0 && which != 1) || nV < 0 || nF < 0 || cap < 0 || !total || (which == 1 && !q) ||
+      (nF > 0 && (!V || !F)) || (cap > 0 && (!out_faces || !out_bary)))
+    return fail(OSR_EINVAL, "bad arguments");
+  for (int64_t i = 0; i < 3 * nF; i++)
+    if (F[i] < 0 || F[i] >= nV) return fail(OSR_EINVAL, "face index out of range");
+  *total = 0;
+  if (nF == 0) return OSR_OK;
+  std::lock_guard<std::mutex> lk(w->mu);
+  Slot& s = w->slots[0];
+  CU(cudaSetDevice(s.dev));
+  const osr::UnitModel& tm = which ? w->rob : w->env;
+  const double* d_tris = which ? s.rob_tris : s.env_tris;
+  osr::Rigid tf;
+  if (which) osr::state_to_rigid(q, tf);          // getRobotGeometry: translate_state_to_transform(q) * V
+  else osr::state_to_rigid(w->perturb, tf);       // getSceneGeometry: the environment transform of getCDTransforms
+  const long long nT = tm.nf(), pairs = nT * (long long)nF;
+  const long long nblocks = (pairs + osr::SURF_BLOCK - 1) / osr::SURF_BLOCK;
+  if (nblocks > 0x7fffffffLL) return fail(OSR_EINVAL, "too many triangle pairs for one call");
+  CU(s.surf_v.need((size_t)nV * 24));
+  CU(s.surf_f.need((size_t)nF * 12));
+  CU(s.surf_flags.need((size_t)pairs));
+  CU(s.surf_cnt.need((size_t)nblocks * 4));
+  CU(s.surf_off.need((size_t)nblocks * 8));
+  CU(cudaMemcpyAsync(s.surf_v.p, V, (size_t)nV * 24, cudaMemcpyHostToDevice, s.stream));
+  CU(cudaMemcpyAsync(s.surf_f.p, F, (size_t)nF * 12, cudaMemcpyHostToDevice, s.stream));
+  osr::k_surface_flags<<<(unsigned)nblocks, osr::SURF_BLOCK, 0, s.stream>>>(
+      d_tris, tf, nT, (const double*)s.surf_v.p, (const int*)s.surf_f.p, (long long)nF, (uint8_t*)s.surf_flags.p,
+      (int*)s.surf_cnt.p);
+  CU(cudaGetLastError());
+  w->host_counters.kernel_launches++;
+  std::vector<int> cnt((size_t)nblocks);
+  CU(cudaMemcpyAsync(cnt.data(), s.surf_cnt.p, (size_t)nblocks * 4, cudaMemcpyDeviceToHost, s.stream));
+  CU(cudaStreamSynchronize(s.stream));
+  std::vector<long long> off((size_t)nblocks);
+  long long found = 0;
+  for (long long b = 0; b < nblocks; b++) { off[(size_t)b] = found; found += cnt[(size_t)b]; }
+  *total = found;
+  long long rows = std::min<long long>(found, cap);
+  if (rows == 0) return OSR_OK;
+  CU(s.surf_face.need((size_t)rows * 4));
+  CU(s.surf_l.need((size_t)rows * 72));
+  CU(cudaMemcpyAsync(s.surf_off.p, off.data(), (size_t)nblocks * 8, cudaMemcpyHostToDevice, s.stream));
+  osr::k_surface_emit<<<(unsigned)nblocks, osr::SURF_BLOCK, 0, s.stream>>>(
+      d_tris, tf, nT, (const double*)s.surf_v.p, (const int*)s.surf_f.p, (long long)nF, (const uint8_t*)s.surf_flags.p,
+      (const long long*)s.surf_off.p, rows, (int*)s.surf_face.p, (double*)s.surf_l.p);
+  CU(cudaGetLastError());
+  w->host_counters.kernel_launches++;
+  std::vector<int> face((size_t)rows);
+  CU(cudaMemcpyAsync(face.data(), s.surf_face.p, (size_t)rows * 4, cudaMemcpyDeviceToHost, s.stream));
+  CU(cudaMemcpyAsync(out_bary, s.surf_l.p, (size_t)rows * 72, cudaMemcpyDeviceToHost, s.stream));
+  CU(cudaStreamSynchronize(s.stream));
+  for (long long r = 0; r < rows; r++)  // retF.row = targetF.row(target_fi)
+    for (int k = 0; k < 3; k++) out_faces[3 * r + k] = tm.F[(size_t)3 * face[(size_t)r] + k];
   return OSR_OK;
 }
 

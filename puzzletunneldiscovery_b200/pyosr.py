@@ -73,6 +73,145 @@ def compose_from_angleaxis(tr, angle, axis):
     return np.concatenate([np.asarray(tr, dtype=np.float64), q])
 
 
+def _quat_normalized(q):
+    q = np.asarray(q, dtype=np.float64)
+    n2 = float((q * q).sum())
+    return q / np.sqrt(n2) if n2 > 0 else q.copy()
+
+
+def _quat_mul(a, b):
+    aw, ax, ay, az = a
+    bw, bx, by, bz = b
+    return np.array([aw * bw - ax * bx - ay * by - az * bz, aw * bx + ax * bw + ay * bz - az * by,
+                     aw * by + ay * bw + az * bx - ax * bz, aw * bz + az * bw + ax * by - ay * bx])
+
+
+def _quat_to_rot(q):
+    w, x, y, z = q
+    tx, ty, tz = 2 * x, 2 * y, 2 * z
+    twx, twy, twz = tx * w, ty * w, tz * w
+    txx, txy, txz = tx * x, ty * x, tz * x
+    tyy, tyz, tzz = ty * y, tz * y, tz * z
+    return np.array([[1 - (tyy + tzz), txy - twz, txz + twy], [txy + twz, 1 - (txx + tzz), tyz - twx],
+                     [txz - twy, tyz + twx, 1 - (txx + tyy)]])
+
+
+def _quat_rotate(q, v):
+    """Eigen Quaternion::_transformVector: v + w (2 u x v) + u x (2 u x v)."""
+    u = np.asarray(q[1:4], dtype=np.float64)
+    uv = 2.0 * np.cross(u, v)
+    return v + q[0] * uv + np.cross(u, uv)
+
+
+def _angle_axis_from_quat(q):
+    """Eigen 3.3 AngleAxis(Quaternion): angle = 2 atan2(|vec|, |w|), axis = vec / (+-|vec|); (0, x) if vec = 0."""
+    n = float(np.linalg.norm(q[1:4]))
+    if n != 0.0:
+        angle = 2.0 * np.arctan2(n, abs(q[0]))
+        if q[0] < 0:
+            n = -n
+        return angle, np.asarray(q[1:4], dtype=np.float64) / n
+    return 0.0, np.array([1.0, 0.0, 0.0])
+
+
+def _angular_distance(a, b):
+    """Eigen 3.3 Quaternion::angularDistance: 2 atan2(|vec(d)|, |w(d)|), d = a * conj(b)."""
+    d = _quat_mul(a, np.array([b[0], -b[1], -b[2], -b[3]]))
+    return 2.0 * np.arctan2(np.linalg.norm(d[1:4]), abs(d[0]))
+
+
+def _quat_from_two_vectors(a, b):
+    """Eigen 3.3 Quaternion::setFromTwoVectors (generic branch; antiparallel: any perpendicular axis)."""
+    v0 = np.asarray(a, dtype=np.float64) / np.linalg.norm(a)
+    v1 = np.asarray(b, dtype=np.float64) / np.linalg.norm(b)
+    c = float(v1 @ v0)
+    if c < -1.0 + 1e-12:
+        h = np.array([0.0, 1.0, 0.0]) if abs(v0[0]) > 0.9 else np.array([1.0, 0.0, 0.0])
+        ax = np.cross(v0, h)
+        ax /= np.linalg.norm(ax)
+        return np.concatenate([[0.0], ax])
+    ax = np.cross(v0, v1)
+    s = np.sqrt((1.0 + c) * 2.0)
+    return np.concatenate([[s * 0.5], ax / s])
+
+
+def decompose_2(state):
+    """osr_state.cc:94-99 -> (translation, rotation matrix of the normalised quaternion)."""
+    s = _states(state)[0]
+    return s[0:3].copy(), _quat_to_rot(_quat_normalized(s[3:7]))
+
+
+def decompose_3(state):
+    """osr_state.cc:101-108 -> (translation, angle, axis)."""
+    s = _states(state)[0]
+    angle, axis = _angle_axis_from_quat(_quat_normalized(s[3:7]))
+    return s[0:3].copy(), angle, axis
+
+
+def extract_rotation_matrix(state):
+    """osr_state.cc:169-174 (quaternion used as given)."""
+    return _quat_to_rot(_states(state)[0][3:7])
+
+
+def differential(from_state, to_state):
+    """osr_state.cc:176-222 -> (translation, angle-axis vector, SE(3) delta state)."""
+    a = _states(from_state)[0]; b = _states(to_state)[0]
+    tr = b[0:3] - a[0:3]
+    qa, qb = a[3:7], b[3:7]
+    inv = np.array([qa[0], -qa[1], -qa[2], -qa[3]]) / float((qa * qa).sum())   # Eigen inverse(): conj / |q|^2
+    delta = _quat_mul(qb, inv)
+    angle, axis = _angle_axis_from_quat(delta)
+    aav = axis * angle
+    half = 0.5 * angle
+    rec = _quat_mul(np.concatenate([[np.cos(half)], np.sin(half) * axis]), qa)
+    if _angular_distance(qb, rec) > 1e-3:
+        raise OsrError("differential is buggy")
+    nrm = np.linalg.norm(aav)
+    if nrm > 0:
+        rec2 = _quat_mul(np.concatenate([[np.cos(0.5 * nrm)], np.sin(0.5 * nrm) * (aav / nrm)]), qa)
+        if _angular_distance(qb, rec2) > 1e-3:
+            raise OsrError("differential is buggy in aa->quat")
+    return tr, aav, np.concatenate([tr, _quat_normalized(delta)])
+
+
+def multi_differential(from_state, to_states, with_se3=False):
+    """osr_state.cc:224-241."""
+    tos = _states(to_states)
+    rows = []
+    for t in tos:
+        tr, aav, se3 = differential(from_state, t)
+        rows.append(np.concatenate([tr, aav, se3]) if with_se3 else np.concatenate([tr, aav]))
+    return np.array(rows).reshape(len(tos), 13 if with_se3 else 6)
+
+
+def path_metrics(qs):
+    """osr_state.cc:46-59: cumulative osr distance along a path."""
+    qs = _states(qs)
+    out = np.zeros(len(qs))
+    d = 0.0
+    for i in range(len(qs)):
+        if i > 0:
+            d += distance(qs[i - 1], qs[i])
+        out[i] = d
+    return out
+
+
+def path_interpolate(qs, metrics, tau):
+    """osr_state.cc:61-84."""
+    qs = _states(qs)
+    metrics = np.asarray(metrics, dtype=np.float64)
+    key = -1
+    for i in range(len(qs) - 1):
+        if metrics[i] <= tau < metrics[i + 1]:
+            key = i
+            break
+    if key < 0:
+        return qs[0].copy()
+    d = metrics[key + 1] - metrics[key]
+    t = 0.0 if d < 1e-6 else (tau - metrics[key]) / d
+    return interpolate(qs[key], qs[key + 1], t)
+
+
 class UnitWorld:
     """Drop-in for pyosr.UnitWorld (hot-path subset).  See include/osrgpu.h for the ABI below it."""
 
@@ -129,6 +268,7 @@ class UnitWorld:
     def set_perturbation(self, q):
         q = _states(q)[0]
         check(self._L.osr_set_perturbation(self._h, _p(q, c_dp)))
+        self._perturbation = q.copy()
 
     @property
     def scene_scale(self):
@@ -294,6 +434,147 @@ class UnitWorld:
         seg = r["seg"]
         mag = np.sqrt(((seg[:, 3:6] - seg[:, 0:3]) ** 2).sum(axis=1)).reshape(-1, 1)
         return seg[:, 0:3].copy(), seg[:, 3:6].copy(), mag, r["faces"]
+
+    # ---- discrete actions (module.cc:140; unit_world.cc:267-336) ---------------------------------
+    def transit_state(self, state, action, transit_magnitude, verify_delta):
+        """12 discrete actions: 0-5 = +-x, +-y, +-z translation, 6-11 = rotation about x, y, z.  The reference
+        keeps magnitudes and deltas in C float and halves verify_delta until the walk makes progress."""
+        state = _states(state)[0]
+        if action >= 12:
+            return state.copy(), False, 0.0
+        if not self.is_valid_state(state):
+            return state.copy(), False, 0.0
+        action_type = 0 if action < 6 else 1
+        deltacap = float(np.float32(verify_delta) if action_type == 0 else np.float32(verify_delta * 2))
+        sym = 1.0 if action % 2 == 0 else -1.0
+        axis_id = (action - 6 * action_type) // 2
+        tfvec = np.zeros(3); tfvec[axis_id] = 1.0
+        trans = state[0:3].copy()
+        rot = _quat_normalized(state[3:7])
+        if action_type == 0:
+            trans = trans + deltacap * tfvec * sym
+        else:
+            half = 0.5 * deltacap * sym
+            rot = _quat_mul(np.concatenate([[np.cos(half)], np.sin(half) * tfvec]), rot)
+        to_state = np.concatenate([trans, _quat_normalized(rot)])
+        cur = np.float32(verify_delta)
+        while True:
+            free_state, done, prog = self.transit_state_to(state, to_state, float(cur))
+            if not self.is_valid_state(free_state):
+                raise OsrError("SAN check failed, invalid state from transitStateTo")
+            if prog > 0.0 or cur == 0.0:
+                return free_state, done, prog
+            cur = np.float32(cur / np.float32(2.0))
+
+    # ---- frames (module.cc:136-137, 164-167, 241, 249-250) ----------------------------------------
+    @property
+    def perturbation(self):
+        return getattr(self, "_perturbation", get_identity_state_vector())
+
+    def get_ompl_center(self, geo=1):
+        c = np.zeros(3)
+        check(self._L.osr_get_ompl_center(self._h, int(geo), _p(c, c_dp)))
+        return c
+
+    @property
+    def scene_matrix(self):
+        """Scene::getCalibrationTransform after angleModel(0,0): glm::scale(scene_scale) in C float."""
+        s = np.float32(self.scene_scale)
+        return np.diag([s, s, s, np.float32(1)]).astype(np.float64)
+
+    @property
+    def robot_matrix(self):
+        """scale(scene_scale) * translate(-center), float arithmetic (unit_world.cc:152-158, scene.cc:211-230)."""
+        s = np.float32(self.scene_scale)
+        m = np.diag([s, s, s, np.float32(1)]).astype(np.float32)
+        m[0:3, 3] = s * (-self.robot_center.astype(np.float32))
+        return m.astype(np.float64)
+
+    def translate_vanilla_to_ompl(self, qs):
+        """unit_world.cc:606-631: w-last quaternions, t_ompl = t_vanilla + R * ompl_center."""
+        q = _states(qs)
+        oc = self.get_ompl_center(self.GEO_ROB)
+        out = q.copy()
+        for i in range(len(q)):
+            rot = _quat_normalized(np.array([q[i, 6], q[i, 3], q[i, 4], q[i, 5]]))
+            out[i, 0:3] = q[i, 0:3] + _quat_rotate(rot, oc)
+        return out
+
+    def translate_ompl_to_vanilla(self, qs):
+        """unit_world.cc:641-661."""
+        q = _states(qs)
+        oc = self.get_ompl_center(self.GEO_ROB)
+        out = q.copy()
+        for i in range(len(q)):
+            rot = _quat_normalized(np.array([q[i, 6], q[i, 3], q[i, 4], q[i, 5]]))
+            out[i, 0:3] = q[i, 0:3] - _quat_rotate(rot, oc)
+        return out
+
+    def translate_vanilla_to_unit(self, qs):
+        return self.translate_ompl_to_unit(self.translate_vanilla_to_ompl(qs))
+
+    def translate_vanilla_pts_to_unit(self, geo, pts):
+        """unit_world.cc:669-687: (pts - ompl_center [robot only]) scaled by the calibration matrix."""
+        pts = np.asarray(pts, dtype=np.float64).reshape(-1, 3)
+        if len(pts) == 0:
+            return np.zeros((0, 3))
+        if geo != self.GEO_ENV:
+            pts = pts - self.get_ompl_center(self.GEO_ROB)
+        return pts * float(np.float32(self.scene_scale))
+
+    # ---- sampled key configurations (module.cc:211-218; unit_world.cc:1295-1337) ------------------
+    def sample_free_configuration(self, rob_surface_point, rob_surface_normal, env_surface_point, env_surface_normal,
+                                  margin, max_trials=-1, rng=None, batch=64):
+        """Random rotation about the environment normal until the placed robot is free.  The reference draws
+        one angle per trial from std::random_device; here trials are evaluated `batch` at a time on the GPU
+        (angles from `rng`, a numpy Generator) and the first free one in draw order is returned, or the last
+        trial when max_trials is exhausted -- the reference's return value in that case."""
+        rng = rng or np.random.default_rng()
+        rp, rn, ep, en = (np.asarray(x, dtype=np.float64).reshape(3) for x in
+                          (rob_surface_point, rob_surface_normal, env_surface_point, env_surface_normal))
+        rob_o = rp + rn * margin
+        env_o = ep + en * margin
+        rot1 = _quat_from_two_vectors(rn, -en)
+        done = 0
+        while True:
+            n = batch if max_trials < 0 else min(batch, max_trials + 1 - done)
+            ang = rng.uniform(0.0, 2.0 * np.pi, n)
+            qs = np.empty((n, 7))
+            for i, a in enumerate(ang):
+                rot2 = np.concatenate([[np.cos(0.5 * a)], np.sin(0.5 * a) * en])   # AngleAxis: axis used as given
+                acc = _quat_mul(rot2, rot1)
+                qs[i, 0:3] = env_o - _quat_rotate(acc, rob_o)
+                qs[i, 3:7] = _quat_normalized(acc)
+            v = self.is_valid_states(qs)
+            if v.any():
+                return qs[int(np.argmax(v))]
+            done += n
+            if max_trials >= 0 and done > max_trials:
+                return qs[-1]
+
+    # ---- surface mapping (module.cc: intersecting_to_robot_surface / intersecting_to_model_surface) ----
+    def _to_surface(self, which, q, q_is_unit, V, F):
+        """unit_world.cc:928-957 + 1092-1176 -> (faces int32[K,3], barycentrics float64[3K,3])."""
+        qu = _states(q)[0] if q_is_unit else self.translate_to_unit_state(q)
+        V = np.ascontiguousarray(np.asarray(V, dtype=np.float64).reshape(-1, 3))
+        F = np.ascontiguousarray(np.asarray(F, dtype=np.int32).reshape(-1, 3))
+        total = C.c_int64(0)
+        cap = 1 << 14
+        while True:
+            of = np.zeros((cap, 3), np.int32); ob = np.zeros((3 * cap, 3))
+            check(self._L.osr_intersecting_to_surface(self._h, which, _p(np.ascontiguousarray(qu), c_dp), _p(V, c_dp),
+                                                      len(V), _p(F, c_i32p), len(F), cap, _p(of, c_i32p),
+                                                      _p(ob, c_dp), C.byref(total)))
+            k = int(total.value)
+            if k <= cap:
+                return of[:k].copy(), ob[:3 * k].copy()
+            cap = k
+
+    def intersecting_to_robot_surface(self, q, q_is_unit, V, F):
+        return self._to_surface(self.GEO_ROB, q, q_is_unit, V, F)
+
+    def intersecting_to_model_surface(self, q, q_is_unit, V, F):
+        return self._to_surface(self.GEO_ENV, q, q_is_unit, V, F)
 
     # ---- key configurations (module.cc:219-227) --------------------------------------------------
     def enum_free_configurations(self, pts, margin, denominator, only_median=False):

@@ -132,3 +132,47 @@ def test_product_package_never_imports_the_oracle():
                 assert "oracle" not in src.replace("test oracle", "").replace("the oracle", "") or f == "workloads.py" \
                     or "import oracle" not in src and "from oracle" not in src
                 assert "from oracle" not in src and "import oracle" not in src and "libosr_oracle" not in src
+
+
+def test_state_helpers_round_trips(oracle_mod):
+    """osr_state.cc helpers mirrored on the host: differential inverts apply, decompose_3 inverts
+    compose_from_angleaxis, path_interpolate hits the way points of a path at its own metrics."""
+    rs = np.random.RandomState(5)
+    a = W.random_states(1, 9)[0]
+    for _ in range(16):
+        tr = rs.rand(3) - 0.5
+        aa = (rs.rand(3) - 0.5) * 2.0
+        b = pyosr.apply(a, tr, aa)
+        dtr, daa, se3 = pyosr.differential(a, b)
+        assert np.abs(dtr - tr).max() < 1e-12 and np.abs(daa - aa).max() < 1e-9
+        assert abs(np.linalg.norm(se3[3:]) - 1.0) < 1e-12
+    t, ang, ax = pyosr.decompose_3(pyosr.compose_from_angleaxis([1, 2, 3], 0.7, [0, 0.6, 0.8]))
+    assert np.allclose(t, [1, 2, 3]) and abs(ang - 0.7) < 1e-12 and np.allclose(ax, [0, 0.6, 0.8])
+    t, R = pyosr.decompose_2(a)
+    assert np.allclose(R @ R.T, np.eye(3), atol=1e-12) and np.allclose(t, a[:3])
+    assert pyosr.multi_differential(a, W.random_states(5, 3), with_se3=True).shape == (5, 13)
+    path = np.load(os.path.join(ASSETS, "alpha-1.2.org.w-first.npz"))["VS"][:12]
+    m = pyosr.path_metrics(path)
+    assert m[0] == 0.0 and (np.diff(m) >= 0).all()
+    assert abs(m[3] - sum(oracle_mod.distance(path[i], path[i + 1]) for i in range(3))) < 1e-12
+    for i in (0, 4, 10):
+        got = pyosr.path_interpolate(path, m, m[i])
+        want = path[i].copy(); want[3:] /= np.linalg.norm(want[3:])
+        assert np.abs(got - want).max() < 1e-12 or np.abs(got[3:] + want[3:]).max() < 1e-12
+    assert np.array_equal(pyosr.path_interpolate(path, m, m[-1] + 1.0), path[0])   # outside: first row (:73-75)
+
+
+def test_vanilla_frames_and_matrices():
+    w, _ = _host_world("wt2", W.ROB_OMPL_CENTER)
+    q = W.random_states(16, 4)
+    q = np.concatenate([q[:, :3] * 30, q[:, 4:7], q[:, 3:4]], axis=1)     # OMPL-style: w-last
+    back = w.translate_ompl_to_vanilla(w.translate_vanilla_to_ompl(q))
+    assert np.abs(back - q).max() < 1e-12
+    oc = w.get_ompl_center(1)
+    V, _ = W.load_obj_vf(os.path.join(ASSETS, W.REF_ALPHA_FILES["wt2"][1]))
+    assert np.abs(oc - V.mean(axis=0)).max() < 1e-3
+    s = w.scene_scale
+    assert np.allclose(np.diag(w.scene_matrix), [s, s, s, 1.0])
+    assert np.allclose(w.robot_matrix[:3, 3], -s * np.asarray(W.ROB_OMPL_CENTER), rtol=1e-6)
+    p = w.translate_vanilla_pts_to_unit(w.GEO_ROB, oc[None])
+    assert np.abs(p).max() < 1e-12 and w.translate_vanilla_pts_to_unit(w.GEO_ENV, np.ones((2, 3))).shape == (2, 3)

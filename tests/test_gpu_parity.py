@@ -320,3 +320,94 @@ def test_no_cpu_fallback_counters_show_gpu_work(uw_org):
     uw_org.is_valid_states(W.random_states(1024, 1))
     c = uw_org.counters()
     assert c["kernel_launches"] == 1 and c["poses"] == 1024 and c["bv_tests"] >= 1024
+
+
+# ---- A16: intersection mesh -> surface faces + barycentrics -------------------------------------------
+def _world_vertices(q, V):
+    """translate_state_to_transform(q) * v with the engine's / Eigen's operation order (no FMA in numpy)."""
+    w, x, y, z = q[3:7]
+    tx, ty, tz = 2 * x, 2 * y, 2 * z
+    twx, twy, twz = tx * w, ty * w, tz * w
+    txx, txy, txz = tx * x, ty * x, tz * x
+    tyy, tyz, tzz = ty * y, tz * y, tz * z
+    R = [[1 - (tyy + tzz), txy - twz, txz + twy], [txy + twz, 1 - (txx + tzz), tyz - twx],
+         [txz - twy, tyz + twx, 1 - (txx + tyy)]]
+    return np.stack([(R[k][0] * V[:, 0] + R[k][1] * V[:, 1] + R[k][2] * V[:, 2]) + q[k] for k in range(3)], axis=1)
+
+
+@pytest.mark.gpu
+def test_intersecting_to_surface_matches_oracle(uw_org, oracle_mod):
+    g = golden("contacts_org.npz")
+    q = g["q"][0]
+    r = uw_org.intersecting_segments_batch(q, cap=1 << 14)
+    assert r["total"] > 0
+    Ve, Fe = uw_org._geometry(0)
+    Vr, Fr = uw_org._geometry(1)
+    Wr = _world_vertices(q, Vr)
+    # a stand-in for the CGAL boolean result: shrunken copies of the touching robot and environment triangles
+    # (coplanar with, and inside, their source faces) in world space
+    rt = np.unique(r["faces"][:, 1])[:24]
+    et = np.unique(r["faces"][:, 0])[:24]
+    tri = np.concatenate([Wr[Fr[rt]], Ve[Fe[et]]])
+    cen = tri.mean(axis=1, keepdims=True)
+    V = (cen + 0.5 * (tri - cen)).reshape(-1, 3)
+    F = np.arange(len(V), dtype=np.int32).reshape(-1, 3)
+    for which, TV, TF, src in ((1, Wr, Fr, rt), (0, Ve, Fe, et)):
+        fn = uw_org.intersecting_to_robot_surface if which else uw_org.intersecting_to_model_surface
+        f, L = fn(q, True, V, F)
+        of, oL = oracle_mod.surface_map(TV, TF, V, F)
+        assert np.array_equal(f, of) and len(f) >= len(src)
+        assert np.abs(L - oL).max() < 1e-12
+        # every shrunken triangle lands on its source face with barycentrics inside [0, 1]
+        rows = {tuple(x) for x in f.tolist()}
+        assert all(tuple(TF[t].tolist()) in rows for t in src)
+        assert np.allclose(L.sum(axis=1), 1.0, atol=1e-9)
+    # empty mesh, capacity handling and bad indices
+    f, L = uw_org.intersecting_to_robot_surface(q, True, np.zeros((0, 3)), np.zeros((0, 3), np.int32))
+    assert f.shape == (0, 3) and L.shape == (0, 3)
+    with pytest.raises(RuntimeError):
+        uw_org.intersecting_to_robot_surface(q, True, V, F + 10 ** 6)
+
+
+@pytest.mark.gpu
+def test_transit_state_actions_and_sampled_configurations(uw_org, ow_org):
+    g = golden("validity_org_seed0.npz")
+    free = g["q"][g["valid"] == 1]
+    q0 = free[3]
+    # 12 discrete actions (unit_world.cc:267-336): the returned state is valid and moved along one axis only
+    for action in range(12):
+        st, done, prog = uw_org.transit_state(q0, action, 0.05, 0.0125)
+        assert uw_org.is_valid_state(st) and 0.0 <= prog <= 1.0
+        if action < 6:
+            d = st[:3] - q0[:3]
+            assert np.abs(np.delete(d, action // 2)).max() < 1e-12 and d[action // 2] * (1 if action % 2 == 0 else -1) >= 0
+            assert np.abs(st[3:] - q0[3:] / np.linalg.norm(q0[3:])).max() < 1e-12
+        else:
+            assert np.abs(st[:3] - q0[:3]).max() < 1e-12
+        # same walk as transit_state_to on the explicitly built target, checked against the oracle
+        if action == 0:
+            to = q0.copy(); to[3:] /= np.linalg.norm(to[3:]); to[0] += float(np.float32(0.0125))
+            olf, ofh, oisf, oft, ott = ow_org.transit_state_to_with_contact(q0, to, float(np.float32(0.0125)))
+            if oft > 0:
+                assert np.abs(st - olf).max() < 1e-12 and done == oisf
+    st, done, prog = uw_org.transit_state(q0, 12, 0.05, 0.0125)       # invalid action id
+    assert np.array_equal(st, q0) and not done and prog == 0.0
+    bad = g["q"][g["valid"] == 0][0]
+    st, done, prog = uw_org.transit_state(bad, 0, 0.05, 0.0125)       # invalid initial state
+    assert np.array_equal(st, bad) and not done
+    # sample_free_configuration (unit_world.cc:1295-1337): contact construction + validity of the result
+    V0, F0 = uw_org._geometry(0)
+    V1, F1 = uw_org._geometry(1)
+
+    def face(V, F, i):
+        a, b, c = V[F[i]]
+        n = np.cross(b - a, c - a)
+        return (a + b + c) / 3, n / np.linalg.norm(n)
+    ep, en = face(V0, F0, 100)
+    rp, rn = face(V1, F1, 200)
+    q = uw_org.sample_free_configuration(rp, rn, ep, en, 1e-3, max_trials=255, rng=np.random.default_rng(3))
+    from puzzletunneldiscovery_b200.pyosr import _rotate_points
+    p = _rotate_points(q, (rp + 1e-3 * rn)[None])[0]
+    assert np.abs(p - (ep + 1e-3 * en)).max() < 1e-9
+    n_world = _rotate_points(np.concatenate([[0, 0, 0], q[3:]]), rn[None])[0]
+    assert np.abs(n_world + en).max() < 1e-9                            # robot normal opposes the env normal

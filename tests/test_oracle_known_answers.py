@@ -3,6 +3,7 @@ and on the committed golden vectors.  CPU only."""
 import os
 
 import numpy as np
+import pytest
 
 from conftest import ASSETS, golden, make_world
 from puzzletunneldiscovery_b200 import workloads as W
@@ -141,3 +142,22 @@ def test_contacts_golden_and_moller(ow_org, oracle_mod):
             if oracle_mod.sat17(P, Q[F1[j]]) and oracle_mod.contact_multiplicity(P, Q[F1[j]]) > 0:
                 brute.add((i, int(j)))
     assert got == brute
+
+
+def test_surface_map_closed_form(oracle_mod):
+    """A16 (unit_world.cc:1092-1176): coplanar overlapping pair -> one row with the analytic barycentrics;
+    a crossing (non-coplanar) pair and a coplanar but disjoint pair -> no row.  Rows are ordered mesh face
+    outer, surface face inner (Eigen column-major SparseMatrix iteration)."""
+    O = oracle_mod
+    if not O.has_reference_moller():
+        pytest.skip("oracle/_ref/libmoller97d.so not built")
+    TV = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [5, 5, 0], [6, 5, 0], [5, 6, 0]], float)
+    TF = np.array([[0, 1, 2], [3, 4, 5]], np.int32)
+    V = np.array([[0.25, 0.25, 0], [0.5, 0.25, 0], [0.25, 0.5, 0],          # inside surface face 0, coplanar
+                  [0.2, 0.2, -1], [0.2, 0.2, 1], [0.4, 0.4, 1],             # crosses face 0, not coplanar
+                  [5.1, 5.1, 0], [5.5, 5.1, 0], [5.1, 5.5, 0]], float)      # inside surface face 1
+    F = np.array([[6, 7, 8], [3, 4, 5], [0, 1, 2]], np.int32)
+    f, L = O.surface_map(TV, TF, V, F)
+    assert f.tolist() == [[3, 4, 5], [0, 1, 2]]
+    assert np.allclose(L[0:3], [[0.8, 0.1, 0.1], [0.4, 0.5, 0.1], [0.4, 0.1, 0.5]], atol=1e-15)
+    assert np.allclose(L[3:6], [[0.5, 0.25, 0.25], [0.25, 0.5, 0.25], [0.25, 0.25, 0.5]], atol=1e-15)
