@@ -65,6 +65,7 @@ struct Slot {  // one GPU
   int dfs_env_smem = 0, dfs_rob_smem = 0;
   bool dfs_all_smem = false;   // both trees fit into shared memory entirely
   size_t dfs_smem_bytes = 0;
+  int transit_minb = 3;        // tile K2: blocks per SM its registers are capped for (OSR_TRANSIT_BLOCKS)
   int seg_warps = 0;           // K2 on the depth-first traversal: warps per block (0: tile kernel only)
   int seg_env_smem = 0, seg_rob_smem = 0;
   bool seg_all_smem = false;
@@ -200,12 +201,20 @@ int init_slot(osr_world* w, Slot& s, int dev) {
   CU(cudaMemset(s.err, 0, sizeof(int)));
   // persistent grid: as many blocks as fit, on every SM
   CU(cudaFuncSetAttribute(osr::k_is_valid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_PER_BLOCK));
-  CU(cudaFuncSetAttribute(osr::k_transit, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_PER_BLOCK));
+  CU(cudaFuncSetAttribute(osr::k_transit<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_PER_BLOCK));
+  CU(cudaFuncSetAttribute(osr::k_transit<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_PER_BLOCK));
+  CU(cudaFuncSetAttribute(osr::k_transit<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_PER_BLOCK));
+  {
+    const char* e = getenv("OSR_TRANSIT_BLOCKS");
+    s.transit_minb = e ? std::min(4, std::max(2, atoi(e))) : 3;
+  }
   CU(cudaFuncSetAttribute(osr::k_contacts, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_PER_BLOCK));
   int nsm = 0, bpsm = 0, b2 = 0, b3 = 0;
   CU(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev));
   CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bpsm, osr::k_is_valid, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK));
-  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b2, osr::k_transit, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK));
+  if (s.transit_minb == 4) CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b2, osr::k_transit<4>, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK));
+  else if (s.transit_minb == 3) CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b2, osr::k_transit<3>, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK));
+  else CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b2, osr::k_transit<2>, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK));
   CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b3, osr::k_contacts, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK));
   s.grid_valid = nsm * std::max(1, bpsm);
   s.grid_transit = nsm * std::max(1, b2);
@@ -575,8 +584,15 @@ static int launch_transit(osr_world* w, Slot& s, const double* d_from, const dou
   }
   osr::KParams P = w->params(s);
   CU(cudaEventRecord(s.ev0, s.stream));
-  osr::k_transit<<<s.grid_transit, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK, s.stream>>>(
-      P, d_from, d_to, (long long)n, d_vd, (long long)vd_count, vd_scalar, transition_mode, O);
+  if (s.transit_minb == 4)
+    osr::k_transit<4><<<s.grid_transit, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK, s.stream>>>(
+        P, d_from, d_to, (long long)n, d_vd, (long long)vd_count, vd_scalar, transition_mode, O);
+  else if (s.transit_minb == 3)
+    osr::k_transit<3><<<s.grid_transit, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK, s.stream>>>(
+        P, d_from, d_to, (long long)n, d_vd, (long long)vd_count, vd_scalar, transition_mode, O);
+  else
+    osr::k_transit<2><<<s.grid_transit, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK, s.stream>>>(
+        P, d_from, d_to, (long long)n, d_vd, (long long)vd_count, vd_scalar, transition_mode, O);
   CU(cudaGetLastError());
   CU(cudaEventRecord(s.ev1, s.stream));
   w->host_counters.kernel_launches++;

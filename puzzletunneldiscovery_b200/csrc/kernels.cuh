@@ -528,7 +528,8 @@ struct SegOut {
 };
 
 // transition_mode: vd := min(dist/2, vd) (isValidTransition)
-__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
+template <int MINB>  // resident blocks per SM the register allocation is capped for
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB)
     k_transit(KParams P, const double* __restrict__ from, const double* __restrict__ to, long long n,
               const double* __restrict__ vd_arr, long long vd_count, double vd_scalar, int transition_mode,
               SegOut O) {

@@ -411,3 +411,29 @@ def test_transit_state_actions_and_sampled_configurations(uw_org, ow_org):
     assert np.abs(p - (ep + 1e-3 * en)).max() < 1e-9
     n_world = _rotate_points(np.concatenate([[0, 0, 0], q[3:]]), rn[None])[0]
     assert np.abs(n_world + en).max() < 1e-9                            # robot normal opposes the env normal
+
+
+# ---- multi-GPU: one handle, several devices (index-range shards, host gather) ---------------------------
+@pytest.mark.gpu
+def test_two_devices_one_handle_equal_one_device(uw_org):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    from conftest import make_world as mk
+    import functools
+    uw2 = mk(functools.partial(pyosr.UnitWorld, devices=[0, 1]))
+    q = W.random_states(100001, seed=41)
+    v1 = uw_org.is_valid_states(q)
+    assert np.array_equal(uw2.is_valid_states(q), v1)
+    assert np.array_equal(uw2.is_disentangled_states(q), uw_org.is_disentangled_states(q))
+    fr, to = W.touch_rays(q[v1][:64], 1001, seed=42)
+    a = uw_org.transit_states_to_with_contact(fr, to, VD_TOUCH, with_steps=True)
+    b = uw2.transit_states_to_with_contact(fr, to, VD_TOUCH, with_steps=True)
+    assert all(np.array_equal(x, y) for x, y in zip(a, b))
+    hit = a[1][~a[2]][:257]
+    ra = uw_org.intersecting_segments_batch(hit, cap=1 << 16)
+    rb = uw2.intersecting_segments_batch(hit, cap=1 << 16)
+    assert ra["total"] == rb["total"] and np.array_equal(ra["offsets"], rb["offsets"])
+    assert np.array_equal(ra["faces"], rb["faces"]) and np.array_equal(ra["seg"], rb["seg"])
+    from puzzletunneldiscovery_b200 import sharding as S
+    assert np.array_equal(S.sharded_map(uw2.is_valid_states, [q], np.bool_), v1)   # no process group: plain call
