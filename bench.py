@@ -59,6 +59,15 @@ def make_world(cls, **kw):
     return w
 
 
+def host_threads():
+    """Every host thread this process may use.  torchrun exports OMP_NUM_THREADS=1 to its workers; the CPU arm is
+    meant to use the whole box, so the count comes from the affinity mask and is passed to the oracle explicitly."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
 def hbm_peak():
     """Roofline denominator: the driver-measured copy bandwidth, else the profiling guide's fallback."""
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
@@ -158,13 +167,13 @@ def run_reference(args):
     from puzzletunneldiscovery_b200 import workloads as W
     ow = make_world(O.OracleWorld)
     n = args.states
-    cores = O.lib().orc_max_threads()
+    cores = host_threads()
     qs = [W.random_states(n, batch_seed(0, b)) for b in range(min(NBATCH, args.steps + args.warmup))]
     for i in range(args.warmup):
-        ow.is_valid_states(qs[i % len(qs)][: n // 8])
+        ow.is_valid_states(qs[i % len(qs)][: n // 8], threads=cores)
     t0 = time.perf_counter()
     for i in range(args.steps):
-        ow.is_valid_states(qs[i % len(qs)])
+        ow.is_valid_states(qs[i % len(qs)], threads=cores)
     dt = time.perf_counter() - t0
     val = n * args.steps / dt
     sample = "%d steps x %d states (full batches), oracle port, %d OpenMP threads" % (args.steps, n, cores)
@@ -315,11 +324,11 @@ def run_ours(args):
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         from oracle import oracle as O
         ow = make_world(O.OracleWorld)
-        cores = O.lib().orc_max_threads()
+        cores = host_threads()
         qs = host_q[0].numpy()
-        ow.is_valid_states(qs[:4096])
+        ow.is_valid_states(qs[:4096], threads=cores)
         tc = time.perf_counter()
-        vo = ow.is_valid_states(qs)
+        vo = ow.is_valid_states(qs, threads=cores)
         dtc = time.perf_counter() - tc
         cpu = {"value": n / dtc, "unit": UNIT, "cores": cores, "kind": "port",
                "sample": "one full batch of %d states (seed %d), oracle port, %d OpenMP threads, %.1f s" %

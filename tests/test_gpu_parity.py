@@ -420,6 +420,7 @@ def test_two_devices_one_handle_equal_one_device(uw_org):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs")
     from conftest import make_world as mk
+    from puzzletunneldiscovery_b200 import pyosr
     import functools
     uw2 = mk(functools.partial(pyosr.UnitWorld, devices=[0, 1]))
     q = W.random_states(100001, seed=41)
