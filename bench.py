@@ -276,6 +276,24 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_value = world * n * K / float(te.item())
+    # the same call with float32 host samples (what the reference's Python callers hold; widened on the device)
+    host_q32 = [q.to(torch.float32).pin_memory() for q in host_q[:4]]
+
+    def e2e_call32(b):
+        check(L.osr_is_valid_states_f32(h, C.cast(host_q32[b].data_ptr(), C.POINTER(C.c_float)), n,
+                                        C.cast(host_out.data_ptr(), C.POINTER(C.c_uint8))))
+    for i in range(Wm):
+        e2e_call32(i % 4)
+    barrier()
+    te0 = time.perf_counter()
+    for i in range(K):
+        e2e_call32((Wm + i) % 4)
+    barrier()
+    te32 = torch.tensor([time.perf_counter() - te0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(te32, op=dist.ReduceOp.MAX)
+    e2e32_value = world * n * K / float(te32.item())
+    e2e_call(0)
     valid_frac = float(host_out.numpy().mean())
     clocks = sampler.stop(t0, t1) if sampler else None
 
@@ -354,6 +372,8 @@ def run_ours(args):
                              "fraction is small by construction -- see DESIGN.md"},
         "cpu_baseline": cpu,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n * 56, "d2h_bytes_per_step": n},
+        "e2e_f32_states": {"value": e2e32_value, "unit": UNIT, "h2d_bytes_per_step": n * 28, "d2h_bytes_per_step": n,
+                           "note": "osr_is_valid_states_f32: float32 host samples, exact widening on the device"},
         "gpu_launches": int(launches),
         "clocks": clocks,
         "valid_fraction": valid_frac,

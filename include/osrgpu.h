@@ -90,6 +90,10 @@ int osr_get_counters(osr_world* w, osr_counters* out, int reset);
 
 /* UnitWorld::isValid per row (unit_world.cc:215-247): out[i]=1 iff state i is collision free */
 int osr_is_valid_states(osr_world* w, const double* q, int64_t n, uint8_t* out);
+/* Same labels for float32 states: the reference's callers hold float32 samples (src/GP/pipeline/uw_random.py:15-17)
+ * that pybind11 widens to float64 on the host (module.cc:138); here the widening -- exact -- happens on the device
+ * and the upload is half the size. */
+int osr_is_valid_states_f32(osr_world* w, const float* q, int64_t n, uint8_t* out);
 /* UnitWorld::isDisentangled per row (unit_world.cc:249-264) */
 int osr_is_disentangled_states(osr_world* w, const double* q, int64_t n, uint8_t* out);
 

@@ -45,6 +45,7 @@ SIGNATURES = {
     "osr_get_bvh_nodes": (C.c_int, [C.c_void_p, C.c_int, c_fp]),
     "osr_get_counters": (C.c_int, [C.c_void_p, C.POINTER(Counters), C.c_int]),
     "osr_is_valid_states": (C.c_int, [C.c_void_p, c_dp, C.c_int64, c_u8p]),
+    "osr_is_valid_states_f32": (C.c_int, [C.c_void_p, c_fp, C.c_int64, c_u8p]),
     "osr_is_disentangled_states": (C.c_int, [C.c_void_p, c_dp, C.c_int64, c_u8p]),
     "osr_transit_states_to_with_contact": (C.c_int, [C.c_void_p, c_dp, c_dp, C.c_int64, c_dp, C.c_int64, c_dp, c_dp,
                                                      c_u8p, c_dp, c_dp, c_i64p]),

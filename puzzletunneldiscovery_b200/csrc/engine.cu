@@ -10,6 +10,7 @@
 #include <memory>
 #include <mutex>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 #include "../../include/osrgpu.h"
@@ -244,7 +245,8 @@ int init_slot(osr_world* w, Slot& s, int dev) {
         s.dfs_all_smem = se == ne && sr == nr;
 #define OSR_DFS_ATTR(...)                                                                                         \
   CU(cudaFuncSetAttribute(osr::k_valid_dfs<__VA_ARGS__, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem)); \
-  CU(cudaFuncSetAttribute(osr::k_valid_dfs<__VA_ARGS__, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem))
+  CU(cudaFuncSetAttribute(osr::k_valid_dfs<__VA_ARGS__, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));  \
+  CU(cudaFuncSetAttribute(osr::k_valid_dfs<__VA_ARGS__, true, float>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem))
         OSR_DFS_ATTR(uint32_t, 32, true);
         OSR_DFS_ATTR(uint32_t, 32, false);
         OSR_DFS_ATTR(uint32_t, 64, false);
@@ -318,17 +320,17 @@ int check_device_error(osr_world* w, Slot& s) {
 
 namespace {
 // the four tree-size variants of K1 x {resident input, stream-fed input}
-template <bool FEED>
-void launch_dfs_variant(const Slot& s, const osr::DfsParams& D, const double* d_q, long long n, uint8_t* d_out,
-                               cudaStream_t st) {
+template <bool FEED, typename T>
+void launch_dfs_variant(const Slot& s, const osr::DfsParams& D, const T* d_q, long long n, uint8_t* d_out,
+                        cudaStream_t st) {
   if (s.dfs_variant == 0 && s.dfs_all_smem)
-    osr::k_valid_dfs<uint32_t, 32, true, FEED><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, st>>>(D, d_q, n, d_out);
+    osr::k_valid_dfs<uint32_t, 32, true, FEED, T><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, st>>>(D, d_q, n, d_out);
   else if (s.dfs_variant == 0)
-    osr::k_valid_dfs<uint32_t, 32, false, FEED><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, st>>>(D, d_q, n, d_out);
+    osr::k_valid_dfs<uint32_t, 32, false, FEED, T><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, st>>>(D, d_q, n, d_out);
   else if (s.dfs_variant == 1)
-    osr::k_valid_dfs<uint32_t, 64, false, FEED><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, st>>>(D, d_q, n, d_out);
+    osr::k_valid_dfs<uint32_t, 64, false, FEED, T><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, st>>>(D, d_q, n, d_out);
   else
-    osr::k_valid_dfs<unsigned long long, 48, false, FEED><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, st>>>(D, d_q, n, d_out);
+    osr::k_valid_dfs<unsigned long long, 48, false, FEED, T><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, st>>>(D, d_q, n, d_out);
 }
 
 }  // namespace
@@ -534,15 +536,15 @@ static int launch_valid(osr_world* w, Slot& s, const double* d_q, int64_t n, uin
     if (lane != 0) {
       if (ready) {
         CU(cudaEventRecord(s.ev0, st));
-        launch_dfs_variant<true>(s, D, d_q, (long long)n, d_out, st);
-      } else launch_dfs_variant<false>(s, D, d_q, (long long)n, d_out, st);
+        launch_dfs_variant<true, double>(s, D, d_q, (long long)n, d_out, st);
+      } else launch_dfs_variant<false, double>(s, D, d_q, (long long)n, d_out, st);
       CU(cudaGetLastError());
       if (ready) CU(cudaEventRecord(s.ev1, st));
       w->host_counters.kernel_launches++;
       return OSR_OK;
     }
     CU(cudaEventRecord(s.ev0, s.stream));
-    launch_dfs_variant<false>(s, D, d_q, (long long)n, d_out, s.stream);
+    launch_dfs_variant<false, double>(s, D, d_q, (long long)n, d_out, s.stream);
     CU(cudaGetLastError());
     CU(cudaEventRecord(s.ev1, s.stream));
     w->host_counters.kernel_launches++;
@@ -613,7 +615,27 @@ static int64_t host_chunk_states() {
   return v;
 }
 
-int osr_is_valid_states(osr_world* w, const double* q, int64_t n, uint8_t* out) {
+}  // extern "C" (templates cannot have C linkage)
+
+// stream-fed K1 launch on the main stream (work word [2]); T = double or float states
+template <typename T>
+static int launch_valid_feed(osr_world* w, Slot& s, const T* d_q, int64_t n, uint8_t* d_out, const long long* ready) {
+  if (n > 0x7fffffffLL) return fail(OSR_EINVAL, "more than 2^31-1 states in one launch");
+  unsigned long long* work = s.work + 2;
+  CU(cudaMemsetAsync(work, 0, sizeof(unsigned long long), s.stream));
+  osr::DfsParams D = dfs_params(w, s);
+  D.work_counter = work;
+  D.ready = ready;
+  CU(cudaEventRecord(s.ev0, s.stream));
+  launch_dfs_variant<true, T>(s, D, d_q, (long long)n, d_out, s.stream);
+  CU(cudaGetLastError());
+  CU(cudaEventRecord(s.ev1, s.stream));
+  w->host_counters.kernel_launches++;
+  return OSR_OK;
+}
+
+template <typename T>
+static int valid_states_host(osr_world* w, const T* q, int64_t n, uint8_t* out) {
   int rc = check_ready(w);
   if (rc) return rc;
   if (n < 0 || (n > 0 && (!q || !out))) return fail(OSR_EINVAL, "bad arguments");
@@ -628,10 +650,13 @@ int osr_is_valid_states(osr_world* w, const double* q, int64_t n, uint8_t* out) 
     shard(n, parts, i, lo, hi);
     if (hi == lo) continue;
     CU(cudaSetDevice(s.dev));
-    CU(s.in0.need((size_t)(hi - lo) * 56));
+    CU(s.in0.need((size_t)(hi - lo) * 7 * sizeof(T)));
     CU(s.out[0].need((size_t)(hi - lo)));
     int64_t nchunks = (hi - lo + chunk - 1) / chunk;
-    if (nchunks > 1 && s.dfs_variant >= 0 && !w->force_tile_kernel && !no_feed) {
+    const bool dfs_ok = s.dfs_variant >= 0 && !w->force_tile_kernel;
+    if (!dfs_ok && !std::is_same<T, double>::value)
+      return fail(OSR_EINVAL, "float32 states need the depth-first validity kernel (trees too deep for it)");
+    if (dfs_ok && ((nchunks > 1 && !no_feed) || !std::is_same<T, double>::value)) {
       // Stream-fed launch: ONE persistent kernel over the whole range.  The upload is queued chunk by chunk on
       // the copy stream, each chunk followed by an 8-byte copy that advances the device word `ready`; the
       // kernel's warps pull states in index order and wait on that word, so compute runs under the PCIe
@@ -651,15 +676,16 @@ int osr_is_valid_states(osr_world* w, const double* q, int64_t n, uint8_t* out) 
       for (int64_t c0 = 0; c0 < m; c0 += ck, c++) {
         int64_t len = std::min(ck, m - c0);
         if (!s.feed_ev[c]) CU(cudaEventCreateWithFlags(&s.feed_ev[c], cudaEventDisableTiming));
-        CU(cudaMemcpyAsync((double*)s.in0.p + 7 * c0, q + 7 * (lo + c0), (size_t)len * 56, cudaMemcpyHostToDevice, s.stream2));
+        CU(cudaMemcpyAsync((T*)s.in0.p + 7 * c0, q + 7 * (lo + c0), (size_t)len * 7 * sizeof(T), cudaMemcpyHostToDevice, s.stream2));
         CU(cudaEventRecord(s.feed_ev[c], s.stream2));
         CU(cudaStreamWaitEvent(s.stream3, s.feed_ev[c], 0));
         s.h_ready[c] = c0 + len;
         if (!wv || wv(s.stream3, (unsigned long long)(uintptr_t)s.ready, (unsigned long long)(c0 + len), 0) != 0)
           CU(cudaMemcpyAsync(s.ready, s.h_ready + c, sizeof(long long), cudaMemcpyHostToDevice, s.stream3));
       }
-      CU(cudaStreamWaitEvent(s.stream, s.feed_ev[0], 0));
-      rc = launch_valid(w, s, (const double*)s.in0.p, m, (uint8_t*)s.out[0].p, 1, s.ready);
+      static const bool wait_all = getenv("OSR_FEED_WAIT_ALL") != nullptr;  // probe: kernel starts after the last chunk
+      CU(cudaStreamWaitEvent(s.stream, s.feed_ev[wait_all ? c - 1 : 0], 0));
+      rc = launch_valid_feed<T>(w, s, (const T*)s.in0.p, m, (uint8_t*)s.out[0].p, s.ready);
       if (rc) return rc;
       CU(cudaMemcpyAsync(out + lo, s.out[0].p, (size_t)m, cudaMemcpyDeviceToHost, s.stream));
       CU(cudaEventRecord(s.evq, s.stream3));
@@ -674,9 +700,9 @@ int osr_is_valid_states(osr_world* w, const double* q, int64_t n, uint8_t* out) 
       int64_t c0 = c * chunk, m = std::min(chunk, hi - lo - c0);
       int lane = nchunks == 1 ? 1 : 1 + (int)(c & 1);
       cudaStream_t st = lane == 2 ? s.stream2 : s.stream;
-      double* d_in = (double*)s.in0.p + 7 * c0;
+      double* d_in = (double*)s.in0.p + 7 * c0;  // (T == double here: float32 input always takes the fed path)
       uint8_t* d_out = (uint8_t*)s.out[0].p + c0;
-      CU(cudaMemcpyAsync(d_in, q + 7 * (lo + c0), (size_t)m * 56, cudaMemcpyHostToDevice, st));
+      CU(cudaMemcpyAsync(d_in, (const void*)(q + 7 * (lo + c0)), (size_t)m * 56, cudaMemcpyHostToDevice, st));
       rc = launch_valid(w, s, d_in, m, d_out, lane);
       if (rc) return rc;
       CU(cudaMemcpyAsync(out + lo + c0, d_out, (size_t)m, cudaMemcpyDeviceToHost, st));
@@ -693,6 +719,15 @@ int osr_is_valid_states(osr_world* w, const double* q, int64_t n, uint8_t* out) 
     if (rc) return rc;
   }
   return OSR_OK;
+}
+
+extern "C" {
+
+int osr_is_valid_states(osr_world* w, const double* q, int64_t n, uint8_t* out) {
+  return valid_states_host<double>(w, q, n, out);
+}
+int osr_is_valid_states_f32(osr_world* w, const float* q, int64_t n, uint8_t* out) {
+  return valid_states_host<float>(w, q, n, out);
 }
 
 int osr_is_valid_states_device(osr_world* w, const double* d_q, int64_t n, uint8_t* d_out) {

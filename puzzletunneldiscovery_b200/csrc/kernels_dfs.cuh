@@ -40,19 +40,16 @@ struct DfsParams {
 };
 
 // Wait (one lane polls, with back-off) until at least `need` states are resident; returns the count observed.
-// Gives up after ~4 s of GPU time: raises the error flag and returns a short count instead of hanging the device
-// if the copies never arrive.
-__device__ __noinline__ long long wait_for_states(const long long* ready, int* error_flag, long long need, int lane) {
+// Gives up after ~2^22 polls (seconds): raises the error flag and returns a short count instead of hanging the
+// device if the copies never arrive.  Kept tiny and inline: a call in K1's loop costs registers on the hot path.
+__device__ __forceinline__ long long wait_for_states(const long long* ready, int* error_flag, long long need, int lane) {
   long long seen = 0;
   if (lane == 0) {
-    unsigned long long t0, t1;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-    while (true) {
+    for (int spins = 0;; spins++) {
       asm volatile("ld.acquire.sys.global.s64 %0, [%1];" : "=l"(seen) : "l"(ready) : "memory");
       if (seen >= need) break;
-      __nanosleep(500);
-      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-      if (t1 - t0 > 4000000000ull) { atomicExch(error_flag, 2); break; }
+      if (spins > (1 << 22)) { atomicExch(error_flag, 2); break; }
+      __nanosleep(1000);
     }
   }
   return __shfl_sync(0xffffffffu, seen, 0);
@@ -136,14 +133,18 @@ __device__ __forceinline__ void load_pair_exact_r(const double* __restrict__ Pt,
 
 // ---- pose sources -----------------------------------------------------------------------------------
 // A source hands out poses by an integer tag and can rebuild the exact fp64 transform of a tag.
+// T = double, or float for callers whose samples are float32 (the reference's own sampler,
+// src/GP/pipeline/uw_random.py:8-17, makes float32 arrays that pybind11 widens on the host: widening here is
+// the same exact conversion and halves the PCIe traffic of a host call).
+template <typename T>
 struct ValiditySource {
-  const double* q;
+  const T* q;
   long long n;
   uint8_t* out;
   __device__ __forceinline__ void exact_pose(const DfsParams& P, int tag, Rigid& rel, double* quat) const {
     double s[7];
 #pragma unroll
-    for (int k = 0; k < 7; k++) s[k] = __ldg(q + 7 * (long long)tag + k);
+    for (int k = 0; k < 7; k++) s[k] = (double)__ldg(q + 7 * (long long)tag + k);
     Rigid rob;
     state_to_rigid(s, rob);
     relative_rigid(P.env_tf, rob, rel);
@@ -168,9 +169,9 @@ constexpr unsigned F_PR = 8u;   // ... in the exact-recheck queue
 // The loop body is kept small on purpose: its instruction working set (box test + stack step + the two
 // drains) has to stay inside the 32 KB L1.5 instruction cache shared by the 12 warps.
 // ---------------------------------------------------------------------------------------------------
-template <typename E, int DEPTH, bool ALL_SMEM, bool FEED>
+template <typename E, int DEPTH, bool ALL_SMEM, bool FEED, typename T = double>
 __global__ void __launch_bounds__(DFS_THREADS, 1)
-    k_valid_dfs(DfsParams P, const double* __restrict__ q, long long n, uint8_t* __restrict__ out) {
+    k_valid_dfs(DfsParams P, const T* __restrict__ q, long long n, uint8_t* __restrict__ out) {
   typedef TaskCodec<E> TC;
   typedef DfsWarpMem<E, DEPTH> WM;
   extern __shared__ uint4 dfs_smem[];
@@ -183,7 +184,7 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
 
   const int lane = threadIdx.x & 31;
   const unsigned ltmask = (1u << lane) - 1u;
-  ValiditySource src = {q, n, out};
+  ValiditySource<T> src = {q, n, out};
   const bool root_leafpair = ((int)sm_env[0].w < 0) && ((int)sm_rob[0].w < 0);  // two single-triangle meshes
 
   // lane state

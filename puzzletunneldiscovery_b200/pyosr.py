@@ -312,6 +312,11 @@ class UnitWorld:
 
     # ---- validity (module.cc:138-139) ------------------------------------------------------------
     def is_valid_states(self, qs):
+        if isinstance(qs, np.ndarray) and qs.dtype == np.float32 and qs.ndim == 2 and qs.shape[1] == 7:
+            q = np.ascontiguousarray(qs)      # float32 samples go up as they are and are widened on the device
+            out = np.empty(len(q), np.uint8)
+            check(self._L.osr_is_valid_states_f32(self._h, _p(q, c_fp), len(q), _p(out, c_u8p)))
+            return out.astype(bool)
         q = _states(qs)
         out = np.empty(len(q), np.uint8)
         check(self._L.osr_is_valid_states(self._h, _p(q, c_dp), len(q), _p(out, c_u8p)))

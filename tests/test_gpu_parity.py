@@ -438,3 +438,13 @@ def test_two_devices_one_handle_equal_one_device(uw_org):
     assert np.array_equal(ra["faces"], rb["faces"]) and np.array_equal(ra["seg"], rb["seg"])
     from puzzletunneldiscovery_b200 import sharding as S
     assert np.array_equal(S.sharded_map(uw2.is_valid_states, [q], np.bool_), v1)   # no process group: plain call
+
+
+@pytest.mark.gpu
+def test_float32_states_give_the_same_labels(uw_org, uw_wt2):
+    """osr_is_valid_states_f32: float32 samples (uw_random.py:15-17) widened on the device -- exact, so the
+    labels equal those of the float64 call on the widened array; ragged sizes cross the upload chunks."""
+    for uw, n in ((uw_org, 200003), (uw_wt2, 70001), (uw_org, 5), (uw_org, 65536)):
+        q32 = W.random_states(n, seed=n % 97).astype(np.float32)
+        assert np.array_equal(uw.is_valid_states(q32), uw.is_valid_states(q32.astype(np.float64)))
+    assert uw_org.is_valid_states(np.zeros((0, 7), np.float32)).shape == (0,)
