@@ -561,22 +561,21 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB)
       const double inv_dist = 1.0 / dist;
       double carry = 0.0;       // delta of the last step of the previous tile (0 before the first)
       double prev_tau = 0.0;    // tau of that step
-      bool first = true;
       long long k0 = 0;         // steps completed before this tile
       bool done = false;
       while (!done) {
-        // step deltas of this tile: lane j takes the (j+1)-th value after `carry`
+        // step deltas of this tile: lane j takes the (j+1)-th value after `carry`.  The chain of fp64 adds is
+        // inherently serial (the reference's running sum, rounding included), so all lanes run it; it is kept to
+        // add / compare / select per step: with carry = 0 the first value is 0 + vd = vd exactly, and since the
+        // sequence increases strictly, "every delta up to mine is <= dist" is just mine <= dist.
         double d = carry, mine = 0.0;
-        bool mine_ok = false, ok = true;
-#pragma unroll 1
+#pragma unroll
         for (int j = 0; j < 32; j++) {
-          if (first && j == 0) d = vd;
-          else if (d < dist) d = fmin(dist, d + vd);
-          else { d = d + vd; }
-          ok = ok && (d <= dist);
-          if (j == lane) { mine = d; mine_ok = ok; }
+          const double t = d + vd;
+          d = (d < dist) ? fmin(dist, t) : t;
+          if (j == lane) mine = d;
         }
-        first = false;
+        const bool mine_ok = mine <= dist;
         carry = d;  // delta of slot 31 (only used when all 32 slots were valid)
         double tau = mine * inv_dist;
         if (mine_ok) {
