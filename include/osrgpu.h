@@ -155,6 +155,13 @@ int osr_intersecting_to_surface(osr_world* w, int which, const double* q, const 
                                 const int32_t* F, int64_t nF, int64_t cap, int32_t* out_faces,
                                 double* out_bary, int64_t* total);
 
+/* k nearest states under osr::distance (lib/osr/osr_state.cc:130-154) inside windows of `window` consecutive
+ * indices (a positive multiple of 256; the last window may be short), the query itself excluded: the k-NN edge
+ * generator of the RDT-forest edge-validation workload.  out_idx[n][k] = global indices ordered by
+ * (distance, index), -1 where a window holds fewer than k other states; out_dist[n][k] optional.  1 <= k <= 16. */
+int osr_knn_windowed(osr_world* w, const double* q, int64_t n, int k, int64_t window, int32_t* out_idx,
+                     double* out_dist);
+
 /* Device-resident variants (pointers on the handle's first device).  Launch only; the caller
  * synchronises with osr_sync() (or its own stream wait on osr_stream()). */
 int osr_is_valid_states_device(osr_world* w, const double* d_q, int64_t n, uint8_t* d_out);

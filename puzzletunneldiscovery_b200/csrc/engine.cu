@@ -19,6 +19,7 @@
 #include "kernels_dfs.cuh"
 #include "kernels_seg.cuh"
 #include "kernels_surface.cuh"
+#include "kernels_knn.cuh"
 
 namespace {
 
@@ -1218,6 +1219,34 @@ int osr_intersecting_to_surface(osr_world* w, int which, const double* q, const 
   CU(cudaStreamSynchronize(s.stream));
   for (long long r = 0; r < rows; r++)  // retF.row = targetF.row(target_fi)
     for (int k = 0; k < 3; k++) out_faces[3 * r + k] = tm.F[(size_t)3 * face[(size_t)r] + k];
+  return OSR_OK;
+}
+
+// ---- windowed k-NN under the state metric (config 3 edge generation) ------------------------------
+int osr_knn_windowed(osr_world* w, const double* q, int64_t n, int k, int64_t window, int32_t* out_idx,
+                     double* out_dist) {
+  int rc = check_ready(w);
+  if (rc) return rc;
+  if (n < 0 || (n > 0 && (!q || !out_idx)) || k <= 0 || k > osr::KNN_KMAX || window <= 0 ||
+      window % osr::KNN_TILE != 0 || n > 0x7fffffffLL)
+    return fail(OSR_EINVAL, "bad arguments (1 <= k <= 16, window a positive multiple of 256)");
+  if (n == 0) return OSR_OK;
+  std::lock_guard<std::mutex> lk(w->mu);
+  Slot& s = w->slots[0];
+  CU(cudaSetDevice(s.dev));
+  CU(s.in0.need((size_t)n * 56));
+  CU(s.faces.need((size_t)n * k * 4));
+  if (out_dist) CU(s.seg.need((size_t)n * k * 8));
+  CU(cudaMemcpyAsync(s.in0.p, q, (size_t)n * 56, cudaMemcpyHostToDevice, s.stream));
+  CU(cudaEventRecord(s.ev0, s.stream));
+  osr::k_knn_window<<<(unsigned)((n + osr::KNN_TILE - 1) / osr::KNN_TILE), osr::KNN_TILE, 0, s.stream>>>(
+      (const double*)s.in0.p, (long long)n, k, (long long)window, (int*)s.faces.p, out_dist ? (double*)s.seg.p : nullptr);
+  CU(cudaGetLastError());
+  CU(cudaEventRecord(s.ev1, s.stream));
+  w->host_counters.kernel_launches++;
+  CU(cudaMemcpyAsync(out_idx, s.faces.p, (size_t)n * k * 4, cudaMemcpyDeviceToHost, s.stream));
+  if (out_dist) CU(cudaMemcpyAsync(out_dist, s.seg.p, (size_t)n * k * 8, cudaMemcpyDeviceToHost, s.stream));
+  CU(cudaStreamSynchronize(s.stream));
   return OSR_OK;
 }
 

@@ -557,6 +557,25 @@ class UnitWorld:
             if max_trials >= 0 and done > max_trials:
                 return qs[-1]
 
+    # ---- k-NN edge generation -----------------------------------------
+    def knn_windowed(self, qs, k=8, window=4096, with_distance=False):
+        """k nearest states under pyosr.distance inside windows of consecutive indices -> int32[N,k]."""
+        q = _states(qs)
+        idx = np.empty((len(q), k), np.int32)
+        dist = np.empty((len(q), k)) if with_distance else None
+        check(self._L.osr_knn_windowed(self._h, _p(q, c_dp), len(q), int(k), int(window), _p(idx, c_i32p),
+                                       _p(dist, c_dp)))
+        return (idx, dist) if with_distance else idx
+
+    def knn_edges(self, qs, k=8, window=4096):
+        """(from, to) state arrays of the k-NN edges, milestone-major like workloads.knn_edges."""
+        q = _states(qs)
+        idx = self.knn_windowed(q, k, window)
+        src = np.repeat(np.arange(len(q)), k)
+        dst = idx.reshape(-1)
+        keep = dst >= 0
+        return np.ascontiguousarray(q[src[keep]]), np.ascontiguousarray(q[dst[keep]])
+
     # ---- surface mapping (module.cc: intersecting_to_robot_surface / intersecting_to_model_surface) ----
     def _to_surface(self, which, q, q_is_unit, V, F):
         """unit_world.cc:928-957 + 1092-1176 -> (faces int32[K,3], barycentrics float64[3K,3])."""

@@ -82,9 +82,13 @@ def leg_edges(O, scale):
     nm = int((1 << 16) * scale)
     q = W.random_states(2 * nm, seed=2)
     q = q[uw.is_valid_states(q)][:nm]
+    uw.knn_edges(q[:4096], k=8, window=4096)
     t = time.perf_counter()
-    fr, to = W.knn_edges(q, k=8, window=4096)
+    fr, to = uw.knn_edges(q, k=8, window=4096)      # K6: windowed k-NN under osr::distance on the GPU
     t_knn = time.perf_counter() - t
+    hfr, hto = W.knn_edges(q[:4096], k=8, window=4096)   # host restatement on the first window
+    same_edges = {(a.tobytes(), b.tobytes()) for a, b in zip(hfr, hto)} == \
+        {(a.tobytes(), b.tobytes()) for a, b in zip(fr[:8 * 4096], to[:8 * 4096])}
     vd = 1.51641e-5
     res, dt = timed(lambda: uw.is_valid_transitions(fr, to, vd))
     m = 256
@@ -94,7 +98,8 @@ def leg_edges(O, scale):
     c = uw.counters(reset=True)
     return {"leg": "edges", "geometry": "G-org", "milestones": len(q), "edges": len(fr), "verify_delta": vd,
             "edges_per_s": len(fr) / dt, "seconds": dt, "valid_edge_fraction": float(res.mean()),
-            "host_knn_seconds": t_knn, "oracle_prefix": m,
+            "gpu_knn_seconds": t_knn, "knn_edges_per_s": len(fr) / t_knn,
+            "knn_first_window_equals_host_restatement": bool(same_edges), "oracle_prefix": m,
             "labels_equal_oracle_on_prefix": bool(np.array_equal(res[:m], ores.astype(bool))),
             "cpu_port": {"edges_per_s": m / dtc, "validity_checks_per_s": float(ocnt[:, 0].sum()) / dtc,
                          "threads": O.lib().orc_max_threads()}}

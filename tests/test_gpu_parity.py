@@ -448,3 +448,28 @@ def test_float32_states_give_the_same_labels(uw_org, uw_wt2):
         q32 = W.random_states(n, seed=n % 97).astype(np.float32)
         assert np.array_equal(uw.is_valid_states(q32), uw.is_valid_states(q32.astype(np.float64)))
     assert uw_org.is_valid_states(np.zeros((0, 7), np.float32)).shape == (0,)
+
+
+@pytest.mark.gpu
+def test_knn_windowed_matches_host_restatement(uw_org):
+    """K6: neighbour sets equal the numpy restatement (workloads.state_distance, osr_state.cc:130-154) per
+    milestone; distances ascending; ragged last window; a window with fewer than k other states pads with -1."""
+    q = W.random_states(2 * 512 + 77, seed=51)
+    idx, dist = uw_org.knn_windowed(q, k=8, window=512, with_distance=True)
+    assert idx.shape == (len(q), 8) and (np.diff(dist, axis=1) >= 0).all()
+    for w0 in range(0, len(q), 512):
+        blk = q[w0:w0 + 512]
+        m = len(blk)
+        for i in range(0, m, 37):
+            d = W.state_distance(np.repeat(blk[i:i + 1], m, axis=0), blk)
+            d[i] = np.inf
+            want = set((np.argsort(d, kind="stable")[:8] + w0).tolist())
+            assert set(idx[w0 + i].tolist()) == want
+            assert np.abs(np.sort(d)[:8] - dist[w0 + i]).max() < 1e-12
+    assert (idx >= 0).all() and (idx != np.arange(len(q))[:, None]).all()
+    small = uw_org.knn_windowed(q[:5], k=8, window=256)
+    assert (small[:, :4] >= 0).all() and (small[:, 4:] == -1).all()
+    fr, to = uw_org.knn_edges(q[:5], k=8, window=256)
+    assert fr.shape == (20, 7) and to.shape == (20, 7)
+    with pytest.raises(RuntimeError):
+        uw_org.knn_windowed(q, k=17, window=512)
