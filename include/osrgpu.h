@@ -162,6 +162,14 @@ int osr_intersecting_to_surface(osr_world* w, int which, const double* q, const 
 int osr_knn_windowed(osr_world* w, const double* q, int64_t n, int k, int64_t window, int32_t* out_idx,
                      double* out_dist);
 
+/* Renderer::renderBarycentric (lib/osr/osr_render.cc:590-759, shaders lib/osr/shader/bary.{vert,geom,frag}) as a
+ * headless rasteriser: primitive p has three vertices with uv[3p+v][2] (UV corners of its surface face),
+ * bary[3p+v][3] and weight[3p+v]; vertex v is drawn at sum_k uv[3p+k]*bary[3p+v][k] in a res_x x res_y chart,
+ * fragments whose interpolated barycentrics leave [0,1] are discarded, the rest ADD their weight.  out[res_y][res_x]
+ * (row y bottom-up as glReadPixels returns it) is cleared by the call. */
+int osr_rasterize_barycentric(osr_world* w, const float* uv, const float* bary, const float* weight, int64_t nprim,
+                              int res_x, int res_y, float* out);
+
 /* Device-resident variants (pointers on the handle's first device).  Launch only; the caller
  * synchronises with osr_sync() (or its own stream wait on osr_stream()). */
 int osr_is_valid_states_device(osr_world* w, const double* d_q, int64_t n, uint8_t* d_out);

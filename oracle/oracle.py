@@ -277,3 +277,50 @@ class OracleWorld:
         m = int(off[-1])
         r = (off, segs[:m].copy(), faces[:m].copy(), cop[:m].copy(), int(total))
         return r + (cnt,) if counters else r
+
+
+def rasterize_barycentric(uv, bary, weight, res_x, res_y):
+    """CPU restatement of the reference's barycentric chart splat (lib/osr/shader/bary.{vert,geom,frag} +
+    lib/osr/osr_render.cc:590-759): vertex positions blended in float32 like the geometry shader, coverage at
+    pixel centres with the top-left rule, linear attribute interpolation, discard outside [0,1], additive
+    blending.  PARITY UNPINNED: the GL path cannot run on this box (no graphics stack); this states the
+    rasterisation rules the engine's kernel (csrc/kernels_raster.cuh) follows, pixel loops in numpy."""
+    uv = np.asarray(uv, np.float32).reshape(-1, 3, 2)
+    bary = np.asarray(bary, np.float32).reshape(-1, 3, 3)
+    weight = np.asarray(weight, np.float32).reshape(-1, 3)
+    out = np.zeros((res_y, res_x), np.float64)
+
+    def top_left(ex, ey):
+        return ey < 0.0 or (ey == 0.0 and ex < 0.0)
+    for p in range(len(uv)):
+        u, b, wt = uv[p], bary[p], weight[p]
+        X = np.zeros(3); Y = np.zeros(3)
+        for v in range(3):
+            bx = np.float32(u[0, 0] * b[v, 0]); bx = np.float32(bx + np.float32(u[1, 0] * b[v, 1]))
+            bx = np.float32(bx + np.float32(u[2, 0] * b[v, 2]))
+            by = np.float32(u[0, 1] * b[v, 0]); by = np.float32(by + np.float32(u[1, 1] * b[v, 1]))
+            by = np.float32(by + np.float32(u[2, 1] * b[v, 2]))
+            X[v] = float(bx) * res_x; Y[v] = float(by) * res_y
+        area = (X[1] - X[0]) * (Y[2] - Y[0]) - (X[2] - X[0]) * (Y[1] - Y[0])
+        if not np.isfinite(area) or area == 0.0:
+            continue
+        i1, i2 = (1, 2) if area > 0 else (2, 1)
+        area = abs(area)
+        x0, y0, x1, y1, x2, y2 = X[0], Y[0], X[i1], Y[i1], X[i2], Y[i2]
+        tl = (top_left(x2 - x1, y2 - y1), top_left(x0 - x2, y0 - y2), top_left(x1 - x0, y1 - y0))
+        px0 = int(max(np.floor(min(x0, x1, x2)), 0)); px1 = int(min(np.ceil(max(x0, x1, x2)), res_x))
+        py0 = int(max(np.floor(min(y0, y1, y2)), 0)); py1 = int(min(np.ceil(max(y0, y1, y2)), res_y))
+        if px1 <= px0 or py1 <= py0:
+            continue
+        cx, cy = np.meshgrid(np.arange(px0, px1) + 0.5, np.arange(py0, py1) + 0.5)
+        e0 = (x2 - x1) * (cy - y1) - (y2 - y1) * (cx - x1)
+        e1 = (x0 - x2) * (cy - y2) - (y0 - y2) * (cx - x2)
+        e2 = (x1 - x0) * (cy - y0) - (y1 - y0) * (cx - x0)
+        inside = ((e0 > 0) | ((e0 == 0) & tl[0])) & ((e1 > 0) | ((e1 == 0) & tl[1])) & ((e2 > 0) | ((e2 == 0) & tl[2]))
+        l0, l1, l2 = e0 / area, e1 / area, e2 / area
+        fb = [l0 * float(b[0, k]) + l1 * float(b[i1, k]) + l2 * float(b[i2, k]) for k in range(3)]
+        mn = np.minimum(np.minimum(fb[0], fb[1]), fb[2]); mx = np.maximum(np.maximum(fb[0], fb[1]), fb[2])
+        keep = inside & ~(mn < 0.0) & ~(mx > 1.0)
+        fw = l0 * float(wt[0]) + l1 * float(wt[i1]) + l2 * float(wt[i2])
+        out[py0:py1, px0:px1] += np.where(keep, fw.astype(np.float32), 0.0)
+    return out

@@ -58,6 +58,7 @@ SIGNATURES = {
                                             c_u8p, c_i64p]),
     "osr_intersecting_to_surface": (C.c_int, [C.c_void_p, C.c_int, c_dp, c_dp, C.c_int64, c_i32p, C.c_int64, C.c_int64,
                                               c_i32p, c_dp, c_i64p]),
+    "osr_rasterize_barycentric": (C.c_int, [C.c_void_p, c_fp, c_fp, c_fp, C.c_int64, C.c_int, C.c_int, c_fp]),
     "osr_knn_windowed": (C.c_int, [C.c_void_p, c_dp, C.c_int64, C.c_int, C.c_int64, c_i32p, c_dp]),
     "osr_enum_free_configurations": (C.c_int, [C.c_void_p, c_dp, C.c_int64, C.c_double, C.c_int, C.c_int, c_dp, c_u8p,
                                                c_i32p]),

@@ -20,6 +20,7 @@
 #include "kernels_seg.cuh"
 #include "kernels_surface.cuh"
 #include "kernels_knn.cuh"
+#include "kernels_raster.cuh"
 
 namespace {
 
@@ -1246,6 +1247,41 @@ int osr_knn_windowed(osr_world* w, const double* q, int64_t n, int k, int64_t wi
   w->host_counters.kernel_launches++;
   CU(cudaMemcpyAsync(out_idx, s.faces.p, (size_t)n * k * 4, cudaMemcpyDeviceToHost, s.stream));
   if (out_dist) CU(cudaMemcpyAsync(out_dist, s.seg.p, (size_t)n * k * 8, cudaMemcpyDeviceToHost, s.stream));
+  CU(cudaStreamSynchronize(s.stream));
+  return OSR_OK;
+}
+
+// ---- barycentric UV-chart splat (Renderer::renderBarycentric, osr_render.cc:590-759) ---------------
+int osr_rasterize_barycentric(osr_world* w, const float* uv, const float* bary, const float* weight, int64_t nprim,
+                              int res_x, int res_y, float* out) {
+  int rc = check_ready(w);
+  if (rc) return rc;
+  if (nprim < 0 || res_x <= 0 || res_y <= 0 || !out || (nprim > 0 && (!uv || !bary || !weight)))
+    return fail(OSR_EINVAL, "bad arguments");
+  std::lock_guard<std::mutex> lk(w->mu);
+  Slot& s = w->slots[0];
+  CU(cudaSetDevice(s.dev));
+  const size_t img = (size_t)res_x * res_y * 4;
+  CU(s.surf_l.need(img));
+  CU(cudaMemsetAsync(s.surf_l.p, 0, img, s.stream));   // bary_tex_->clear()
+  if (nprim > 0) {
+    CU(s.surf_v.need((size_t)nprim * 24));
+    CU(s.surf_f.need((size_t)nprim * 36));
+    CU(s.surf_off.need((size_t)nprim * 12));
+    CU(cudaMemcpyAsync(s.surf_v.p, uv, (size_t)nprim * 24, cudaMemcpyHostToDevice, s.stream));
+    CU(cudaMemcpyAsync(s.surf_f.p, bary, (size_t)nprim * 36, cudaMemcpyHostToDevice, s.stream));
+    CU(cudaMemcpyAsync(s.surf_off.p, weight, (size_t)nprim * 12, cudaMemcpyHostToDevice, s.stream));
+    const long long blocks = (nprim * 32 + 255) / 256;
+    if (blocks > 0x7fffffffLL) return fail(OSR_EINVAL, "too many primitives for one call");
+    CU(cudaEventRecord(s.ev0, s.stream));
+    osr::k_bary_raster<<<(unsigned)blocks, 256, 0, s.stream>>>((const float*)s.surf_v.p, (const float*)s.surf_f.p,
+                                                              (const float*)s.surf_off.p, (long long)nprim, res_x,
+                                                              res_y, (float*)s.surf_l.p);
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(s.ev1, s.stream));
+    w->host_counters.kernel_launches++;
+  }
+  CU(cudaMemcpyAsync(out, s.surf_l.p, img, cudaMemcpyDeviceToHost, s.stream));
   CU(cudaStreamSynchronize(s.stream));
   return OSR_OK;
 }

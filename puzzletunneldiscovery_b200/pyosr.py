@@ -659,3 +659,66 @@ def _rotate_points(q, V):
                   [2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)],
                   [2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)]])
     return V @ R.T + q[0:3]
+
+
+class Renderer(UnitWorld):
+    """Headless subset of pyosr.Renderer (module.cc:253-300): the barycentric UV-chart splat that turns
+    `intersecting_to_*_surface` output into a surface weight chart (src/GP/pipeline/preprocess_surface.py:248-311).
+    The GL context, depth / RGB rendering and the other Renderer members are outside the accelerated path; the
+    splat itself runs as a CUDA rasteriser (csrc/kernels_raster.cuh)."""
+
+    BARY_RENDERING_ROBOT = 0
+    BARY_RENDERING_SCENE = 1
+
+    def __init__(self, devices=None):
+        super().__init__(devices)
+        self._uv = {0: None, 1: None}
+        self._brd = {0: ([], [], []), 1: ([], [], [])}
+
+    def set_uv(self, target, uv):
+        """Per-vertex texture coordinates of the target mesh (Mesh::getUV), rows in the vertex numbering of
+        get_robot_geometry / get_scene_geometry."""
+        self._uv[self._target(target)] = np.ascontiguousarray(np.asarray(uv, dtype=np.float32).reshape(-1, 2))
+
+    def loadRobotTextureImage(self, fn):   # kept for call compatibility; the chart splat needs no texture image
+        pass
+
+    @staticmethod
+    def _target(target):
+        if target not in (0, 1):
+            raise OsrError("invalid barycentric rendering target")
+        return int(target)
+
+    def add_barycentric(self, F, V, target, weight=1.0):
+        """Renderer::addBarycentric (osr_render.cc:538-569): F int[P,3] = vertex ids of the surface face of each
+        primitive, V float[3P,3] = barycentrics of its three vertices, one weight for the whole batch."""
+        t = self._target(target)
+        if self._uv[t] is None:
+            raise OsrError("the target mesh has no UV coordinates (set_uv)")
+        F = np.asarray(F, dtype=np.int64).reshape(-1, 3)
+        V = np.asarray(V, dtype=np.float32).reshape(-1, 3)
+        if len(V) != 3 * len(F):
+            raise OsrError("V must hold three barycentric rows per face of F")
+        uvs, barys, weights = self._brd[t]
+        uvs.append(self._uv[t][F.reshape(-1)])
+        barys.append(V)
+        weights.append(np.full(len(V), weight, dtype=np.float32))
+
+    def clear_barycentric(self, target):
+        self._brd[self._target(target)] = ([], [], [])
+
+    def render_barycentric(self, target, res, svg_fn=""):
+        """Renderer::renderBarycentric (osr_render.cc:590-759) -> float32[res[0], res[1]], rows bottom-up."""
+        t = self._target(target)
+        res = np.asarray(res, dtype=np.int64).reshape(2)
+        uvs, barys, weights = self._brd[t]
+        out = np.zeros((int(res[1]), int(res[0])), np.float32)
+        if uvs:
+            uv = np.ascontiguousarray(np.concatenate(uvs)); ba = np.ascontiguousarray(np.concatenate(barys))
+            we = np.ascontiguousarray(np.concatenate(weights))
+        else:
+            uv = ba = we = None
+        n = 0 if uv is None else len(uv) // 3
+        check(self._L.osr_rasterize_barycentric(self._h, _p(uv, c_fp), _p(ba, c_fp), _p(we, c_fp), n, int(res[0]),
+                                                int(res[1]), _p(out, c_fp)))
+        return out

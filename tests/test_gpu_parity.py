@@ -473,3 +473,49 @@ def test_knn_windowed_matches_host_restatement(uw_org):
     assert fr.shape == (20, 7) and to.shape == (20, 7)
     with pytest.raises(RuntimeError):
         uw_org.knn_windowed(q, k=17, window=512)
+
+
+@pytest.mark.gpu
+def test_chart_splat_matches_restatement_and_chains_from_surface_mapping(oracle_mod):
+    """K7: the CUDA rasteriser covers exactly the pixels of the numpy restatement of the
+    reference's shaders and adds the same weights; then the whole chain contact state -> intersecting_to_*_surface
+    -> add_barycentric -> render_barycentric on a mesh with synthetic per-vertex UVs."""
+    from puzzletunneldiscovery_b200 import pyosr
+    r = make_world(pyosr.Renderer)
+    rs = np.random.RandomState(7)
+    P = 300
+    uv = rs.rand(P, 3, 2).astype(np.float32)
+    bary = rs.dirichlet([1, 1, 1], size=(P, 3)).astype(np.float32)
+    bary[::5] *= 1.3                                        # some primitives leave their face: discard path
+    w = np.repeat(rs.rand(P, 1).astype(np.float32) + 0.5, 3, axis=1)
+    out = np.zeros((64, 64), np.float32)
+    from puzzletunneldiscovery_b200._lib import check, c_fp
+    check(r._L.osr_rasterize_barycentric(r._h, uv.ctypes.data_as(c_fp), bary.ctypes.data_as(c_fp),
+                                         w.ctypes.data_as(c_fp), P, 64, 64, out.ctypes.data_as(c_fp)))
+    ref = oracle_mod.rasterize_barycentric(uv, bary, w, 64, 64)
+    assert np.array_equal(out > 0, ref > 0) and (ref > 0).sum() > 500
+    assert np.abs(out - ref).max() <= 1e-4 * max(1.0, ref.max())   # fp32 additive blending, order of adds differs
+    # chain on the alpha robot with a synthetic planar UV unwrap
+    g = golden("contacts_org.npz")
+    q = g["q"][0]
+    V1, F1 = r._geometry(1)
+    lo, hi = V1.min(axis=0), V1.max(axis=0)
+    r.set_uv(r.BARY_RENDERING_ROBOT, ((V1 - lo) / (hi - lo))[:, :2])
+    Wr = _world_vertices(q, V1)
+    c = r.intersecting_segments_batch(q, cap=1 << 14)
+    rt = np.unique(c["faces"][:, 1])[:16]
+    tri = Wr[F1[rt]]
+    cen = tri.mean(axis=1, keepdims=True)
+    IV = (cen + 0.5 * (tri - cen)).reshape(-1, 3)
+    IFc = np.arange(len(IV), dtype=np.int32).reshape(-1, 3)
+    IF, IBV = r.intersecting_to_robot_surface(q, True, IV, IFc)
+    r.clear_barycentric(r.BARY_RENDERING_ROBOT)
+    r.add_barycentric(IF, IBV, r.BARY_RENDERING_ROBOT, 127.0)
+    fb = r.render_barycentric(r.BARY_RENDERING_ROBOT, np.array([512, 512], np.int32))
+    assert fb.shape == (512, 512) and fb.dtype == np.float32 and fb.max() >= 127.0 and (fb >= 0).all()
+    ref = oracle_mod.rasterize_barycentric(r._uv[0][IF.reshape(-1)], IBV, np.full(len(IBV), 127.0), 512, 512)
+    assert np.array_equal(fb > 0, ref > 0) and np.abs(fb - ref).max() < 1e-2
+    r.clear_barycentric(r.BARY_RENDERING_ROBOT)
+    assert r.render_barycentric(r.BARY_RENDERING_ROBOT, [32, 32]).sum() == 0
+    with pytest.raises(RuntimeError):
+        r.add_barycentric(IF, IBV, r.BARY_RENDERING_SCENE, 1.0)      # no UVs set for the environment

@@ -161,3 +161,24 @@ def test_surface_map_closed_form(oracle_mod):
     assert f.tolist() == [[3, 4, 5], [0, 1, 2]]
     assert np.allclose(L[0:3], [[0.8, 0.1, 0.1], [0.4, 0.5, 0.1], [0.4, 0.1, 0.5]], atol=1e-15)
     assert np.allclose(L[3:6], [[0.5, 0.25, 0.25], [0.25, 0.5, 0.25], [0.25, 0.25, 0.5]], atol=1e-15)
+
+
+def test_chart_splat_rules_closed_form(oracle_mod):
+    """N4 restatement (bary.geom / bary.frag, osr_render.cc:745-748): pixel-centre coverage, shared edges counted
+    once (additive blending would show a double hit), discard of the part outside the surface face."""
+    O = oracle_mod
+    eye = np.eye(3, dtype=np.float32)
+    one = np.ones(3, np.float32)
+    tri = np.array([[0, 0], [1, 0], [0, 1]], np.float32)
+    img = O.rasterize_barycentric(tri, eye, one, 8, 8)
+    assert img.sum() == 28 and img[0, 0] == 1 and img[7, 0] == 0 and img[0, 7] == 0   # centres with x + y < 8
+    quad = np.array([[[0, 0], [1, 0], [1, 1]], [[0, 0], [1, 1], [0, 1]]], np.float32)
+    img = O.rasterize_barycentric(quad, np.stack([eye, eye]), np.stack([one, one]) * 2.5, 16, 16)
+    assert (img == 2.5).all()                                                         # every pixel exactly once
+    # barycentrics (2,-1,0) .. : the primitive sticks out of its face; only the part with all b in [0,1] is drawn
+    b = np.array([[1, 0, 0], [-1, 2, 0], [-1, 0, 2]], np.float32)
+    img = O.rasterize_barycentric(tri, b, one, 8, 8)
+    full = O.rasterize_barycentric(tri, eye, one, 8, 8)
+    # ... plus the 8 centres lying exactly ON the face's hypotenuse: interior to the big primitive, b0 == 0 is not < 0
+    assert img.sum() == 36 and (img >= full).all() and img[7, 7] == 0
+    assert O.rasterize_barycentric(tri, eye * 0, one, 8, 8).sum() == 0                # degenerate: no fragments
