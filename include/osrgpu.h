@@ -170,6 +170,17 @@ int osr_knn_windowed(osr_world* w, const double* q, int64_t n, int k, int64_t wi
 int osr_rasterize_barycentric(osr_world* w, const float* uv, const float* bary, const float* weight, int64_t nprim,
                               int res_x, int res_y, float* out);
 
+/* OMPL-frame batched validators (rows x y z qx qy qz qw, StateSpace::copyFromEigen3):
+ * OmplDriver::validateStates (lib/pyse3ompl/ompldriver.cc:566-589) = isValid after translateOMPLStateToUnitState;
+ * OmplDriver::validateMotionPairs (:592-621) = DiscreteMotionValidator::checkMotion
+ * (third-party/ompl.app/ompl/src/ompl/base/src/DiscreteMotionValidator.cpp:96-150): out[i]=1 iff s2 and every
+ * interior point m/nd of OMPL's SE(3) interpolation are valid, nd = max(ceil(|dt| / (resolution*trans_extent)),
+ * ceil(acos|q1.q2| / (resolution*pi/2))).  trans_extent = diagonal of the planner's translation bounds (OMPL
+ * frame); resolution = the state-validity-checking resolution (OmplDriver::setCDRes).  nd_out optional. */
+int osr_ompl_validate_states(osr_world* w, const double* q_ompl, int64_t n, uint8_t* out);
+int osr_ompl_check_motions(osr_world* w, const double* q0, const double* q1, int64_t n, double trans_extent,
+                           double resolution, uint8_t* out, int64_t* nd_out);
+
 /* Device-resident variants (pointers on the handle's first device).  Launch only; the caller
  * synchronises with osr_sync() (or its own stream wait on osr_stream()). */
 int osr_is_valid_states_device(osr_world* w, const double* d_q, int64_t n, uint8_t* d_out);

@@ -73,6 +73,8 @@ def lib():
     L.orc_contact_multiplicity.argtypes = [_dp]
     L.orc_surface_map.argtypes = [_dp, _ip, C.c_longlong, _dp, _ip, C.c_longlong, C.c_longlong, _ip, _dp]
     L.orc_surface_map.restype = C.c_longlong
+    L.orc_ompl_check_motions.argtypes = [C.c_void_p, _dp, _dp, C.c_longlong, C.c_double, _dp, C.c_double, C.c_double,
+                                         _u8p, _llp, C.c_int]
     ref = os.path.join(_HERE, "_ref", "libmoller97d.so")
     if os.path.exists(ref):
         _MOLLER = C.CDLL(ref)
@@ -264,6 +266,16 @@ class OracleWorld:
         self.L.orc_is_valid_transitions(self.h, _ptr(fr, _dp), _ptr(to, _dp), len(fr), float(ivd), _ptr(out, _u8p),
                                         _ptr(cnt, _llp), threads)
         return (out, cnt) if counters else out
+
+    def ompl_check_motions(self, q0, q1, scale, dc, trans_extent, resolution, threads=0):
+        """DiscreteMotionValidator::checkMotion per OMPL-frame row pair -> (valid uint8[N], nd int64[N])."""
+        q0 = _states(q0); q1 = _states(q1)
+        dc = np.ascontiguousarray(dc, dtype=np.float64)
+        out = np.zeros(len(q0), np.uint8); nd = np.zeros(len(q0), np.int64)
+        self.L.orc_ompl_check_motions(self.h, _ptr(q0, _dp), _ptr(q1, _dp), len(q0), float(scale), _ptr(dc, _dp),
+                                      float(resolution * trans_extent), float(resolution * 0.5 * np.pi),
+                                      _ptr(out, _u8p), _ptr(nd, _llp), threads)
+        return out, nd
 
     def intersecting_segments_batch(self, q, cap=1 << 22, counters=False):
         """unit_world.cc:959-1012 per row: CSR offsets, segments[.,6], faces[.,2], coplanar."""

@@ -44,6 +44,7 @@
 #include <limits>
 #include <sstream>
 #include <string>
+#include <utility>
 #include <vector>
 #ifdef _OPENMP
 #include <omp.h>
@@ -986,6 +987,70 @@ long long orc_surface_map(const double* TV, const int* TF, long long nTF, const 
     }
   }
   return rows;
+}
+
+// OmplDriver::validateMotionPairs (lib/pyse3ompl/ompldriver.cc:592-621) -> DiscreteMotionValidator::checkMotion
+// (third-party/ompl.app/ompl/src/ompl/base/src/DiscreteMotionValidator.cpp:96-150), literally: s2 first, then
+// the interior points in bisection order from a FIFO queue.  OMPL pieces restated from the vendored sources:
+// validSegmentCount (StateSpace.cpp, CompoundStateSpace: maximum over sub-spaces), SO3StateSpace arcLength /
+// interpolate (spaces/src/SO3StateSpace.cpp:252-316), RealVectorStateSpace::interpolate.  Each OMPL-frame state
+// is mapped to the unit frame as UnitWorld::translateOMPLStateToUnitState (unit_world.cc:689-711, identity
+// perturbation): t = scale*t - Rot(q)*dc.  PARITY UNPINNED: OMPL itself cannot be built here (boost absent).
+static void ompl_to_unit(const double* o, double scale, const double* dc, double* u) {
+  double w = o[6], x = o[3], y = o[4], z = o[5];
+  double n2 = x * x + y * y + z * z + w * w;
+  if (n2 > 0) { double n = std::sqrt(n2); w /= n; x /= n; y /= n; z /= n; }
+  double uvx = 2.0 * (y * dc[2] - z * dc[1]), uvy = 2.0 * (z * dc[0] - x * dc[2]), uvz = 2.0 * (x * dc[1] - y * dc[0]);
+  double rx = dc[0] + w * uvx + (y * uvz - z * uvy), ry = dc[1] + w * uvy + (z * uvx - x * uvz),
+         rz = dc[2] + w * uvz + (x * uvy - y * uvx);
+  u[0] = scale * o[0] - rx; u[1] = scale * o[1] - ry; u[2] = scale * o[2] - rz;
+  u[3] = w; u[4] = x; u[5] = y; u[6] = z;
+}
+void orc_ompl_check_motions(void* h, const double* q0, const double* q1, long long N, double scale, const double* dc,
+                            double seg_trans, double seg_rot, uint8_t* out, long long* nd_out, int threads) {
+  World* w = (World*)h;
+#ifdef _OPENMP
+  int nt = threads > 0 ? threads : omp_get_max_threads();
+#pragma omp parallel for schedule(dynamic, 4) num_threads(nt)
+#endif
+  for (long long i = 0; i < N; i++) {
+    const double* a = q0 + 7 * i; const double* b = q1 + 7 * i;
+    double dx = a[0] - b[0], dy = a[1] - b[1], dz = a[2] - b[2];
+    double dtr = std::sqrt(dx * dx + dy * dy + dz * dz);
+    double dq = std::fabs(a[3] * b[3] + a[4] * b[4] + a[5] * b[5] + a[6] * b[6]);
+    double theta = dq > 1.0 - 1e-9 ? 0.0 : std::acos(dq);
+    long long n1 = (long long)std::ceil(dtr / seg_trans), n2 = (long long)std::ceil(theta / seg_rot);
+    long long nd = n1 > n2 ? n1 : n2;
+    if (nd_out) nd_out[i] = nd;
+    double u[7];
+    ompl_to_unit(b, scale, dc, u);
+    bool result = w->is_valid(u);
+    if (result && nd >= 2) {
+      std::vector<std::pair<long long, long long>> pos;
+      size_t head = 0;
+      pos.emplace_back(1, nd - 1);
+      while (head < pos.size()) {
+        std::pair<long long, long long> x = pos[head];
+        long long mid = (x.first + x.second) / 2;
+        double t = (double)mid / (double)nd, o[7];
+        for (int k = 0; k < 3; k++) o[k] = a[k] + (b[k] - a[k]) * t;
+        if (theta > 2.220446049250313e-16) {
+          double d = 1.0 / std::sin(theta), s0 = std::sin((1.0 - t) * theta), s1 = std::sin(t * theta);
+          double dot = a[3] * b[3] + a[4] * b[4] + a[5] * b[5] + a[6] * b[6];
+          if (dot < 0) s1 = -s1;
+          for (int k = 0; k < 4; k++) o[3 + k] = (a[3 + k] * s0 + b[3 + k] * s1) * d;
+        } else {
+          for (int k = 0; k < 4; k++) o[3 + k] = a[3 + k];
+        }
+        ompl_to_unit(o, scale, dc, u);
+        if (!w->is_valid(u)) { result = false; break; }
+        head++;
+        if (x.first < mid) pos.emplace_back(x.first, mid - 1);
+        if (x.second > mid) pos.emplace_back(mid + 1, x.second);
+      }
+    }
+    out[i] = result ? 1 : 0;
+  }
 }
 
 }  // extern "C"

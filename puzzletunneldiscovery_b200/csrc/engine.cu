@@ -204,6 +204,7 @@ int init_slot(osr_world* w, Slot& s, int dev) {
   CU(cudaMemset(s.err, 0, sizeof(int)));
   // persistent grid: as many blocks as fit, on every SM
   CU(cudaFuncSetAttribute(osr::k_is_valid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_PER_BLOCK));
+  CU(cudaFuncSetAttribute(osr::k_ompl_motion, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_PER_BLOCK));
   CU(cudaFuncSetAttribute(osr::k_transit<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_PER_BLOCK));
   CU(cudaFuncSetAttribute(osr::k_transit<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_PER_BLOCK));
   CU(cudaFuncSetAttribute(osr::k_transit<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_PER_BLOCK));
@@ -1283,6 +1284,69 @@ int osr_rasterize_barycentric(osr_world* w, const float* uv, const float* bary, 
   }
   CU(cudaMemcpyAsync(out, s.surf_l.p, img, cudaMemcpyDeviceToHost, s.stream));
   CU(cudaStreamSynchronize(s.stream));
+  return OSR_OK;
+}
+
+// ---- OMPL-frame batched validators (OmplDriver::validateStates / validateMotionPairs, ompldriver.cc:566-621) ----
+int osr_ompl_validate_states(osr_world* w, const double* q_ompl, int64_t n, uint8_t* out) {
+  int rc = check_ready(w);
+  if (rc) return rc;
+  if (n < 0 || (n > 0 && (!q_ompl || !out))) return fail(OSR_EINVAL, "bad arguments");
+  if (n == 0) return OSR_OK;
+  std::vector<double> u((size_t)n * 7);
+  rc = osr_translate_ompl_to_unit(w, q_ompl, n, u.data());
+  if (rc) return rc;
+  return osr_is_valid_states(w, u.data(), n, out);
+}
+
+int osr_ompl_check_motions(osr_world* w, const double* q0, const double* q1, int64_t n, double trans_extent,
+                           double resolution, uint8_t* out, int64_t* nd_out) {
+  int rc = check_ready(w);
+  if (rc) return rc;
+  if (n < 0 || (n > 0 && (!q0 || !q1 || !out)) || !(trans_extent > 0.0) || !(resolution > 0.0))
+    return fail(OSR_EINVAL, "bad arguments");
+  const double ident[7] = {0, 0, 0, 1, 0, 0, 0};
+  if (memcmp(w->perturb, ident, sizeof(ident)) != 0)
+    return fail(OSR_EINVAL, "OMPL-frame motion checks need the identity perturbation");
+  if (n == 0) return OSR_OK;
+  std::lock_guard<std::mutex> lk(w->mu);
+  osr::OmplFrame F;
+  F.scale = (double)w->scene_scale;
+  for (int k = 0; k < 3; k++) F.dc[k] = (double)(w->ompl_centre[k] - w->centre[k]) * (double)w->scene_scale;
+  F.seg_trans = resolution * trans_extent;
+  F.seg_rot = resolution * (0.5 * 3.14159265358979323846);
+  int parts = (int)w->slots.size();
+  for (int i = 0; i < parts; i++) {
+    Slot& s = w->slots[i];
+    int64_t lo, hi;
+    shard(n, parts, i, lo, hi);
+    int64_t m = hi - lo;
+    if (m == 0) continue;
+    CU(cudaSetDevice(s.dev));
+    CU(s.in0.need((size_t)m * 56));
+    CU(s.in1.need((size_t)m * 56));
+    CU(s.out[0].need((size_t)m));
+    CU(s.out[5].need((size_t)m * 8));
+    CU(cudaMemcpyAsync(s.in0.p, q0 + 7 * lo, (size_t)m * 56, cudaMemcpyHostToDevice, s.stream));
+    CU(cudaMemcpyAsync(s.in1.p, q1 + 7 * lo, (size_t)m * 56, cudaMemcpyHostToDevice, s.stream));
+    CU(cudaMemsetAsync(s.work, 0, 2 * sizeof(unsigned long long), s.stream));
+    osr::KParams P = w->params(s);
+    CU(cudaEventRecord(s.ev0, s.stream));
+    osr::k_ompl_motion<<<s.grid_transit, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK, s.stream>>>(
+        P, F, (const double*)s.in0.p, (const double*)s.in1.p, (long long)m, (uint8_t*)s.out[0].p,
+        nd_out ? (long long*)s.out[5].p : nullptr);
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(s.ev1, s.stream));
+    w->host_counters.kernel_launches++;
+    CU(cudaMemcpyAsync(out + lo, s.out[0].p, (size_t)m, cudaMemcpyDeviceToHost, s.stream));
+    if (nd_out) CU(cudaMemcpyAsync(nd_out + lo, s.out[5].p, (size_t)m * 8, cudaMemcpyDeviceToHost, s.stream));
+  }
+  for (int i = 0; i < parts; i++) {
+    Slot& s = w->slots[i];
+    CU(cudaSetDevice(s.dev));
+    rc = check_device_error(w, s);
+    if (rc) return rc;
+  }
   return OSR_OK;
 }
 

@@ -633,6 +633,112 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB)
 }
 
 // ---------------------------------------------------------------------------------------------
+// K2b: OMPL motion validation on OMPL-frame states: what OmplDriver::validateMotionPairs
+// (/root/reference/lib/pyse3ompl/ompldriver.cc:592-621) asks of ompl::base::DiscreteMotionValidator::checkMotion
+// (third-party/ompl.app/ompl/src/ompl/base/src/DiscreteMotionValidator.cpp:96-150): s2 is valid and so is every
+// interior point interpolate(s1, s2, m/nd), m = 1..nd-1 (checkMotion visits them in bisection order; the boolean
+// does not depend on the order), with
+//   nd = max over the two sub-spaces of ceil(distance / (resolution * maximum extent))
+//        (StateSpace::validSegmentCount, CompoundStateSpace takes the maximum; SO(3) extent pi/2, distance
+//         acos|q1.q2| with the 1e-9 clamp of SO3StateSpace.cpp:252-260),
+//   interpolate = RealVectorStateSpace (from + (to - from) t) x SO3StateSpace::interpolate (:287-316).
+// States are rows x y z qx qy qz qw (StateSpace::copyFromEigen3).  Each interpolated OMPL state is mapped to the
+// unit frame like UnitWorld::translateOMPLStateToUnitState (unit_world.cc:689-711) with identity perturbation:
+// t_unit = scale * t - Rot(q) * dc,  dc = (ompl centre - robot centre) * scale.
+// One warp per pair, 32 consecutive sample points per tile, the same warp-shared traversal as K2.
+// ---------------------------------------------------------------------------------------------
+struct OmplFrame {
+  double scale;       // scene_scale (float widened)
+  double dc[3];       // (ompl centre - centre) * scale
+  double seg_trans;   // resolution * maximum extent of the translation bounds
+  double seg_rot;     // resolution * pi/2
+};
+
+__device__ __forceinline__ double ompl_arc_length(const double* a, const double* b) {
+  double dq = fabs(a[3] * b[3] + a[4] * b[4] + a[5] * b[5] + a[6] * b[6]);
+  if (dq > 1.0 - 1e-9) return 0.0;
+  return acos(dq);
+}
+
+// OMPL-frame interpolation at t, then the unit-frame state (w-first) of the result
+__device__ __forceinline__ void ompl_point_to_unit(const OmplFrame& F, const double* a, const double* b, double theta,
+                                                   double t, double* s) {
+  double p[3], q[4];  // q = x y z w
+#pragma unroll
+  for (int k = 0; k < 3; k++) p[k] = a[k] + (b[k] - a[k]) * t;
+  if (theta > 2.220446049250313e-16) {
+    double d = 1.0 / sin(theta), s0 = sin((1.0 - t) * theta), s1 = sin(t * theta);
+    double dq = a[3] * b[3] + a[4] * b[4] + a[5] * b[5] + a[6] * b[6];
+    if (dq < 0) s1 = -s1;
+#pragma unroll
+    for (int k = 0; k < 4; k++) q[k] = (a[3 + k] * s0 + b[3 + k] * s1) * d;
+  } else {
+#pragma unroll
+    for (int k = 0; k < 4; k++) q[k] = a[3 + k];
+  }
+  double w = q[3], x = q[0], y = q[1], z = q[2];
+  quat_normalize(w, x, y, z);
+  // Eigen quaternion * vector: v + w (2 u x v) + u x (2 u x v)
+  double uvx = 2.0 * (y * F.dc[2] - z * F.dc[1]), uvy = 2.0 * (z * F.dc[0] - x * F.dc[2]),
+         uvz = 2.0 * (x * F.dc[1] - y * F.dc[0]);
+  double rx = F.dc[0] + w * uvx + (y * uvz - z * uvy), ry = F.dc[1] + w * uvy + (z * uvx - x * uvz),
+         rz = F.dc[2] + w * uvz + (x * uvy - y * uvx);
+  s[0] = F.scale * p[0] - rx; s[1] = F.scale * p[1] - ry; s[2] = F.scale * p[2] - rz;
+  s[3] = w; s[4] = x; s[5] = y; s[6] = z;
+}
+
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, 3)
+    k_ompl_motion(KParams P, OmplFrame F, const double* __restrict__ q0, const double* __restrict__ q1, long long n,
+                  uint8_t* __restrict__ out, long long* __restrict__ nd_out) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  WarpShared& S = reinterpret_cast<WarpShared*>(smem_raw)[threadIdx.x >> 5];
+  const int lane = threadIdx.x & 31;
+  WarpCtx C;
+  ctx_init(P, C);
+  unsigned long long nposes = 0;
+  while (true) {
+    unsigned long long pr = 0;
+    if (lane == 0) pr = atomicAdd(P.work_counter, 1ull);
+    pr = __shfl_sync(FULL, pr, 0);
+    if ((long long)pr >= n) break;
+    double a[7], b[7];
+#pragma unroll
+    for (int k = 0; k < 7; k++) { a[k] = __ldg(q0 + 7 * pr + k); b[k] = __ldg(q1 + 7 * pr + k); }
+    const double dx = a[0] - b[0], dy = a[1] - b[1], dz = a[2] - b[2];
+    const double dtr = sqrt(dx * dx + dy * dy + dz * dz);
+    const double theta = ompl_arc_length(a, b);
+    const long long nt = (long long)ceil(dtr / F.seg_trans), nr = (long long)ceil(theta / F.seg_rot);
+    const long long nd = nt > nr ? nt : nr;
+    // sample points: index 0 = s2 itself, index m = interior point m/nd (m = 1..nd-1)
+    const long long total = nd >= 2 ? nd : 1;
+    bool valid = true;
+    for (long long base = 0; base < total && valid; base += 32) {
+      const long long m = base + lane;
+      const bool have = m < total;
+      if (have) {
+        double s[7];
+        ompl_point_to_unit(F, a, b, theta, m == 0 ? 1.0 : (double)m / (double)nd, s);
+        if (m == 0) ompl_point_to_unit(F, b, b, 0.0, 0.0, s);   // s2 exactly, not its slerp image
+        set_pose(P, S, lane, s);
+      }
+      unsigned alive = __ballot_sync(FULL, have);
+      __syncwarp();
+      unsigned hits = traverse_tile<MODE_SEGMENT>(P, S, C, alive, lane);
+      if (C.overflow) { valid = false; break; }
+      nposes += hits ? (unsigned)__ffs(hits) : __popc(alive);
+      if (hits) valid = false;
+      __syncwarp();
+    }
+    if (lane == 0) {
+      out[pr] = valid ? 1 : 0;
+      if (nd_out) nd_out[pr] = nd;
+    }
+    if (C.overflow) break;
+  }
+  ctx_flush(P, C, nposes, lane);
+}
+
+// ---------------------------------------------------------------------------------------------
 // K3: all contacts of a state + Moeller intersection segment per contact
 // (CDModel::collideForDetails, /root/reference/lib/osr/cdmodel.cc:200-229;
 //  UnitWorld::intersectingSegments, lib/osr/unit_world.cc:959-1012).

@@ -557,6 +557,25 @@ class UnitWorld:
             if max_trials >= 0 and done > max_trials:
                 return qs[-1]
 
+    # ---- OMPL-frame batched validators (lib/pyse3ompl/pyse3ompl.cc:77-81) --------------------------
+    def ompl_validate_states(self, qs):
+        """OmplDriver.validate_states: int32[N], rows x y z qx qy qz qw in the OMPL frame."""
+        q = _states(qs)
+        out = np.empty(len(q), np.uint8)
+        check(self._L.osr_ompl_validate_states(self._h, _p(q, c_dp), len(q), _p(out, c_u8p)))
+        return out.astype(np.int32)
+
+    def ompl_validate_motion_pairs(self, qs0, qs1, trans_extent, resolution, with_counts=False):
+        """OmplDriver.validate_motion_pairs under OMPL's DiscreteMotionValidator: int32[min(N0, N1)]."""
+        a = _states(qs0); b = _states(qs1)
+        n = min(len(a), len(b))
+        a = np.ascontiguousarray(a[:n]); b = np.ascontiguousarray(b[:n])
+        out = np.empty(n, np.uint8)
+        nd = np.empty(n, np.int64) if with_counts else None
+        check(self._L.osr_ompl_check_motions(self._h, _p(a, c_dp), _p(b, c_dp), n, float(trans_extent),
+                                             float(resolution), _p(out, c_u8p), _p(nd, c_i64p)))
+        return (out.astype(np.int32), nd) if with_counts else out.astype(np.int32)
+
     # ---- k-NN edge generation (SURVEY 8(d) D4 / 8(f) N1) -----------------------------------------
     def knn_windowed(self, qs, k=8, window=4096, with_distance=False):
         """k nearest states under pyosr.distance inside windows of consecutive indices -> int32[N,k]."""

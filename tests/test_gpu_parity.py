@@ -519,3 +519,38 @@ def test_chart_splat_matches_restatement_and_chains_from_surface_mapping(oracle_
     assert r.render_barycentric(r.BARY_RENDERING_ROBOT, [32, 32]).sum() == 0
     with pytest.raises(RuntimeError):
         r.add_barycentric(IF, IBV, r.BARY_RENDERING_SCENE, 1.0)      # no UVs set for the environment
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shift", [None, (1.0, -2.0, 3.0)])
+def test_ompl_frame_validators_match_restatement(shift, oracle_mod):
+    """N1: OmplDriver.validate_states / validate_motion_pairs semantics (DiscreteMotionValidator::checkMotion with
+    OMPL's own SE(3) interpolation and segment count) on OMPL-frame rows, against the oracle's literal
+    restatement; `shift` moves the robot centre away from the OMPL centre so the frame map is not a pure scale."""
+    from puzzletunneldiscovery_b200 import pyosr
+    import functools
+    probe = make_world(pyosr.UnitWorld)
+    centre = None if shift is None else probe.get_ompl_center(1) + np.asarray(shift)
+    uw = make_world(pyosr.UnitWorld, "org", centre)
+    ow = make_world(oracle_mod.OracleWorld, "org", centre)
+    q = W.random_states(6000, seed=61)
+    valid = uw.is_valid_states(q)
+    qo = uw.translate_unit_to_ompl(q)
+    assert np.array_equal(uw.ompl_validate_states(qo).astype(bool), uw.is_valid_states(uw.translate_ompl_to_unit(qo)))
+    assert (uw.ompl_validate_states(qo).astype(bool) == valid).mean() > 0.999     # round trip of the frame maps
+    ms = q[valid][:1024]
+    fr, to = uw.knn_edges(ms, k=4, window=256)
+    a, b = uw.translate_unit_to_ompl(fr), uw.translate_unit_to_ompl(to)
+    scale = uw.scene_scale
+    dc = (uw.get_ompl_center(1).astype(np.float32) - uw.robot_center.astype(np.float32)).astype(np.float64) * scale
+    extent, res = 150.0, 0.01
+    got, nd = uw.ompl_validate_motion_pairs(a, b, extent, res, with_counts=True)
+    want, ond = ow.ompl_check_motions(a, b, scale, dc, extent, res)
+    assert np.array_equal(nd, ond) and nd.max() > 32 and nd.min() >= 1
+    assert np.array_equal(got.astype(bool), want.astype(bool)) and 0.05 < got.mean() < 0.999
+    # an invalid goal fails whatever lies in between; coincident states need one check only
+    bad = uw.translate_unit_to_ompl(q[~valid][:8])
+    g2, n2 = uw.ompl_validate_motion_pairs(a[:8], bad, extent, res, with_counts=True)
+    assert not g2.any()
+    g3, n3 = uw.ompl_validate_motion_pairs(a[:8], a[:8], extent, res, with_counts=True)
+    assert g3.all() and (n3 == 0).all()
