@@ -365,7 +365,12 @@ def run_ours(args):
         "dtype": "f32 box tests + f32-filtered/f64-exact triangle SAT", "data": "synthetic",
         "config": workload_config(n),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak if peak else None, "traffic": None, "peak_source": peak_src,
+                     "frac": achieved / peak if peak else None,
+                     # DRAM bytes per launch of this kernel from the committed ncu --set full capture
+                     # (dram__bytes_read.sum 59.03 MB + dram__bytes_write.sum 0.30 MB at 2^20 states per launch)
+                     "traffic": 59.333e6 if n == (1 << 20) else None,
+                     "traffic_unit": "bytes per launch (ncu, profiles/r01/ncu_full_k_valid_dfs_final.raw.csv)",
+                     "peak_source": peak_src,
                      "kernel": "k_valid_dfs", "kernel_ms": kernel_ms, "algorithmic_bytes_per_launch": alg,
                      "note": "algorithmic bytes = 57 B/state + 128 B x oracle OBB tests + 72 B x oracle triangle "
                              "tests (SURVEY 8(d) D8); the working set (0.33 MB) lives in L1/L2, so the HBM "
