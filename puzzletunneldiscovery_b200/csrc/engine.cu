@@ -521,6 +521,7 @@ static osr::DfsParams dfs_params(const osr_world* w, const Slot& s) {
   P.work_counter = s.work;
   P.error_flag = s.err;
   P.ready = nullptr;
+  P.ready_floor = 0;
   return P;
 }
 
@@ -547,6 +548,9 @@ static int launch_valid(osr_world* w, Slot& s, const double* d_q, int64_t n, uin
       return OSR_OK;
     }
     CU(cudaEventRecord(s.ev0, s.stream));
+    static const bool probe_feed = getenv("OSR_PROBE_FEED_KERNEL") != nullptr;  // A/B: the fed variant on resident input
+    if (probe_feed) { D.ready_floor = (long long)n; launch_dfs_variant<true, double>(s, D, d_q, (long long)n, d_out, s.stream); }
+    else
     launch_dfs_variant<false, double>(s, D, d_q, (long long)n, d_out, s.stream);
     CU(cudaGetLastError());
     CU(cudaEventRecord(s.ev1, s.stream));
@@ -622,13 +626,15 @@ static int64_t host_chunk_states() {
 
 // stream-fed K1 launch on the main stream (work word [2]); T = double or float states
 template <typename T>
-static int launch_valid_feed(osr_world* w, Slot& s, const T* d_q, int64_t n, uint8_t* d_out, const long long* ready) {
+static int launch_valid_feed(osr_world* w, Slot& s, const T* d_q, int64_t n, uint8_t* d_out, const long long* ready,
+                             long long ready_floor) {
   if (n > 0x7fffffffLL) return fail(OSR_EINVAL, "more than 2^31-1 states in one launch");
   unsigned long long* work = s.work + 2;
   CU(cudaMemsetAsync(work, 0, sizeof(unsigned long long), s.stream));
   osr::DfsParams D = dfs_params(w, s);
   D.work_counter = work;
   D.ready = ready;
+  D.ready_floor = ready_floor;
   CU(cudaEventRecord(s.ev0, s.stream));
   launch_dfs_variant<true, T>(s, D, d_q, (long long)n, d_out, s.stream);
   CU(cudaGetLastError());
@@ -688,7 +694,8 @@ static int valid_states_host(osr_world* w, const T* q, int64_t n, uint8_t* out) 
       }
       static const bool wait_all = getenv("OSR_FEED_WAIT_ALL") != nullptr;  // probe: kernel starts after the last chunk
       CU(cudaStreamWaitEvent(s.stream, s.feed_ev[wait_all ? c - 1 : 0], 0));
-      rc = launch_valid_feed<T>(w, s, (const T*)s.in0.p, m, (uint8_t*)s.out[0].p, s.ready);
+      rc = launch_valid_feed<T>(w, s, (const T*)s.in0.p, m, (uint8_t*)s.out[0].p, s.ready,
+                                (long long)(wait_all ? m : std::min(ck, m)));  // the launch waits for that event
       if (rc) return rc;
       CU(cudaMemcpyAsync(out + lo, s.out[0].p, (size_t)m, cudaMemcpyDeviceToHost, s.stream));
       CU(cudaEventRecord(s.evq, s.stream3));

@@ -37,23 +37,8 @@ struct DfsParams {
   // stream-fed launches (FEED): number of leading states whose upload has completed, advanced by small H2D
   // copies queued behind each chunk of the input on the copy stream (engine.cu: osr_is_valid_states)
   const long long* ready;
+  long long ready_floor;  // states certainly resident when the kernel starts (the launch is ordered behind them)
 };
-
-// Wait (one lane polls, with back-off) until at least `need` states are resident; returns the count observed.
-// Gives up after ~2^22 polls (seconds): raises the error flag and returns a short count instead of hanging the
-// device if the copies never arrive.  Kept tiny and inline: a call in K1's loop costs registers on the hot path.
-__device__ __forceinline__ long long wait_for_states(const long long* ready, int* error_flag, long long need, int lane) {
-  long long seen = 0;
-  if (lane == 0) {
-    for (int spins = 0;; spins++) {
-      asm volatile("ld.acquire.sys.global.s64 %0, [%1];" : "=l"(seen) : "l"(ready) : "memory");
-      if (seen >= need) break;
-      if (spins > (1 << 22)) { atomicExch(error_flag, 2); break; }
-      __nanosleep(1000);
-    }
-  }
-  return __shfl_sync(0xffffffffu, seen, 0);
-}
 
 constexpr int DFS_WARPS = 12;   // 3 per scheduler: 4 would need <= 128 registers (16 K registers per SM sub-partition)
 constexpr int DFS_THREADS = DFS_WARPS * 32;
@@ -89,6 +74,8 @@ struct __align__(16) DfsWarpMem {
   int pend_idx[32];
   int parts[32];       // work sharing at the end of the input: lanes still working on the pose of home lane i
   int hitf[32];        // ... and whether one of them has found an intersecting pair
+  int ready_seen;      // stream-fed launches: states known to be resident (kept out of the register file)
+  int pad_[3];
 };
 
 // leaf-queue entry: owner lane:5 | epoch:11 | env triangle:24 | robot triangle:24
@@ -199,7 +186,7 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
   bool exhausted = false, draining_leaf = false, draining_re = false, steal_mode = false;
   unsigned n_bv = 0, n_leaf = 0, n_fp64 = 0;
   unsigned long long nposes = 0;
-  long long ready_seen = 0;  // FEED: states known to be resident (the device word is polled only past this)
+  if (FEED) M.ready_seen = (int)min(P.ready_floor, 0x7fffffffLL);  // same value from every lane
 #ifdef OSR_DFS_STATS
   unsigned st_iters = 0, st_active = 0, st_wait = 0, st_idle = 0;
 #endif
@@ -226,11 +213,23 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
         unsigned long long base = 0;
         if (lane == 0) base = atomicAdd(P.work_counter, 32ull);
         base = __shfl_sync(FULL, base, 0);
+        if (FEED && (long long)base < n) {
+          // Wait until the states [base, base+32) have been uploaded.  Written so that control flow stays
+          // warp-uniform (every lane polls, the value of lane 0 decides): a one-lane polling loop or an
+          // out-of-line call here costs the whole traversal loop its convergence (+25 % instructions, +8 % time).
+          const long long need = min((long long)base + 32, n);
+          long long seen = __shfl_sync(FULL, (long long)M.ready_seen, 0);
+          for (int spins = 0; seen < need; spins++) {
+            long long v;
+            asm volatile("ld.acquire.sys.global.s64 %0, [%1];" : "=l"(v) : "l"(P.ready) : "memory");
+            seen = __shfl_sync(FULL, v, 0);
+            if (seen >= need) { M.ready_seen = (int)min(seen, 0x7fffffffLL); break; }
+            if (spins > (1 << 22)) { atomicExch(P.error_flag, 2); base = (unsigned long long)n; break; }   // gave up
+            __nanosleep(1000);
+          }
+          __syncwarp();
+        }
         if ((long long)base >= n) exhausted = true;
-        else if (FEED && min((long long)base + 32, n) > ready_seen &&
-                 (ready_seen = wait_for_states(P.ready, P.error_flag, min((long long)base + 32, n), lane)) <
-                     min((long long)base + 32, n))
-          exhausted = true;
         else {
           long long i = (long long)base + lane;
           bool have = i < n;
