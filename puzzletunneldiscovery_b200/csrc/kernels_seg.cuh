@@ -48,7 +48,7 @@ struct SegArgs {
 };
 
 // Results of one segment (all lanes compute the same values; lane 0 / lanes 0..6 store them).
-__device__ __noinline__ void seg_store(const SegArgs& A, long long seg, const double* ab, bool free_flag,
+__device__ __forceinline__ void seg_store(const SegArgs& A, long long seg, const double* ab, bool free_flag,
                                        double free_tau, double touch_tau, long long steps, int mode, int lane) {
   // mode 0: lf = from, fh = to (vd >= dist);  1: hit at the first step (lf = from);  2: hit later;  3: all free
   double lf[7], fh[7];
@@ -83,7 +83,7 @@ __device__ __noinline__ void seg_store(const SegArgs& A, long long seg, const do
 // Prepare the next (up to) 32 steps of the warp's segment: lane j takes the (j+1)-th delta after `carry`.
 // Returns the number of steps prepared (a prefix of the lanes); fewer than 32 means the walk ends with them.
 template <typename WM>
-__device__ __noinline__ int seg_prepare(const DfsParams& P, WM& M, double vd, double dist, double& carry, bool first,
+__device__ __forceinline__ int seg_prepare(const DfsParams& P, WM& M, double vd, double dist, double& carry, bool first,
                                         int lane) {
   double d = carry, mine = 0.0;
   bool mine_ok = false, ok = true;
@@ -193,6 +193,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) k_transit_dfs(DfsParams P, SegA
       bool done = (fl & F_HAS) && ((fl & F_HIT) || (cur == 0 && !(fl & (F_PL | F_PR))));
       bool hit_now = done && (fl & F_HIT);
       unsigned kmin = __reduce_min_sync(FULL, hit_now ? kstep : NO_HIT);
+      kmin = __shfl_sync(FULL, kmin, 0);  // tells the compiler the value is warp-uniform (it steers the loop)
       if (kmin < hit_k) {
         hit_k = kmin;
         if (hit_now && kstep == kmin) { M.hit_tau = M.lane_tau[0][lane]; M.hit_ptau = M.lane_tau[1][lane]; }
