@@ -155,6 +155,17 @@ int osr_intersecting_to_surface(osr_world* w, int which, const double* q, const 
                                 const int32_t* F, int64_t nF, int64_t cap, int32_t* out_faces,
                                 double* out_bary, int64_t* total);
 
+/* Clearance statistics of m key-configuration candidates (replaces the host loop touchq_util.calc_touch +
+ * pyosr.multi_distance + numpy statistics: src/GP/pipeline/touchq_util.py:8-27, preprocess_key.py:174-184 and
+ * :275-281, keyconf.py:312-315; lib/osr/osr_state.cc:157-167).  Candidate c (unit state q0[c]) owns the touch
+ * segments q0[c] -> to[c * npoint + i], i < npoint, walked as by osr_transit_states_to_with_contact with
+ * `verify_delta`; d_i = osr::distance(q0[c], last free state of segment i).
+ * stats[c][5] = {median, max, min, mean, std} of d (numpy conventions: median of an even count is the mean of
+ * the two middle values, std is the population deviation); distances[m * npoint] optional (may be NULL).
+ * 1 <= npoint <= 8192.  Candidates are sharded over the devices of the handle. */
+int osr_clearance_stats(osr_world* w, const double* q0, int64_t m, const double* to, int npoint,
+                        double verify_delta, double* stats, double* distances);
+
 /* k nearest states under osr::distance (lib/osr/osr_state.cc:130-154) inside windows of `window` consecutive
  * indices (a positive multiple of 256; the last window may be short), the query itself excluded: the k-NN edge
  * generator of the RDT-forest edge-validation workload.  out_idx[n][k] = global indices ordered by

@@ -21,6 +21,7 @@
 #include "kernels_surface.cuh"
 #include "kernels_knn.cuh"
 #include "kernels_raster.cuh"
+#include "kernels_clearance.cuh"
 
 namespace {
 
@@ -82,6 +83,7 @@ struct Slot {  // one GPU
   int spill_cap = 0;
   DevBuf in0, in1, vd, out[6], recs, rowrec, seg, faces, cop, bary;
   DevBuf surf_v, surf_f, surf_flags, surf_cnt, surf_off, surf_face, surf_l;  // K5 (kernels_surface.cuh)
+  DevBuf clr_q0, clr_stats, clr_dist;                                         // K8 (kernels_clearance.cuh)
 };
 
 }  // namespace
@@ -160,6 +162,7 @@ void free_slot(Slot& s) {
   for (auto& b : s.out) b.release();
   s.surf_v.release(); s.surf_f.release(); s.surf_flags.release(); s.surf_cnt.release(); s.surf_off.release();
   s.surf_face.release(); s.surf_l.release();
+  s.clr_q0.release(); s.clr_stats.release(); s.clr_dist.release();
   s.recs.release(); s.rowrec.release(); s.seg.release(); s.faces.release(); s.cop.release(); s.bary.release();
   if (s.ev0) cudaEventDestroy(s.ev0);
   if (s.ev1) cudaEventDestroy(s.ev1);
@@ -1256,6 +1259,65 @@ int osr_knn_windowed(osr_world* w, const double* q, int64_t n, int k, int64_t wi
   CU(cudaMemcpyAsync(out_idx, s.faces.p, (size_t)n * k * 4, cudaMemcpyDeviceToHost, s.stream));
   if (out_dist) CU(cudaMemcpyAsync(out_dist, s.seg.p, (size_t)n * k * 8, cudaMemcpyDeviceToHost, s.stream));
   CU(cudaStreamSynchronize(s.stream));
+  return OSR_OK;
+}
+
+// ---- clearance statistics of key-configuration candidates ----------------------
+// calc_touch + multi_distance + [median, max, min, mean, std] per candidate (preprocess_key.py:174-184,275-281):
+// candidates are sharded over the devices, every device walks its candidates' touch segments (K2) and reduces
+// the last free states in place (K8); 40 bytes per candidate come back instead of npoint x 15 doubles.
+int osr_clearance_stats(osr_world* w, const double* q0, int64_t m, const double* to, int npoint, double verify_delta,
+                        double* stats, double* distances) {
+  int rc = check_ready(w);
+  if (rc) return rc;
+  if (m < 0 || npoint <= 0 || npoint > osr::CLR_MAX_POINTS || (m > 0 && (!q0 || !to || !stats)) || !(verify_delta > 0.0))
+    return fail(OSR_EINVAL, "bad arguments (1 <= npoint <= 8192, verify_delta > 0)");
+  if (m == 0) return OSR_OK;
+  std::lock_guard<std::mutex> lk(w->mu);
+  int padded = 1;
+  while (padded < npoint) padded <<= 1;
+  const size_t smem = (size_t)padded * 8;
+  int parts = (int)w->slots.size();
+  for (int i = 0; i < parts; i++) {
+    Slot& s = w->slots[i];
+    int64_t lo, hi;
+    shard(m, parts, i, lo, hi);
+    const int64_t mc = hi - lo, n = mc * npoint;
+    if (mc == 0) continue;
+    CU(cudaSetDevice(s.dev));
+    CU(s.clr_q0.need((size_t)mc * 56));
+    CU(s.in0.need((size_t)n * 56));
+    CU(s.in1.need((size_t)n * 56));
+    CU(s.out[0].need((size_t)n * 56));
+    CU(s.clr_stats.need((size_t)mc * 40));
+    if (distances) CU(s.clr_dist.need((size_t)n * 8));
+    CU(cudaMemcpyAsync(s.clr_q0.p, q0 + 7 * lo, (size_t)mc * 56, cudaMemcpyHostToDevice, s.stream));
+    CU(cudaMemcpyAsync(s.in1.p, to + 7 * lo * npoint, (size_t)n * 56, cudaMemcpyHostToDevice, s.stream));
+    const long long total = (long long)n * 7;
+    osr::k_repeat_states<<<(unsigned)((total + 255) / 256), 256, 0, s.stream>>>((const double*)s.clr_q0.p, (long long)mc,
+                                                                               npoint, (double*)s.in0.p);
+    CU(cudaGetLastError());
+    w->host_counters.kernel_launches++;
+    osr::SegOut O = {(double*)s.out[0].p, nullptr, nullptr, nullptr, nullptr, nullptr};
+    rc = launch_transit(w, s, (const double*)s.in0.p, (const double*)s.in1.p, n, nullptr, 1, verify_delta, 0, O);
+    if (rc) return rc;
+    if (smem > 48 * 1024)
+      CU(cudaFuncSetAttribute(osr::k_clearance_stats, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    osr::k_clearance_stats<<<(unsigned)mc, osr::CLR_THREADS, smem, s.stream>>>(
+        (const double*)s.clr_q0.p, (const double*)s.out[0].p, npoint, padded, (double*)s.clr_stats.p,
+        distances ? (double*)s.clr_dist.p : nullptr);
+    CU(cudaGetLastError());
+    w->host_counters.kernel_launches++;
+    CU(cudaMemcpyAsync(stats + 5 * lo, s.clr_stats.p, (size_t)mc * 40, cudaMemcpyDeviceToHost, s.stream));
+    if (distances)
+      CU(cudaMemcpyAsync(distances + lo * npoint, s.clr_dist.p, (size_t)n * 8, cudaMemcpyDeviceToHost, s.stream));
+  }
+  for (int i = 0; i < parts; i++) {
+    Slot& s = w->slots[i];
+    CU(cudaSetDevice(s.dev));
+    rc = check_device_error(w, s);
+    if (rc) return rc;
+  }
   return OSR_OK;
 }
 

@@ -595,6 +595,25 @@ class UnitWorld:
         keep = dst >= 0
         return np.ascontiguousarray(q[src[keep]]), np.ascontiguousarray(q[dst[keep]])
 
+    # ---- clearance statistics (touchq_util.calc_touch + preprocess_key.py:275-281 on the device) ----
+    def clearance_stats(self, q0, to, verify_delta=None, with_distances=False):
+        """For every candidate unit state q0[c] and its touch targets to[c, i] (shape [M, npoint, 7]; build them
+        with pyosr.apply as touchq_util.sample_one_touch does): walk q0[c] -> to[c, i] until first contact and
+        return float64[M, 5] = [median, max, min, mean, std] of pyosr.multi_distance(q0[c], FREE_V) -- the row
+        preprocess_key.py keeps per candidate -- and, when asked, the distances themselves
+        (keyconf.estimate_keyconf_clearance's DISTANCE_BATCH)."""
+        q = _states(q0)
+        t = np.ascontiguousarray(np.asarray(to, dtype=np.float64))
+        if t.ndim != 3 or t.shape[0] != len(q) or t.shape[2] != 7:
+            raise ValueError("`to` must have shape [len(q0), npoint, 7]")
+        npoint = t.shape[1]
+        vd = self.recommended_cres if verify_delta is None else float(verify_delta)
+        stats = np.empty((len(q), 5))
+        dist = np.empty((len(q), npoint)) if with_distances else None
+        check(self._L.osr_clearance_stats(self._h, _p(q, c_dp), len(q), _p(t, c_dp), int(npoint), vd,
+                                          _p(stats, c_dp), _p(dist, c_dp)))
+        return (stats, dist) if with_distances else stats
+
     # ---- surface mapping (module.cc: intersecting_to_robot_surface / intersecting_to_model_surface) ----
     def _to_surface(self, which, q, q_is_unit, V, F):
         """unit_world.cc:928-957 + 1092-1176 -> (faces int32[K,3], barycentrics float64[3K,3])."""

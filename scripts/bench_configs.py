@@ -5,7 +5,7 @@ Every leg goes through the C ABI (`libosrgpu.so`) with HOST buffers, is timed by
 (copies included), and a prefix of its output is compared with the CPU oracle (test infrastructure, used here
 only as the checker and as the timed CPU baseline).  One JSON line per leg; keep the output under profiles/.
 
-    python scripts/bench_configs.py [--legs touch,touch_fine,edges,hipoly,contacts] [--scale 1.0]
+    python scripts/bench_configs.py [--legs touch,touch_fine,edges,hipoly,contacts,clearance] [--scale 1.0]
 """
 import argparse
 import json
@@ -164,15 +164,43 @@ def leg_contacts(O, scale):
             "cpu_port": {"states_per_s": m / dtc, "contacts_per_s": k / dtc, "threads": 1}}
 
 
+def leg_clearance(O, scale):
+    """clearance statistics of key-configuration candidates on G-wt2 -- npoint touch segments per
+    candidate at the pipeline's recommended_cres, reduced on the device to [median, max, min, mean, std]."""
+    uw = world(pyosr.UnitWorld, "wt2", W.ROB_OMPL_CENTER)
+    ow = world(O.OracleWorld, "wt2", W.ROB_OMPL_CENTER)
+    tv = np.load(os.path.join(A, "alpha-1.2.org.tunnel-more.npz"))["TUNNEL_V"]
+    m, npoint, vd = max(1, int(64 * scale)), 1024, 1.5164e-5
+    q0 = np.ascontiguousarray(uw.translate_to_unit_states(tv)[:m])
+    m = len(q0)
+    fr, to = W.touch_rays(np.repeat(q0, npoint, axis=0), m * npoint, seed=5)
+    to = to.reshape(m, npoint, 7)
+    (stats, dist), dt = timed(lambda: uw.clearance_stats(q0, to, vd, with_distances=True))
+    _, dt_stats_only = timed(lambda: uw.clearance_stats(q0, to, vd))
+    k = 64
+    tc = time.perf_counter()
+    olf = ow.transit_states_to_with_contact(fr[:k], to[0, :k], vd)[0]
+    od = np.array([O.distance(q0[0], s) for s in olf])
+    dtc = time.perf_counter() - tc
+    want = np.stack([np.median(dist, 1), dist.max(1), dist.min(1), dist.mean(1), dist.std(1)], axis=1)
+    return {"leg": "clearance", "geometry": "G-wt2", "candidates": m, "points_per_candidate": npoint,
+            "verify_delta": vd, "candidates_per_s": m / dt_stats_only, "segments_per_s": m * npoint / dt_stats_only,
+            "seconds": dt_stats_only, "seconds_with_distances": dt,
+            "d2h_bytes": 40 * m, "d2h_bytes_reference_layout": 15 * 8 * m * npoint,
+            "max_abs_stat_error_vs_numpy": float(np.abs(stats - want).max()),
+            "oracle_prefix_segments": k, "max_abs_distance_error_vs_oracle_on_prefix": float(np.abs(dist[0, :k] - od).max()),
+            "cpu_port": {"segments_per_s": k / dtc, "threads": O.lib().orc_max_threads()}}
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--legs", default="touch,touch_fine,edges,hipoly,contacts")
+    ap.add_argument("--legs", default="touch,touch_fine,edges,hipoly,contacts,clearance")
     ap.add_argument("--scale", type=float, default=1.0)
     args = ap.parse_args()
     from oracle import oracle as O
     legs = {"touch": lambda: leg_touch(O, args.scale), "touch_fine": lambda: leg_touch(O, args.scale, fine=True),
             "edges": lambda: leg_edges(O, args.scale), "hipoly": lambda: leg_hipoly(O, args.scale),
-            "contacts": lambda: leg_contacts(O, args.scale)}
+            "contacts": lambda: leg_contacts(O, args.scale), "clearance": lambda: leg_clearance(O, args.scale)}
     for name in args.legs.split(","):
         t = time.perf_counter()
         try:

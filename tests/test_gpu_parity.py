@@ -554,3 +554,37 @@ def test_ompl_frame_validators_match_restatement(shift, oracle_mod):
     assert not g2.any()
     g3, n3 = uw.ompl_validate_motion_pairs(a[:8], a[:8], extent, res, with_counts=True)
     assert g3.all() and (n3 == 0).all()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("npoint", [96, 257, 4096])
+def test_clearance_stats_match_oracle_and_numpy(npoint, uw_wt2, ow_wt2, oracle_mod):
+    """N3: calc_touch + multi_distance + [median, max, min, mean, std] per candidate (touchq_util.py:8-27,
+    preprocess_key.py:275-281) reduced on the device, against the oracle's segment walk + numpy statistics.
+    Order statistics are exact; mean / std to 1e-13 relative (summation order); even, odd and power-of-two counts."""
+    import os
+    tv = np.load(os.path.join(W.assets_dir(), "alpha-1.2.org.tunnel.npz"))["TUNNEL_V"]
+    free = np.concatenate([tv[:, :3] * uw_wt2.scene_scale, tv[:, 3:]], axis=1)
+    m = 5 if npoint < 4096 else 2
+    q0 = np.ascontiguousarray(free[3:3 + m])
+    fr, to = W.touch_rays(np.repeat(q0, npoint, axis=0), m * npoint, seed=71 + npoint)
+    assert np.array_equal(fr.reshape(m, npoint, 7)[:, 0], q0)
+    stats, dist = uw_wt2.clearance_stats(q0, to.reshape(m, npoint, 7), VD_TOUCH, with_distances=True)
+    # the same reduction from the product's own segment outputs: exact
+    lf = uw_wt2.transit_states_to_with_contact(fr, to, VD_TOUCH)[0]
+    mo = m if npoint < 4096 else 1          # the oracle walks a bounded prefix of the big case
+    olf = ow_wt2.transit_states_to_with_contact(fr[:mo * npoint], to[:mo * npoint], VD_TOUCH)[0]
+    assert _close(lf[:mo * npoint], olf)
+    for c in range(m):
+        d = np.array([oracle_mod.distance(q0[c], s) for s in lf[c * npoint:(c + 1) * npoint]])
+        assert np.abs(dist[c] - d).max() < 1e-13
+        want = np.array([np.median(dist[c]), dist[c].max(), dist[c].min(), dist[c].mean(), dist[c].std()])
+        assert np.array_equal(stats[c, :3], want[:3])
+        assert np.abs(stats[c, 3:] - want[3:]).max() < 1e-13 * max(1.0, want[3])
+        if c < mo:
+            od = np.array([oracle_mod.distance(q0[c], s) for s in olf[c * npoint:(c + 1) * npoint]])
+            ow = np.array([np.median(od), od.max(), od.min(), od.mean(), od.std()])
+            assert np.abs(stats[c] - ow).max() < 1e-12
+    assert stats[:, 2].min() >= 0.0 and (stats[:, 1] > stats[:, 2]).all()
+    with pytest.raises(Exception):
+        uw_wt2.clearance_stats(q0, np.zeros((m, 8193, 7)), VD_TOUCH)
