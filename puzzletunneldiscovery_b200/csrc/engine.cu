@@ -104,6 +104,9 @@ struct osr_world {
   osr_counters host_counters = {};
   bool seg_dfs = false;            // OSR_SEG_KERNEL=dfs: K2 on the lane-owned depth-first traversal
   bool force_tile_kernel = false;  // OSR_VALID_KERNEL=tile: first-generation kernel, kept for A/B measurements
+  int sweep_tiles = 64;            // K2: largest swept window, tiles of 32 steps (OSR_SWEEP_TILES, 0 = off)
+  double rob_radius = 0.0;         // max |p| over the robot's unit-mesh vertices
+  double sweep_rmax = 0.02;        // K2: largest swept radius worth a traversal (OSR_SWEEP_RMAX, unit-scene lengths)
 
   osr::KParams params(const Slot& s) const {
     osr::KParams P;
@@ -112,6 +115,9 @@ struct osr_world {
     P.rob.nodes = s.rob_nodes; P.rob.tris = s.rob_tris;
     P.rob.num_nodes = rob.bvh.num_nodes; P.rob.num_tris = rob.nf();
     osr::state_to_rigid(perturb, P.env_tf);
+    P.rob_radius = rob_radius;
+    P.sweep_tiles = sweep_tiles;
+    P.sweep_rmax = sweep_rmax;
     P.counters = s.counters;
     P.work_counter = s.work;
     P.spill = s.spill;
@@ -355,6 +361,8 @@ int osr_create(osr_world** out) {
   (*out)->force_tile_kernel = k && strcmp(k, "tile") == 0;
   const char* k2 = getenv("OSR_SEG_KERNEL");
   (*out)->seg_dfs = k2 && strcmp(k2, "dfs") == 0;
+  if (const char* k3 = getenv("OSR_SWEEP_TILES")) (*out)->sweep_tiles = std::max(0, std::min(1 << 16, atoi(k3)));
+  if (const char* k4 = getenv("OSR_SWEEP_RMAX")) (*out)->sweep_rmax = std::max(0.0, atof(k4));
   return OSR_OK;
 }
 
@@ -415,6 +423,10 @@ int osr_finalize(osr_world* w, const int* devices, int ndev) {
     // UnitWorld::angleModel(0,0) (unit_world.cc:137-161) -> CDModel (cdmodel.cc:85-160)
     osr::make_unit_model(w->env_mesh, w->scene_scale, nullptr, w->env);
     osr::make_unit_model(w->rob_mesh, w->scene_scale, w->centre, w->rob);
+    double r2 = 0.0;
+    for (size_t v = 0; v + 2 < w->rob.V.size(); v += 3)
+      r2 = std::max(r2, w->rob.V[v] * w->rob.V[v] + w->rob.V[v + 1] * w->rob.V[v + 1] + w->rob.V[v + 2] * w->rob.V[v + 2]);
+    w->rob_radius = std::sqrt(r2) * (1.0 + 1e-12);
     osr::build_gpu_bvh(w->env);
     osr::build_gpu_bvh(w->rob);
     if (w->env.bvh.num_nodes >= (1 << 27) || w->rob.bvh.num_nodes >= (1 << 27))

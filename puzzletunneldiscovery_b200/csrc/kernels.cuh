@@ -45,6 +45,9 @@ struct KParams {
   unsigned long long* spill;         // [total_warps][spill_cap]
   int spill_cap;
   int* error_flag;                   // set to 1 on spill exhaustion
+  double rob_radius;                 // max |p| over the robot's unit-mesh vertices (swept windows of K2)
+  int sweep_tiles;                   // K2: largest swept window in tiles of 32 steps (0 = every step traversed)
+  double sweep_rmax;                 // K2: windows whose swept radius exceeds this are not attempted
 };
 
 constexpr int STACK_CAP = 512;   // shared-memory stack entries per warp
@@ -74,7 +77,7 @@ __device__ __forceinline__ unsigned entry_n2(unsigned long long e) { return (uns
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ bool obb_overlap_f32(const float4 a0, const float4 a1, const float4 a2, const float4 a3,
                                                 const float4 b0, const float4 b1, const float4 b2, const float4 b3,
-                                                const float* __restrict__ Rf, float eta) {
+                                                const float* __restrict__ Rf, float eta, float infl = 0.0f) {
   const float reps = 2e-5f;
   float r0 = Rf[0 * 32], r1 = Rf[1 * 32], r2 = Rf[2 * 32], r3 = Rf[3 * 32], r4 = Rf[4 * 32], r5 = Rf[5 * 32],
         r6 = Rf[6 * 32], r7 = Rf[7 * 32], r8 = Rf[8 * 32];
@@ -103,7 +106,7 @@ __device__ __forceinline__ bool obb_overlap_f32(const float4 a0, const float4 a1
   float F10 = fabsf(B10) + reps, F11 = fabsf(B11) + reps, F12 = fabsf(B12) + reps;
   float F20 = fabsf(B20) + reps, F21 = fabsf(B21) + reps, F22 = fabsf(B22) + reps;
   float ea0 = a3.x + eta, ea1 = a3.y + eta, ea2 = a3.z + eta;
-  float eb0 = b3.x + eta, eb1 = b3.y + eta, eb2 = b3.z + eta;
+  float eb0 = b3.x + eta + infl, eb1 = b3.y + eta + infl, eb2 = b3.z + eta + infl;
   bool sep = false;
   sep |= fabsf(T0) > ea0 + fmaf(F00, eb0, fmaf(F01, eb1, F02 * eb2));
   sep |= fabsf(T1) > ea1 + fmaf(F10, eb0, fmaf(F11, eb1, F12 * eb2));
@@ -438,6 +441,66 @@ __device__ __forceinline__ unsigned traverse_tile(const KParams& P, WarpShared& 
   return hits;
 }
 
+// Swept window of a segment walk: true when NO leaf box pair of the two trees overlaps with the robot at the pose
+// of slot 0 and every robot box grown by `infl`.  When infl bounds the displacement of every robot point between
+// that pose and each pose of a window of steps, no triangle pair can intersect at any of those steps (triangles
+// lie inside their leaf boxes), so the reference's per-step checks (unit_world.cc:445-470) all return "free" and
+// the walk may advance over the window without traversing its steps one by one.  A false return proves nothing:
+// the caller narrows the window or walks the steps exactly.  Bounded work: gives up after `max_iter` rounds or when
+// the stack would spill.
+__device__ __forceinline__ bool swept_clear(const KParams& P, WarpShared& S, WarpCtx& C, int lane, float infl,
+                                            int max_iter) {
+  const unsigned ltmask = (1u << lane) - 1u;
+  int top = 1;
+  if (lane == 0) S.stack[0] = make_entry(0, 0, 0);
+  __syncwarp();
+  for (int it = 0; top > 0; it++) {
+    if (it >= max_iter || top > STACK_CAP - 64) return false;
+    const int cnt = min(32, top);
+    const bool act = lane < cnt;
+    unsigned long long e = act ? S.stack[top - 1 - lane] : 0ull;
+    top -= cnt;
+    __syncwarp();
+    bool leafpair = false, expand = false;
+    unsigned long long c0 = 0, c1 = 0;
+    if (act) {
+      C.n_bv++;
+      const unsigned n1 = entry_n1(e), n2 = entry_n2(e);
+      const float4* na = P.env.nodes + (size_t)4 * n1;
+      const float4* nb = P.rob.nodes + (size_t)4 * n2;
+      float4 a0 = ldg4(na), a1 = ldg4(na + 1), a2 = ldg4(na + 2), a3 = ldg4(na + 3);
+      float4 b0 = ldg4(nb), b1 = ldg4(nb + 1), b2 = ldg4(nb + 2), b3 = ldg4(nb + 3);
+      if (obb_overlap_f32(a0, a1, a2, a3, b0, b1, b2, b3, &S.Rf[0][0], S.eta[0], infl)) {
+        int l1 = __float_as_int(a3.w), l2 = __float_as_int(b3.w);
+        if (l1 < 0 && l2 < 0) {
+          leafpair = true;
+        } else {
+          expand = true;
+          float s1 = a3.x * a3.x + a3.y * a3.y + a3.z * a3.z;
+          float s2 = b3.x * b3.x + b3.y * b3.y + b3.z * b3.z;
+          if (l2 < 0 || (l1 >= 0 && s1 > s2)) {
+            c0 = make_entry(0, (unsigned)l1, n2);
+            c1 = make_entry(0, (unsigned)l1 + 1u, n2);
+          } else {
+            c0 = make_entry(0, n1, (unsigned)l2);
+            c1 = make_entry(0, n1, (unsigned)l2 + 1u);
+          }
+        }
+      }
+    }
+    if (__any_sync(FULL, leafpair)) return false;
+    unsigned be = __ballot_sync(FULL, expand);
+    if (expand) {
+      int off = top + 2 * __popc(be & ltmask);
+      S.stack[off] = c0;
+      S.stack[off + 1] = c1;
+    }
+    top += 2 * __popc(be);
+    __syncwarp();
+  }
+  return true;
+}
+
 // Fill pose slot `lane` from a unit state.
 __device__ __forceinline__ void set_pose(const KParams& P, WarpShared& S, int lane, const double* q) {
   Rigid rob, rel;
@@ -563,7 +626,65 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB)
       double prev_tau = 0.0;    // tau of that step
       long long k0 = 0;         // steps completed before this tile
       bool done = false;
+      // swept windows (see swept_clear): a robot point moves at most `rate` per unit of tau -- |dt| along the
+      // translation plus (rotation angle) x (largest vertex radius) along the slerp arc; dist = |dt| + angle.
+      const double tdx = a[0] - b[0], tdy = a[1] - b[1], tdz = a[2] - b[2];
+      const double trans = sqrt(tdx * tdx + tdy * tdy + tdz * tdz);
+      const double rate = (trans + (fmax(dist - trans, 0.0) + 1e-12) * P.rob_radius) * (1.0 + 1e-9);
+      // tiles per window: doubles after a cleared window, halves after a failed one; never wider than the window
+      // whose radius reaches sweep_rmax (a robot grown by more than that is not expected to clear anything), and no
+      // attempts at all when a single tile already exceeds it (coarse walks)
+      const double tile_radius = 16.0 * vd * inv_dist * rate;
+      const int win_cap = (int)fmin((double)P.sweep_tiles, P.sweep_rmax / tile_radius);
+      int win = min(4, win_cap);
+      int fails = 0;
       while (!done) {
+        if (win > 0 && (fails < 1 || ((k0 >> 5) & 7) == 0)) {
+          // the window's steps have delta in (carry, carry + 32 win vd] up to the rounding of the running sum
+          const int ns = 32 * win;
+          const double tau_lo = carry * inv_dist;
+          const double tau_hi = fmin(1.0, (carry + (double)ns * vd) * inv_dist * (1.0 + 1e-6));
+          const double radius = 0.5 * (tau_hi - tau_lo) * rate * (1.0 + 1e-9) + 1e-6;
+          if (lane == 0) {
+            double s[7];
+            interpolate(a, b, 0.5 * (tau_lo + tau_hi), s);
+            set_pose(P, S, 0, s);
+          }
+          __syncwarp();
+          const bool clear = swept_clear(P, S, C, lane, __double2float_ru(radius), 96);
+          __syncwarp();
+          if (clear) {
+            double d = carry, last = carry;
+            int valid = 0;
+            for (int j = 0; j < ns; j++) {   // the reference's running sum, add by add
+              const double t = d + vd;
+              d = (d < dist) ? fmin(dist, t) : t;
+              if (!(d <= dist)) break;
+              valid++;
+              last = d;
+            }
+            carry = d;
+            nposes += valid;
+            k0 += valid;
+            if (valid > 0) prev_tau = last * inv_dist;
+            if (valid < ns) {  // walked past dist: the whole segment is free
+              free_tau = prev_tau;
+              touch_tau = 0.0;
+              interpolate(a, b, prev_tau, lf);
+#pragma unroll
+              for (int k = 0; k < 7; k++) fh[k] = lf[k];
+              steps = k0;
+              free_flag = true;
+              done = true;
+            } else {
+              win = min(2 * win, win_cap);
+              fails = 0;
+            }
+            continue;
+          }
+          if (win > 1) { win >>= 1; continue; }
+          fails++;
+        }
         // step deltas of this tile: lane j takes the (j+1)-th value after `carry`.  The chain of fp64 adds is
         // inherently serial (the reference's running sum, rounding included), so all lanes run it; it is kept to
         // add / compare / select per step: with carry = 0 the first value is 0 + vd = vd exactly, and since the

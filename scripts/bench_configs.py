@@ -90,6 +90,7 @@ def leg_edges(O, scale):
     same_edges = {(a.tobytes(), b.tobytes()) for a, b in zip(hfr, hto)} == \
         {(a.tobytes(), b.tobytes()) for a, b in zip(fr[:8 * 4096], to[:8 * 4096])}
     vd = 1.51641e-5
+    uw.counters(reset=True)     # the timed call runs twice (warm-up + measurement): counters below are halved
     res, dt = timed(lambda: uw.is_valid_transitions(fr, to, vd))
     m = 256
     tc = time.perf_counter()
@@ -101,6 +102,8 @@ def leg_edges(O, scale):
             "gpu_knn_seconds": t_knn, "knn_edges_per_s": len(fr) / t_knn,
             "knn_first_window_equals_host_restatement": bool(same_edges), "oracle_prefix": m,
             "labels_equal_oracle_on_prefix": bool(np.array_equal(res[:m], ores.astype(bool))),
+            "steps_reference_semantics": int(c["poses"]) // 2, "box_tests_per_step": c["bv_tests"] / max(1, c["poses"]),
+            "validity_checks_per_s": c["poses"] / dt / 2,
             "cpu_port": {"edges_per_s": m / dtc, "validity_checks_per_s": float(ocnt[:, 0].sum()) / dtc,
                          "threads": O.lib().orc_max_threads()}}
 
