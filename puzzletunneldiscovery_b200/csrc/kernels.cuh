@@ -77,7 +77,7 @@ __device__ __forceinline__ unsigned entry_n2(unsigned long long e) { return (uns
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ bool obb_overlap_f32(const float4 a0, const float4 a1, const float4 a2, const float4 a3,
                                                 const float4 b0, const float4 b1, const float4 b2, const float4 b3,
-                                                const float* __restrict__ Rf, float eta, float infl = 0.0f) {
+                                                const float* __restrict__ Rf, float eta) {
   const float reps = 2e-5f;
   float r0 = Rf[0 * 32], r1 = Rf[1 * 32], r2 = Rf[2 * 32], r3 = Rf[3 * 32], r4 = Rf[4 * 32], r5 = Rf[5 * 32],
         r6 = Rf[6 * 32], r7 = Rf[7 * 32], r8 = Rf[8 * 32];
@@ -106,7 +106,7 @@ __device__ __forceinline__ bool obb_overlap_f32(const float4 a0, const float4 a1
   float F10 = fabsf(B10) + reps, F11 = fabsf(B11) + reps, F12 = fabsf(B12) + reps;
   float F20 = fabsf(B20) + reps, F21 = fabsf(B21) + reps, F22 = fabsf(B22) + reps;
   float ea0 = a3.x + eta, ea1 = a3.y + eta, ea2 = a3.z + eta;
-  float eb0 = b3.x + eta + infl, eb1 = b3.y + eta + infl, eb2 = b3.z + eta + infl;
+  float eb0 = b3.x + eta, eb1 = b3.y + eta, eb2 = b3.z + eta;
   bool sep = false;
   sep |= fabsf(T0) > ea0 + fmaf(F00, eb0, fmaf(F01, eb1, F02 * eb2));
   sep |= fabsf(T1) > ea1 + fmaf(F10, eb0, fmaf(F11, eb1, F12 * eb2));
@@ -164,6 +164,42 @@ __device__ __forceinline__ void axis_gaps(const T* ax, const Tri6<T>& t, T& g1, 
   T mnQ = min3<T>(Q1, Q2, Q3), mxQ = max3<T>(Q1, Q2, Q3);
   g1 = mnP - mxQ;
   g2 = mnQ - mxP;
+}
+
+// Swept windows of K2: true when one of the 11 face-normal / edge x edge axes separates the two triangles by MORE
+// than r (projection gap > r |axis|).  Then the triangles stay strictly apart, along that fixed direction, however
+// the points of one of them move by at most r.  fp64; the caller's r carries an absolute slack far above rounding.
+__device__ __noinline__ bool tri_gap_clear(const Tri6<double>& t, double r) {
+  double e0[3], e1[3], e2[3], f0[3], f1[3], f2[3], ax[3], g1, g2;
+#pragma unroll
+  for (int k = 0; k < 3; k++) {
+    e0[k] = t.p2[k]; e1[k] = t.p3[k] - t.p2[k]; e2[k] = -t.p3[k];
+    f0[k] = t.q2[k] - t.q1[k]; f1[k] = t.q3[k] - t.q2[k]; f2[k] = t.q1[k] - t.q3[k];
+  }
+  const double rr = r * r * (1.0 + 1e-9);
+  crossT(e0, e1, ax);
+  axis_gaps(ax, t, g1, g2);
+  double g = fmax(g1, g2);
+  if (g > 0.0 && g * g > rr * dotT(ax, ax)) return true;
+  crossT(f0, f1, ax);
+  axis_gaps(ax, t, g1, g2);
+  g = fmax(g1, g2);
+  if (g > 0.0 && g * g > rr * dotT(ax, ax)) return true;
+#pragma unroll 1
+  for (int a = 0; a < 9; a++) {
+    const int i = a / 3, j = a - 3 * i;
+    double u[3], w[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+      u[k] = i == 0 ? e0[k] : (i == 1 ? e1[k] : e2[k]);
+      w[k] = j == 0 ? f0[k] : (j == 1 ? f1[k] : f2[k]);
+    }
+    crossT(u, w, ax);
+    axis_gaps(ax, t, g1, g2);
+    g = fmax(g1, g2);
+    if (g > 0.0 && g * g > rr * dotT(ax, ax)) return true;
+  }
+  return false;
 }
 
 // Exact restatement (fp64, reference operation order) -> true iff no axis separates.
@@ -315,12 +351,15 @@ struct ContactRec {
 
 __device__ __forceinline__ unsigned contact_multiplicity_dev(const double* P, const double* Q, const double* Rd);
 
-enum { MODE_VALID = 0, MODE_SEGMENT = 1, MODE_CONTACTS = 2 };
+enum { MODE_VALID = 0, MODE_SEGMENT = 1, MODE_CONTACTS = 2, MODE_SWEPT = 3 };
 
 // alive: bit p set = pose p takes part.  Returns the mask of poses with at least one
 // intersecting triangle pair.  MODE_SEGMENT: once pose p hits, poses >= p are abandoned (only
 // the FIRST colliding step matters, unit_world.cc:452-458).  MODE_CONTACTS: no early out, every
-// intersecting pair is appended to `recs`.
+// intersecting pair is appended to `recs`.  MODE_SWEPT: the poses are the mid poses of consecutive windows of a
+// segment walk, S.eta carries each window's swept radius (boxes) and S.tau the radius itself (triangles); a pose
+// "hits" as soon as one triangle pair is NOT separated by more than the radius along one of its 11 face / edge-edge
+// axes, and then it and all later windows are abandoned.
 template <int MODE>
 __device__ __forceinline__ unsigned traverse_tile(const KParams& P, WarpShared& S, WarpCtx& C, unsigned alive,
                                                   int lane, int state_base = 0, ContactRec* recs = nullptr,
@@ -357,7 +396,8 @@ __device__ __forceinline__ unsigned traverse_tile(const KParams& P, WarpShared& 
         const double* tq = P.rob.tris + (size_t)9 * entry_n2(e);
         Tri6<double> td;
         load_pair_exact(tp, tq, &S.Rd[0][pose], td);
-        hit = tri_pair_intersect(td, C.n_fp64);
+        if (MODE == MODE_SWEPT) hit = !tri_gap_clear(td, S.tau[pose]);
+        else hit = tri_pair_intersect(td, C.n_fp64);
         if (MODE == MODE_CONTACTS && hit) {
           unsigned long long slot = atomicAdd(rec_count, 1ull);
           if (slot < rec_cap) {
@@ -373,8 +413,9 @@ __device__ __forceinline__ unsigned traverse_tile(const KParams& P, WarpShared& 
       unsigned hm = __reduce_or_sync(FULL, hit ? (1u << pose) : 0u);
       hits |= hm;
       if (MODE == MODE_VALID) dead |= hm;
-      else if (MODE == MODE_SEGMENT) { if (hm) dead |= FULL << (__ffs(hm) - 1); }
+      else if (MODE == MODE_SEGMENT || MODE == MODE_SWEPT) { if (hm) dead |= FULL << (__ffs(hm) - 1); }
       __syncwarp();
+      if (MODE == MODE_SWEPT && (dead & alive) == alive) { C.nspill = 0; break; }   // every window abandoned
       continue;
     }
     if (top > STACK_CAP - 32) {  // make room: move the oldest entries to global memory
@@ -439,66 +480,6 @@ __device__ __forceinline__ unsigned traverse_tile(const KParams& P, WarpShared& 
     __syncwarp();
   }
   return hits;
-}
-
-// Swept window of a segment walk: true when NO leaf box pair of the two trees overlaps with the robot at the pose
-// of slot 0 and every robot box grown by `infl`.  When infl bounds the displacement of every robot point between
-// that pose and each pose of a window of steps, no triangle pair can intersect at any of those steps (triangles
-// lie inside their leaf boxes), so the reference's per-step checks (unit_world.cc:445-470) all return "free" and
-// the walk may advance over the window without traversing its steps one by one.  A false return proves nothing:
-// the caller narrows the window or walks the steps exactly.  Bounded work: gives up after `max_iter` rounds or when
-// the stack would spill.
-__device__ __forceinline__ bool swept_clear(const KParams& P, WarpShared& S, WarpCtx& C, int lane, float infl,
-                                            int max_iter) {
-  const unsigned ltmask = (1u << lane) - 1u;
-  int top = 1;
-  if (lane == 0) S.stack[0] = make_entry(0, 0, 0);
-  __syncwarp();
-  for (int it = 0; top > 0; it++) {
-    if (it >= max_iter || top > STACK_CAP - 64) return false;
-    const int cnt = min(32, top);
-    const bool act = lane < cnt;
-    unsigned long long e = act ? S.stack[top - 1 - lane] : 0ull;
-    top -= cnt;
-    __syncwarp();
-    bool leafpair = false, expand = false;
-    unsigned long long c0 = 0, c1 = 0;
-    if (act) {
-      C.n_bv++;
-      const unsigned n1 = entry_n1(e), n2 = entry_n2(e);
-      const float4* na = P.env.nodes + (size_t)4 * n1;
-      const float4* nb = P.rob.nodes + (size_t)4 * n2;
-      float4 a0 = ldg4(na), a1 = ldg4(na + 1), a2 = ldg4(na + 2), a3 = ldg4(na + 3);
-      float4 b0 = ldg4(nb), b1 = ldg4(nb + 1), b2 = ldg4(nb + 2), b3 = ldg4(nb + 3);
-      if (obb_overlap_f32(a0, a1, a2, a3, b0, b1, b2, b3, &S.Rf[0][0], S.eta[0], infl)) {
-        int l1 = __float_as_int(a3.w), l2 = __float_as_int(b3.w);
-        if (l1 < 0 && l2 < 0) {
-          leafpair = true;
-        } else {
-          expand = true;
-          float s1 = a3.x * a3.x + a3.y * a3.y + a3.z * a3.z;
-          float s2 = b3.x * b3.x + b3.y * b3.y + b3.z * b3.z;
-          if (l2 < 0 || (l1 >= 0 && s1 > s2)) {
-            c0 = make_entry(0, (unsigned)l1, n2);
-            c1 = make_entry(0, (unsigned)l1 + 1u, n2);
-          } else {
-            c0 = make_entry(0, n1, (unsigned)l2);
-            c1 = make_entry(0, n1, (unsigned)l2 + 1u);
-          }
-        }
-      }
-    }
-    if (__any_sync(FULL, leafpair)) return false;
-    unsigned be = __ballot_sync(FULL, expand);
-    if (expand) {
-      int off = top + 2 * __popc(be & ltmask);
-      S.stack[off] = c0;
-      S.stack[off + 1] = c1;
-    }
-    top += 2 * __popc(be);
-    __syncwarp();
-  }
-  return true;
 }
 
 // Fill pose slot `lane` from a unit state.
@@ -626,34 +607,58 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB)
       double prev_tau = 0.0;    // tau of that step
       long long k0 = 0;         // steps completed before this tile
       bool done = false;
-      // swept windows (see swept_clear): a robot point moves at most `rate` per unit of tau -- |dt| along the
-      // translation plus (rotation angle) x (largest vertex radius) along the slerp arc; dist = |dt| + angle.
+      // ---- swept windows -------------------------------------------------------------------------------------
+      // A window is a run of consecutive steps.  Between two values of tau a robot point moves at most
+      // |tau - tau'| * rate, rate = |dt| + (rotation angle) x (largest vertex radius): translation is linear in
+      // tau, the slerp arc has constant angular velocity, and dist = |dt| + angle.  If NO pair of leaf boxes
+      // overlaps at the window's mid pose with the boxes grown by the window's radius, no triangle pair can
+      // intersect at any step of the window (triangles lie inside their leaf boxes), so the reference's per-step
+      // checks (unit_world.cc:445-470) all say "free" and the walk advances over the window without traversing
+      // its steps.  A window that does not clear proves nothing: it is split, and single tiles are walked exactly.
+      // One traversal tests up to 32 consecutive windows (one per pose slot, lane-parallel over box pairs).
       const double tdx = a[0] - b[0], tdy = a[1] - b[1], tdz = a[2] - b[2];
       const double trans = sqrt(tdx * tdx + tdy * tdy + tdz * tdz);
       const double rate = (trans + (fmax(dist - trans, 0.0) + 1e-12) * P.rob_radius) * (1.0 + 1e-9);
-      // tiles per window: doubles after a cleared window, halves after a failed one; never wider than the window
-      // whose radius reaches sweep_rmax (a robot grown by more than that is not expected to clear anything), and no
-      // attempts at all when a single tile already exceeds it (coarse walks)
-      const double tile_radius = 16.0 * vd * inv_dist * rate;
-      const int win_cap = (int)fmin((double)P.sweep_tiles, P.sweep_rmax / tile_radius);
-      int win = min(4, win_cap);
+      // steps per window (a power of two >= 4): never wider than the window whose radius reaches sweep_rmax (a
+      // robot grown by more is not expected to clear anything), starts where the radius is a quarter of that,
+      // doubles while everything clears and halves on a blocked window; below 4 steps a tile is walked exactly
+      const double step_radius = 0.5 * vd * inv_dist * rate;
+      const int ws_cap = (int)fmin(32.0 * (double)P.sweep_tiles, P.sweep_rmax / step_radius);
+      int ws = 0;
+      if (ws_cap >= 4) {
+        ws = 4;
+        while (2 * ws <= ws_cap && (double)(2 * ws) * step_radius <= 0.25 * P.sweep_rmax) ws *= 2;
+      }
+      int nb = 4;                  // windows per traversal
       int fails = 0;
+      bool exact_next = false;     // the next tile is known not to clear
       while (!done) {
-        if (win > 0 && (fails < 1 || ((k0 >> 5) & 7) == 0)) {
-          // the window's steps have delta in (carry, carry + 32 win vd] up to the rounding of the running sum
-          const int ns = 32 * win;
-          const double tau_lo = carry * inv_dist;
-          const double tau_hi = fmin(1.0, (carry + (double)ns * vd) * inv_dist * (1.0 + 1e-6));
-          const double radius = 0.5 * (tau_hi - tau_lo) * rate * (1.0 + 1e-9) + 1e-6;
-          if (lane == 0) {
+        if (ws > 0 && !exact_next && (fails < 1 || ((k0 >> 5) & 7) == 0)) {
+          // window `lane` holds the steps whose delta lies in (carry + lane w, carry + (lane + 1) w], w = ws vd,
+          // up to the rounding of the running sum (< 1e-6 relative to w for any vd/dist >= 1e-9)
+          const double w = (double)ws * vd;
+          const double lo = carry + (double)lane * w * (1.0 - 1e-6);
+          const double hi = carry + (double)(lane + 1) * w * (1.0 + 1e-6);
+          const bool mine_w = lane < nb && lo <= dist;
+          if (mine_w) {
+            const double tau_lo = lo * inv_dist, tau_hi = fmin(1.0, hi * inv_dist * (1.0 + 1e-9));
+            const double radius = 0.5 * (tau_hi - tau_lo) * rate * (1.0 + 1e-9) + 1e-6;
             double s[7];
             interpolate(a, b, 0.5 * (tau_lo + tau_hi), s);
-            set_pose(P, S, 0, s);
+            set_pose(P, S, lane, s);
+            // half of the radius on each box: every separating axis gains at least radius x |axis|
+            S.eta[lane] = __fadd_ru(S.eta[lane], __double2float_ru(0.5 * radius));
+            S.tau[lane] = radius;   // triangle-level test of the window (the exact path rewrites tau)
           }
+          const unsigned tried = __ballot_sync(FULL, mine_w);   // a prefix of the lanes
           __syncwarp();
-          const bool clear = swept_clear(P, S, C, lane, __double2float_ru(radius), 96);
+          const unsigned blocked = traverse_tile<MODE_SWEPT>(P, S, C, tried, lane);
+          if (C.overflow) { done = true; break; }
           __syncwarp();
-          if (clear) {
+          const int ntried = __popc(tried);
+          const int cleared = blocked ? __ffs(blocked) - 1 : ntried;
+          if (cleared > 0) {
+            const int ns = cleared * ws;
             double d = carry, last = carry;
             int valid = 0;
             for (int j = 0; j < ns; j++) {   // the reference's running sum, add by add
@@ -676,15 +681,24 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB)
               steps = k0;
               free_flag = true;
               done = true;
-            } else {
-              win = min(2 * win, win_cap);
-              fails = 0;
+              continue;
             }
-            continue;
           }
-          if (win > 1) { win >>= 1; continue; }
-          fails++;
+          if (!blocked) {            // everything tried cleared: widen
+            fails = 0;
+            if (nb < 32) nb *= 2;
+            else if (2 * ws <= ws_cap) ws *= 2;
+          } else if (ws > 4) {       // split the blocked window
+            ws >>= 1;
+            nb = 2;
+          } else {                   // four steps that do not clear: walk the tile step by step
+            exact_next = true;
+            nb = 2;
+            if (cleared == 0) fails++;
+          }
+          continue;
         }
+        exact_next = false;
         // step deltas of this tile: lane j takes the (j+1)-th value after `carry`.  The chain of fp64 adds is
         // inherently serial (the reference's running sum, rounding included), so all lanes run it; it is kept to
         // add / compare / select per step: with carry = 0 the first value is 0 + vd = vd exactly, and since the

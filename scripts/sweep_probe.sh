@@ -1,9 +1,11 @@
 #!/bin/bash
 # A/B of the swept-window parameters of K2 (OSR_SWEEP_TILES x OSR_SWEEP_RMAX) on the segment legs.
 LEGS=${LEGS:-touch,touch_fine,clearance}
-for cfg in "0 0.02" "64 0.005" "64 0.01" "64 0.02"; do set -- $cfg
-  echo "== tiles=$1 rmax=$2"
-  OSR_SWEEP_TILES=$1 OSR_SWEEP_RMAX=$2 python scripts/bench_configs.py --legs $LEGS 2>&1 | grep "^{" | python -c "
+CFGS=${CFGS:-"0:0.02 64:0.005 64:0.01 64:0.02"}
+for cfg in $CFGS; do
+  t=${cfg%%:*}; r=${cfg##*:}
+  echo "== tiles=$t rmax=$r"
+  OSR_SWEEP_TILES=$t OSR_SWEEP_RMAX=$r python scripts/bench_configs.py --legs $LEGS 2>&1 | grep "^{" | python -c "
 import sys, json
 for l in sys.stdin:
     d = json.loads(l)
