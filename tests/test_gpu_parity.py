@@ -588,3 +588,37 @@ def test_clearance_stats_match_oracle_and_numpy(npoint, uw_wt2, ow_wt2, oracle_m
     assert stats[:, 2].min() >= 0.0 and (stats[:, 1] > stats[:, 2]).all()
     with pytest.raises(Exception):
         uw_wt2.clearance_stats(q0, np.zeros((m, 8193, 7)), VD_TOUCH)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("which,vd,n", [("wt2", 0.0125 / 8, 4096), ("wt2", 1.5164e-5, 512), ("org", 1.5164e-5, 512),
+                                         ("org", 3e-4, 2048)])
+def test_swept_windows_leave_every_output_unchanged(which, vd, n, monkeypatch):
+    """K2 advances over windows of steps that one grown-box / triangle-gap traversal proves free
+    (swept windows).  That is a pruning of work, not of semantics: against the same walk with every
+    step traversed (OSR_SWEEP_TILES=0) all six outputs -- first-contact step included -- are bit-identical, on
+    tunnel rays (contact after a long approach) and on k-NN edges between free milestones (mostly free)."""
+    import os
+    from puzzletunneldiscovery_b200 import pyosr
+    centre = W.ROB_OMPL_CENTER if which == "wt2" else None
+    monkeypatch.setenv("OSR_SWEEP_TILES", "0")
+    plain = make_world(pyosr.UnitWorld, which, centre)
+    monkeypatch.delenv("OSR_SWEEP_TILES")
+    swept = make_world(pyosr.UnitWorld, which, centre)
+    if which == "wt2":
+        tv = np.load(os.path.join(W.assets_dir(), "alpha-1.2.org.tunnel.npz"))["TUNNEL_V"]
+        fr, to = W.touch_rays(swept.translate_to_unit_states(tv), n, seed=91)
+    else:
+        q = W.random_states(8 * n, seed=92)
+        ms = q[swept.is_valid_states(q)][: n // 4]
+        fr, to = swept.knn_edges(ms, k=4, window=256)
+    a = swept.transit_states_to_with_contact(fr, to, vd, with_steps=True)
+    swept_boxes = swept.counters(reset=True)["bv_tests"]
+    b = plain.transit_states_to_with_contact(fr, to, vd, with_steps=True)
+    plain_boxes = plain.counters(reset=True)["bv_tests"]
+    for x, y in zip(a, b):
+        assert np.array_equal(x, y)
+    assert 0 < a[2].sum() < len(fr) or which == "wt2"
+    assert np.array_equal(swept.is_valid_transitions(fr, to, vd), plain.is_valid_transitions(fr, to, vd))
+    if vd < 1e-4:
+        assert swept_boxes * 8 < plain_boxes        # and it is where the work goes away
