@@ -141,6 +141,13 @@ int osr_translate_unit_to_ompl(const osr_world* w, const double* q, int64_t n, d
 
 /* module-level state functions (lib/pyosr/module.cc:77-99; lib/osr/osr_state.cc) */
 double osr_distance(const double a[7], const double b[7]);
+/* The step deltas of the segment walk (unit_world.cc:445-470: delta <- delta < dist ? min(dist, delta + vd)
+ * : delta + vd, a running fp64 sum) advanced by up to `nsteps` steps from *delta, stopping at the first value beyond
+ * dist; every rounding of the one-add-per-step loop is reproduced (host build of the routine the segment kernel
+ * uses to advance over swept windows).  Returns the number of steps whose delta is <= dist; *delta = value after the
+ * last executed step, *last_valid = delta of the last valid step (the input delta when there is none). */
+int osr_walk_deltas(double* delta, double verify_delta, double dist, int nsteps, double* last_valid);
+
 void osr_interpolate(const double a[7], const double b[7], double tau, double out[7]);
 void osr_apply(const double from[7], const double tr[3], const double aa[3], double out[7]);
 

@@ -107,6 +107,7 @@ struct osr_world {
   int sweep_tiles = 64;            // K2: largest swept window, tiles of 32 steps (OSR_SWEEP_TILES, 0 = off)
   double rob_radius = 0.0;         // max |p| over the robot's unit-mesh vertices
   double sweep_rmax = 0.02;        // K2: largest swept radius worth a traversal (OSR_SWEEP_RMAX, unit-scene lengths)
+  double sweep_rstart = 0.005;     // K2: swept radius of the first windows of a walk (OSR_SWEEP_RSTART)
 
   osr::KParams params(const Slot& s) const {
     osr::KParams P;
@@ -118,6 +119,7 @@ struct osr_world {
     P.rob_radius = rob_radius;
     P.sweep_tiles = sweep_tiles;
     P.sweep_rmax = sweep_rmax;
+    P.sweep_rstart = sweep_rstart;
     P.counters = s.counters;
     P.work_counter = s.work;
     P.spill = s.spill;
@@ -363,6 +365,7 @@ int osr_create(osr_world** out) {
   (*out)->seg_dfs = k2 && strcmp(k2, "dfs") == 0;
   if (const char* k3 = getenv("OSR_SWEEP_TILES")) (*out)->sweep_tiles = std::max(0, std::min(1 << 16, atoi(k3)));
   if (const char* k4 = getenv("OSR_SWEEP_RMAX")) (*out)->sweep_rmax = std::max(0.0, atof(k4));
+  if (const char* k5 = getenv("OSR_SWEEP_RSTART")) (*out)->sweep_rstart = std::max(0.0, atof(k5));
   return OSR_OK;
 }
 
@@ -1018,6 +1021,12 @@ int osr_translate_unit_to_ompl(const osr_world* w, const double* qin, int64_t n,
 double osr_distance(const double a[7], const double b[7]) { return osr::distance(a, b); }
 void osr_interpolate(const double a[7], const double b[7], double tau, double out[7]) { osr::interpolate(a, b, tau, out); }
 void osr_apply(const double from[7], const double tr[3], const double aa[3], double out[7]) { osr::apply(from, tr, aa, out); }
+int osr_walk_deltas(double* delta, double verify_delta, double dist, int nsteps, double* last_valid) {
+  double last = *delta;
+  int valid = osr::advance_chain(*delta, verify_delta, dist, nsteps, last);
+  if (last_valid) *last_valid = last;
+  return valid;
+}
 
 // ---- visibility (batched isValidTransition) -----------------------------------------------------
 static int visibility_common(osr_world* w, const double* q0, int64_t m, int unit0, const double* q1, int64_t n,

@@ -48,6 +48,7 @@ struct KParams {
   double rob_radius;                 // max |p| over the robot's unit-mesh vertices (swept windows of K2)
   int sweep_tiles;                   // K2: largest swept window in tiles of 32 steps (0 = every step traversed)
   double sweep_rmax;                 // K2: windows whose swept radius exceeds this are not attempted
+  double sweep_rstart;               // K2: swept radius of the first windows of a walk
 };
 
 constexpr int STACK_CAP = 512;   // shared-memory stack entries per warp
@@ -620,14 +621,14 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB)
       const double trans = sqrt(tdx * tdx + tdy * tdy + tdz * tdz);
       const double rate = (trans + (fmax(dist - trans, 0.0) + 1e-12) * P.rob_radius) * (1.0 + 1e-9);
       // steps per window (a power of two >= 4): never wider than the window whose radius reaches sweep_rmax (a
-      // robot grown by more is not expected to clear anything), starts where the radius is a quarter of that,
+      // robot grown by more is not expected to clear anything), starts where the radius is sweep_rstart,
       // doubles while everything clears and halves on a blocked window; below 4 steps a tile is walked exactly
       const double step_radius = 0.5 * vd * inv_dist * rate;
       const int ws_cap = (int)fmin(32.0 * (double)P.sweep_tiles, P.sweep_rmax / step_radius);
       int ws = 0;
       if (ws_cap >= 4) {
         ws = 4;
-        while (2 * ws <= ws_cap && (double)(2 * ws) * step_radius <= 0.25 * P.sweep_rmax) ws *= 2;
+        while (2 * ws <= ws_cap && (double)(2 * ws) * step_radius <= P.sweep_rstart) ws *= 2;
       }
       int nb = 4;                  // windows per traversal
       int fails = 0;
@@ -660,14 +661,7 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB)
           if (cleared > 0) {
             const int ns = cleared * ws;
             double d = carry, last = carry;
-            int valid = 0;
-            for (int j = 0; j < ns; j++) {   // the reference's running sum, add by add
-              const double t = d + vd;
-              d = (d < dist) ? fmin(dist, t) : t;
-              if (!(d <= dist)) break;
-              valid++;
-              last = d;
-            }
+            const int valid = advance_chain(d, vd, dist, ns, last);   // the reference's running sum, rounding included
             carry = d;
             nposes += valid;
             k0 += valid;

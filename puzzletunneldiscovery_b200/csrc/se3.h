@@ -11,6 +11,7 @@
 // the test oracle round identically.
 #pragma once
 #include <math.h>
+#include <string.h>
 
 #if defined(__CUDACC__)
 #define OSR_HD __host__ __device__ __forceinline__
@@ -115,6 +116,78 @@ OSR_HD void apply(const double* from, const double* tr, const double* aa, double
   quat_normalize(q[0], q[1], q[2], q[3]);
   o[0] = from[0] + tr[0]; o[1] = from[1] + tr[1]; o[2] = from[2] + tr[2];
   o[3] = q[0]; o[4] = q[1]; o[5] = q[2]; o[6] = q[3];
+}
+
+OSR_HD long long dbits(double x) {
+#if defined(__CUDA_ARCH__)
+  return __double_as_longlong(x);
+#else
+  long long b;
+  memcpy(&b, &x, 8);
+  return b;
+#endif
+}
+OSR_HD double bits_to_double(long long b) {
+#if defined(__CUDA_ARCH__)
+  return __longlong_as_double(b);
+#else
+  double x;
+  memcpy(&x, &b, 8);
+  return x;
+#endif
+}
+OSR_HD long long imin64(long long a, long long b) { return a < b ? a : b; }
+
+// The reference's running sum over `ns` steps, d <- (d < dist) ? min(dist, d + vd) : d + vd, stopping at the first
+// value beyond dist -- with the result of every fp64 add reproduced exactly but not one add per step.  While d stays
+// inside one binade [2^e, 2^(e+1)) it is a multiple of u = ulp(d), the exact sum d + vd rounds to the multiple of u
+// nearest to it, and unless vd / u ends in exactly one half (a tie, whose rounding depends on the parity of d) that
+// is d + c with the same c for every d of the binade.  So inside a binade k steps are d + k c, computed in integers;
+// binade crossings, the step that reaches dist, ties and d = 0 take ordinary steps.  Returns the number of valid
+// steps (delta <= dist); `last` = delta of the last valid one; `d` = the value after the last executed step.
+OSR_HD int advance_chain(double& d, const double vd, const double dist, const int ns, double& last) {
+  int valid = 0, left = ns;
+  while (left > 0) {
+    int k = 0;
+    long long D = 0, Ci = 0;
+    int e = 0;
+    if (d > 0.0 && d < dist) {
+      const long long bits = dbits(d);
+      e = (int)(bits >> 52);                                      // biased exponent (d > 0: no sign bit)
+      const double t = d + vd;
+      const long long tb = dbits(t);
+      if (e > 0 && e < 2046 && (int)(tb >> 52) == e && t <= dist) {   // normal, same binade, not past dist
+        const double x = scalbn(vd, 53 - (e - 1023));             // 2 vd / u
+        const long long xi = (long long)x;
+        const bool tie = x < 4.0e18 && (double)xi == x && (xi & 1);
+        if (!tie) {
+          D = (bits & 0xfffffffffffffLL) | (1LL << 52);
+          Ci = ((tb & 0xfffffffffffffLL) | (1LL << 52)) - D;      // c / u  (> 0: t > d)
+          if (Ci > 0) {                                           // (vd below half an ulp of d: the sum stalls)
+            long long kk = ((1LL << 53) - 1 - D) / Ci;            // stay inside the binade
+            const long long db = dbits(dist);
+            if ((int)(db >> 52) == e) kk = imin64(kk, (((db & 0xfffffffffffffLL) | (1LL << 52)) - D) / Ci);   // <= dist
+            k = (int)imin64(kk, (long long)left);
+          }
+        }
+      }
+    }
+    if (k > 0) {
+      const long long M = D + (long long)k * Ci;                  // < 2^53, same exponent
+      d = bits_to_double(((long long)e << 52) | (M & 0xfffffffffffffLL));
+      valid += k;
+      left -= k;
+      last = d;
+    } else {
+      const double t = d + vd;
+      d = (d < dist) ? fmin(dist, t) : t;
+      left--;
+      if (!(d <= dist)) break;
+      valid++;
+      last = d;
+    }
+  }
+  return valid;
 }
 
 }  // namespace osr

@@ -24,3 +24,13 @@ if [[ $what == all || $what == ncu ]]; then
   timeout 1500 ncu --set full --clock-control none --import-source on -k regex:k_valid_dfs -s 2 -c 1 -f -o gpurun_out/prof_valid $CMD2 > gpurun_out/ncu_full.log 2>&1
   echo "ncu full rc=$?"; tail -3 gpurun_out/ncu_full.log
 fi
+if [[ $what == all || $what == ncu2 ]]; then
+  # full capture of the segment kernel on the config-2 touch leg (swept windows on)
+  CMD3="python scripts/bench_configs.py --legs touch --scale 0.25"
+  timeout 600 $CMD3 > gpurun_out/ncu_plain3.log 2>&1 &&
+  timeout 1500 ncu --set full --clock-control none --import-source on -k regex:k_transit -s 1 -c 1 -f -o gpurun_out/prof_transit $CMD3 > gpurun_out/ncu_full_transit.log 2>&1
+  echo "ncu transit rc=$?"; tail -3 gpurun_out/ncu_full_transit.log
+fi
+if [[ $what == all || $what == configs ]]; then
+  timeout 1200 python scripts/bench_configs.py 2> gpurun_out/configs.err | grep "^{" > gpurun_out/configs_2_to_5.jsonl; echo "configs lines: $(wc -l < gpurun_out/configs_2_to_5.jsonl)"
+fi

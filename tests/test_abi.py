@@ -176,3 +176,45 @@ def test_vanilla_frames_and_matrices():
     assert np.allclose(w.robot_matrix[:3, 3], -s * np.asarray(W.ROB_OMPL_CENTER), rtol=1e-6)
     p = w.translate_vanilla_pts_to_unit(w.GEO_ROB, oc[None])
     assert np.abs(p).max() < 1e-12 and w.translate_vanilla_pts_to_unit(w.GEO_ENV, np.ones((2, 3))).shape == (2, 3)
+
+
+def _serial_walk(d, vd, dist, ns):
+    """unit_world.cc:445-470's running sum, one fp64 add per step (Python floats are IEEE doubles)."""
+    valid, last = 0, d
+    for _ in range(ns):
+        t = d + vd
+        d = min(dist, t) if d < dist else t
+        if not d <= dist:
+            break
+        valid += 1
+        last = d
+    return d, valid, last
+
+
+def test_walk_deltas_reproduce_every_rounding_of_the_running_sum():
+    """K2 advances over swept windows with osr::advance_chain (k steps inside one binade = one integer
+    multiply-add); here its host build is compared bit for bit with the one-add-per-step loop: random walks, walks
+    that cross binades and reach dist, and the tie case (vd / ulp(d) ending in exactly one half) where the
+    per-step increment is NOT constant."""
+    L = _lib.load()
+    rs = np.random.RandomState(5)
+    cases = []
+    for _ in range(400):
+        vd = float(10.0 ** rs.uniform(-6, -1) * rs.uniform(1, 2))
+        dist = float(vd * 10.0 ** rs.uniform(0.01, 4.5))
+        start = float(rs.choice([0.0, vd, vd * rs.randint(1, 2000)]))
+        cases.append((start, vd, dist, int(rs.choice([1, 4, 32, 128, 2048, 65536]))))
+    for e in range(-12, 1):       # ties: the lowest set bit of vd is half an ulp of d in the binade above vd's
+        vd = float(np.ldexp(1.0 + 2.0 ** -52 * (2 * rs.randint(1, 1 << 20) + 1), e))
+        cases += [(0.0, vd, vd * 37.3, 64), (vd, vd, vd * 1000.0, 4096), (2 * vd, vd, 2.5 * vd, 8)]
+    cases += [(0.0, 0.25, 1.0, 16), (0.0, 0.1, 0.3, 16), (0.7, 0.1, 0.5, 4), (1.0, 1e-17, 2.0, 100),
+              (0.0, 1.5164e-5, 0.0831, 8192), (0.05, 1.5164e-5, 0.05 + 1.5164e-5 * 0.5, 64)]
+    fast_steps = 0
+    for start, vd, dist, ns in cases:
+        d = C.c_double(start)
+        last = C.c_double(-1.0)
+        valid = L.osr_walk_deltas(C.byref(d), vd, dist, ns, C.byref(last))
+        wd, wvalid, wlast = _serial_walk(start, vd, dist, ns)
+        assert (valid, d.value.hex(), last.value.hex()) == (wvalid, wd.hex(), wlast.hex()), (start, vd, dist, ns)
+        fast_steps += valid
+    assert fast_steps > 100000
