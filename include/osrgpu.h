@@ -129,7 +129,8 @@ int osr_intersecting_segments(osr_world* w, const double* q, int64_t n, int64_t 
 
 /* UnitWorld::enumFreeConfiguration per row (unit_world.cc:1340-1389): pts[b] = {rob_o, rob_n,
  * env_o, env_n} (4x3 doubles).  out_q[b][den][7], out_valid[b][den] (after the optional
- * median-of-run filter), counts[b] = number of valid entries. */
+ * median-of-run filter), counts[b] = number of valid entries.  The candidates are built, labelled and
+ * filtered on the device (pairs sharded over the devices of the handle); 96 bytes per pair go up. */
 int osr_enum_free_configurations(osr_world* w, const double* pts, int64_t b, double margin, int den,
                                  int only_median, double* out_q, uint8_t* out_valid, int32_t* counts);
 
@@ -161,6 +162,10 @@ void osr_apply(const double from[7], const double tr[3], const double aa[3], dou
 int osr_intersecting_to_surface(osr_world* w, int which, const double* q, const double* V, int64_t nV,
                                 const int32_t* F, int64_t nF, int64_t cap, int32_t* out_faces,
                                 double* out_bary, int64_t* total);
+
+/* The candidates osr_enum_free_configurations labels, built on the host (no device, no world): out_q[b][den][7].
+ * Same arithmetic as the device construction, bit for bit (csrc/se3.h keyconf_state). */
+int osr_enum_configuration_states(const double* pts, int64_t b, double margin, int den, double* out_q);
 
 /* Clearance statistics of m key-configuration candidates (replaces the host loop touchq_util.calc_touch +
  * pyosr.multi_distance + numpy statistics: src/GP/pipeline/touchq_util.py:8-27, preprocess_key.py:174-184 and

@@ -65,6 +65,7 @@ SIGNATURES = {
     "osr_clearance_stats": (C.c_int, [C.c_void_p, c_dp, C.c_int64, c_dp, C.c_int, C.c_double, c_dp, c_dp]),
     "osr_enum_free_configurations": (C.c_int, [C.c_void_p, c_dp, C.c_int64, C.c_double, C.c_int, C.c_int, c_dp, c_u8p,
                                                c_i32p]),
+    "osr_enum_configuration_states": (C.c_int, [c_dp, C.c_int64, C.c_double, C.c_int, c_dp]),
     "osr_translate_to_unit": (C.c_int, [C.c_void_p, c_dp, C.c_int64, c_dp]),
     "osr_translate_from_unit": (C.c_int, [C.c_void_p, c_dp, C.c_int64, c_dp]),
     "osr_translate_ompl_to_unit": (C.c_int, [C.c_void_p, c_dp, C.c_int64, c_dp]),

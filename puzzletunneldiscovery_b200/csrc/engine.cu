@@ -22,6 +22,7 @@
 #include "kernels_knn.cuh"
 #include "kernels_raster.cuh"
 #include "kernels_clearance.cuh"
+#include "kernels_keyconf.cuh"
 
 namespace {
 
@@ -976,13 +977,7 @@ int osr_translate_from_unit(const osr_world* w, const double* q, int64_t n, doub
   return OSR_OK;
 }
 // Eigen quaternion * vector: v + w*(2 u x v) + u x (2 u x v)
-static void quat_rotate(const double* q, const double* v, double* o) {
-  double u[3] = {q[1], q[2], q[3]};
-  double uv[3] = {u[1] * v[2] - u[2] * v[1], u[2] * v[0] - u[0] * v[2], u[0] * v[1] - u[1] * v[0]};
-  for (int k = 0; k < 3; k++) uv[k] += uv[k];
-  double c[3] = {u[1] * uv[2] - u[2] * uv[1], u[2] * uv[0] - u[0] * uv[2], u[0] * uv[1] - u[1] * uv[0]};
-  for (int k = 0; k < 3; k++) o[k] = v[k] + q[0] * uv[k] + c[k];
-}
+using osr::quat_rotate;
 int osr_translate_ompl_to_unit(const osr_world* w, const double* qin, int64_t n, double* out) {  // unit_world.cc:689-711
   if (!w || !w->host_ready) return fail(OSR_EINVAL, "geometry not built: call osr_finalize()");
   double dc[3];
@@ -1440,25 +1435,26 @@ int osr_ompl_check_motions(osr_world* w, const double* q0, const double* q1, int
   return OSR_OK;
 }
 
-// ---- key-configuration enumeration ---------------------------------------------------------------
-// Eigen Quaternion::setFromTwoVectors (unit inputs), the generic branch and the antiparallel
-// branch (axis from the smallest singular direction is replaced by any perpendicular vector:
-// the reference never hits it with opposing surface normals unless rob_n == env_n).
-static void quat_from_two_vectors(const double* a, const double* b, double* q) {
-  double la = std::sqrt(a[0] * a[0] + a[1] * a[1] + a[2] * a[2]), lb = std::sqrt(b[0] * b[0] + b[1] * b[1] + b[2] * b[2]);
-  double v0[3] = {a[0] / la, a[1] / la, a[2] / la}, v1[3] = {b[0] / lb, b[1] / lb, b[2] / lb};
-  double c = v1[0] * v0[0] + v1[1] * v0[1] + v1[2] * v0[2];
-  if (c < -1.0 + 1e-12) {
-    double h[3] = {1, 0, 0};
-    if (std::fabs(v0[0]) > 0.9) { h[0] = 0; h[1] = 1; }
-    double ax[3] = {v0[1] * h[2] - v0[2] * h[1], v0[2] * h[0] - v0[0] * h[2], v0[0] * h[1] - v0[1] * h[0]};
-    double l = std::sqrt(ax[0] * ax[0] + ax[1] * ax[1] + ax[2] * ax[2]);
-    q[0] = 0; q[1] = ax[0] / l; q[2] = ax[1] / l; q[3] = ax[2] / l;
-    return;
+// ---- key-configuration enumeration (kernels_keyconf.cuh) -------------------------
+static void keyconf_half_angles(int den, std::vector<double>& cs) {   // unit_world.cc:1358-1362: i * (2 pi / den)
+  const double PI2 = 2.0 * 3.14159265358979323846;
+  const double delta = PI2 / (double)den;
+  cs.resize((size_t)2 * den);
+  for (int i = 0; i < den; i++) {
+    double ang = (double)i * delta;
+    cs[2 * i] = std::cos(0.5 * ang);
+    cs[2 * i + 1] = std::sin(0.5 * ang);
   }
-  double ax[3] = {v0[1] * v1[2] - v0[2] * v1[1], v0[2] * v1[0] - v0[0] * v1[2], v0[0] * v1[1] - v0[1] * v1[0]};
-  double s = std::sqrt((1.0 + c) * 2.0), inv = 1.0 / s;
-  q[0] = s * 0.5; q[1] = ax[0] * inv; q[2] = ax[1] * inv; q[3] = ax[2] * inv;
+}
+
+// host construction of the candidates (no device work): the states osr_enum_free_configurations labels
+int osr_enum_configuration_states(const double* pts, int64_t b, double margin, int den, double* out_q) {
+  if (b < 0 || den <= 0 || (b > 0 && (!pts || !out_q))) return fail(OSR_EINVAL, "bad arguments");
+  std::vector<double> cs;
+  keyconf_half_angles(den, cs);
+  for (int64_t r = 0; r < b; r++)
+    for (int i = 0; i < den; i++) osr::keyconf_state(pts + 12 * r, margin, cs[2 * i], cs[2 * i + 1], out_q + 7 * (r * den + i));
+  return OSR_OK;
 }
 
 int osr_enum_free_configurations(osr_world* w, const double* pts, int64_t b, double margin, int den, int only_median,
@@ -1466,49 +1462,44 @@ int osr_enum_free_configurations(osr_world* w, const double* pts, int64_t b, dou
   int rc = check_ready(w);
   if (rc) return rc;
   if (b <= 0 || den <= 0 || !pts || !out_q || !out_valid) return fail(OSR_EINVAL, "bad arguments");
-  // unit_world.cc:1340-1389: rot_1 aligns rob_n with -env_n, rot_2 spins about env_n
-  const double PI2 = 2.0 * 3.14159265358979323846;
-  for (int64_t r = 0; r < b; r++) {
-    const double* ro = pts + 12 * r; const double* rn = ro + 3; const double* eo = ro + 6; const double* en = ro + 9;
-    double men[3] = {-en[0], -en[1], -en[2]}, rot1[4];
-    quat_from_two_vectors(rn, men, rot1);
-    double eo_m[3] = {eo[0] + en[0] * margin, eo[1] + en[1] * margin, eo[2] + en[2] * margin};
-    double ro_m[3] = {ro[0] + rn[0] * margin, ro[1] + rn[1] * margin, ro[2] + rn[2] * margin};
-    const double delta = PI2 / (double)den;
-    for (int i = 0; i < den; i++) {
-      double ang = (double)i * delta, sh = std::sin(0.5 * ang);
-      // Eigen AngleAxis -> Quaternion does not normalise the axis
-      double rot2[4] = {std::cos(0.5 * ang), sh * en[0], sh * en[1], sh * en[2]}, rot[4], p[3];
-      osr::quat_mul(rot2, rot1, rot);
-      quat_rotate(rot, ro_m, p);
-      double* o = out_q + 7 * (r * den + i);
-      osr::quat_normalize(rot[0], rot[1], rot[2], rot[3]);
-      o[0] = eo_m[0] - p[0]; o[1] = eo_m[1] - p[1]; o[2] = eo_m[2] - p[2];
-      o[3] = rot[0]; o[4] = rot[1]; o[5] = rot[2]; o[6] = rot[3];
-    }
+  std::lock_guard<std::mutex> lk(w->mu);
+  std::vector<double> cs;
+  keyconf_half_angles(den, cs);
+  int parts = (int)w->slots.size();
+  for (int i = 0; i < parts; i++) {
+    Slot& s = w->slots[i];
+    int64_t lo, hi;
+    shard(b, parts, i, lo, hi);
+    const int64_t mb = hi - lo, n = mb * den;
+    if (mb == 0) continue;
+    CU(cudaSetDevice(s.dev));
+    CU(s.in1.need((size_t)mb * 96 + (size_t)den * 16));
+    CU(s.in0.need((size_t)n * 56));
+    CU(s.out[2].need((size_t)n));
+    CU(s.out[5].need((size_t)mb * 4));
+    double* d_pts = (double*)s.in1.p;
+    double* d_cs = d_pts + 12 * mb;
+    CU(cudaMemcpyAsync(d_pts, pts + 12 * lo, (size_t)mb * 96, cudaMemcpyHostToDevice, s.stream));
+    CU(cudaMemcpyAsync(d_cs, cs.data(), (size_t)den * 16, cudaMemcpyHostToDevice, s.stream));
+    osr::k_keyconf_states<<<(unsigned)((n + 255) / 256), 256, 0, s.stream>>>(d_pts, (long long)mb, den, margin, d_cs,
+                                                                           (double*)s.in0.p);
+    CU(cudaGetLastError());
+    w->host_counters.kernel_launches++;
+    rc = launch_valid(w, s, (const double*)s.in0.p, n, (uint8_t*)s.out[2].p);
+    if (rc) return rc;
+    osr::k_keyconf_filter<<<(unsigned)((mb + 127) / 128), 128, 0, s.stream>>>((uint8_t*)s.out[2].p, (long long)mb, den,
+                                                                            only_median, (int*)s.out[5].p);
+    CU(cudaGetLastError());
+    w->host_counters.kernel_launches++;
+    CU(cudaMemcpyAsync(out_q + 7 * lo * den, s.in0.p, (size_t)n * 56, cudaMemcpyDeviceToHost, s.stream));
+    CU(cudaMemcpyAsync(out_valid + lo * den, s.out[2].p, (size_t)n, cudaMemcpyDeviceToHost, s.stream));
+    if (counts) CU(cudaMemcpyAsync(counts + lo, s.out[5].p, (size_t)mb * 4, cudaMemcpyDeviceToHost, s.stream));
   }
-  rc = osr_is_valid_states(w, out_q, b * den, out_valid);
-  if (rc) return rc;
-  for (int64_t r = 0; r < b; r++) {
-    uint8_t* v = out_valid + r * den;
-    if (only_median) {  // keep the middle element of every contiguous valid run (:1375-1386)
-      std::vector<uint8_t> keep((size_t)den, 0);
-      int i = 0;
-      while (i < den) {
-        if (!v[i]) { i++; continue; }
-        int j = i;
-        while (j + 1 < den && v[j + 1]) j++;
-        // a run is only flushed by a following invalid sample; mid = begin + size/2
-        if (j + 1 < den) keep[(size_t)(i + (j - i + 1) / 2)] = 1;
-        i = j + 1;
-      }
-      memcpy(v, keep.data(), (size_t)den);
-    }
-    if (counts) {
-      int c = 0;
-      for (int i = 0; i < den; i++) c += v[i];
-      counts[r] = c;
-    }
+  for (int i = 0; i < parts; i++) {
+    Slot& s = w->slots[i];
+    CU(cudaSetDevice(s.dev));
+    rc = check_device_error(w, s);
+    if (rc) return rc;
   }
   return OSR_OK;
 }

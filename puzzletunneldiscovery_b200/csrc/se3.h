@@ -118,6 +118,50 @@ OSR_HD void apply(const double* from, const double* tr, const double* aa, double
   o[3] = q[0]; o[4] = q[1]; o[5] = q[2]; o[6] = q[3];
 }
 
+// v rotated by the (not necessarily unit) quaternion q, Eigen's Quaternion * vector: v + w t + u x t, t = 2 u x v
+OSR_HD void quat_rotate(const double* q, const double* v, double* o) {
+  double u[3] = {q[1], q[2], q[3]};
+  double uv[3] = {u[1] * v[2] - u[2] * v[1], u[2] * v[0] - u[0] * v[2], u[0] * v[1] - u[1] * v[0]};
+  for (int k = 0; k < 3; k++) uv[k] += uv[k];
+  double c[3] = {u[1] * uv[2] - u[2] * uv[1], u[2] * uv[0] - u[0] * uv[2], u[0] * uv[1] - u[1] * uv[0]};
+  for (int k = 0; k < 3; k++) o[k] = v[k] + q[0] * uv[k] + c[k];
+}
+
+// Eigen Quaternion::setFromTwoVectors, the generic branch; in the antiparallel branch Eigen takes the axis from an
+// SVD, here any perpendicular vector (the reference only gets there when rob_n == env_n).
+OSR_HD void quat_from_two_vectors(const double* a, const double* b, double* q) {
+  double la = sqrt(a[0] * a[0] + a[1] * a[1] + a[2] * a[2]), lb = sqrt(b[0] * b[0] + b[1] * b[1] + b[2] * b[2]);
+  double v0[3] = {a[0] / la, a[1] / la, a[2] / la}, v1[3] = {b[0] / lb, b[1] / lb, b[2] / lb};
+  double c = v1[0] * v0[0] + v1[1] * v0[1] + v1[2] * v0[2];
+  if (c < -1.0 + 1e-12) {
+    double h[3] = {1, 0, 0};
+    if (fabs(v0[0]) > 0.9) { h[0] = 0; h[1] = 1; }
+    double ax[3] = {v0[1] * h[2] - v0[2] * h[1], v0[2] * h[0] - v0[0] * h[2], v0[0] * h[1] - v0[1] * h[0]};
+    double l = sqrt(ax[0] * ax[0] + ax[1] * ax[1] + ax[2] * ax[2]);
+    q[0] = 0; q[1] = ax[0] / l; q[2] = ax[1] / l; q[3] = ax[2] / l;
+    return;
+  }
+  double ax[3] = {v0[1] * v1[2] - v0[2] * v1[1], v0[2] * v1[0] - v0[0] * v1[2], v0[0] * v1[1] - v0[1] * v1[0]};
+  double s = sqrt((1.0 + c) * 2.0), inv = 1.0 / s;
+  q[0] = s * 0.5; q[1] = ax[0] * inv; q[2] = ax[1] * inv; q[3] = ax[2] * inv;
+}
+
+// One key-configuration candidate (unit_world.cc:1340-1373): pts = rob point, rob normal, env point, env normal;
+// ch / sh = cos / sin of half the spin angle about the environment normal.
+OSR_HD void keyconf_state(const double* pts, double margin, double ch, double sh, double* o) {
+  const double* ro = pts; const double* rn = pts + 3; const double* eo = pts + 6; const double* en = pts + 9;
+  double men[3] = {-en[0], -en[1], -en[2]}, rot1[4];
+  quat_from_two_vectors(rn, men, rot1);
+  double eo_m[3] = {eo[0] + en[0] * margin, eo[1] + en[1] * margin, eo[2] + en[2] * margin};
+  double ro_m[3] = {ro[0] + rn[0] * margin, ro[1] + rn[1] * margin, ro[2] + rn[2] * margin};
+  double rot2[4] = {ch, sh * en[0], sh * en[1], sh * en[2]}, rot[4], p[3];   // AngleAxis -> Quaternion keeps the axis as is
+  quat_mul(rot2, rot1, rot);
+  quat_rotate(rot, ro_m, p);
+  quat_normalize(rot[0], rot[1], rot[2], rot[3]);
+  o[0] = eo_m[0] - p[0]; o[1] = eo_m[1] - p[1]; o[2] = eo_m[2] - p[2];
+  o[3] = rot[0]; o[4] = rot[1]; o[5] = rot[2]; o[6] = rot[3];
+}
+
 OSR_HD long long dbits(double x) {
 #if defined(__CUDA_ARCH__)
   return __double_as_longlong(x);

@@ -649,6 +649,15 @@ class UnitWorld:
                                                    _p(counts, c_i32p)))
         return q, valid.astype(bool), counts
 
+    @staticmethod
+    def enum_configuration_states(pts, margin, denominator):
+        """The candidate states of enum_free_configurations built on the host (no labels): float64[B, den, 7]."""
+        pts = np.ascontiguousarray(np.asarray(pts, dtype=np.float64).reshape(-1, 12))
+        q = np.empty((len(pts), denominator, 7))
+        check(_lib.load().osr_enum_configuration_states(_p(pts, c_dp), len(pts), float(margin), int(denominator),
+                                                        _p(q, c_dp)))
+        return q
+
     def enum_free_configuration(self, rob_surface_point, rob_surface_normal, env_surface_point, env_surface_normal,
                                 margin, denominator, only_median=False):
         pts = np.concatenate([np.asarray(x, dtype=np.float64).reshape(3) for x in

@@ -301,6 +301,30 @@ def test_enum_free_configurations_labels_are_validity(uw_org):
             assert np.abs(p - (ep[b] + 1e-4 * en[b])).max() < 1e-9
     _, vm, cm = uw_org.enum_free_configurations(pts, 1e-4, 64, only_median=True)
     assert (cm <= counts).all() and (vm & ~valid).sum() == 0
+    # N2: candidates are built on the device -- bit for bit the host construction (unit_world.cc:1340-1373)
+    assert np.array_equal(q, uw_org.enum_configuration_states(pts, 1e-4, 64))
+    # the run filter (unit_world.cc:1375-1386): middle of every valid run that an invalid sample closes
+    want = np.zeros_like(valid)
+    for r in range(len(valid)):
+        i = 0
+        while i < 64:
+            if not valid[r, i]:
+                i += 1
+                continue
+            j = i
+            while j + 1 < 64 and valid[r, j + 1]:
+                j += 1
+            if j + 1 < 64:
+                want[r, i + (j - i + 1) // 2] = True
+            i = j + 1
+    assert np.array_equal(vm, want) and np.array_equal(cm, want.sum(axis=1))
+    # a larger ragged batch (den not a multiple of anything): labels = validity of the returned states
+    rp2, rn2 = sample(V1, F1, 300)
+    ep2, en2 = sample(V0, F0, 300)
+    pts2 = np.stack([rp2, rn2, ep2, en2], axis=1)
+    q2, v2, c2 = uw_org.enum_free_configurations(pts2, 1e-4, 37)
+    assert np.array_equal(v2.reshape(-1), uw_org.is_valid_states(q2.reshape(-1, 7))) and 0 < v2.mean() < 1
+    assert np.array_equal(q2, uw_org.enum_configuration_states(pts2, 1e-4, 37))
 
 
 def test_state_frame_maps_round_trip(uw_wt2):
