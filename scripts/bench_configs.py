@@ -5,7 +5,7 @@ Every leg goes through the C ABI (`libosrgpu.so`) with HOST buffers, is timed by
 (copies included), and a prefix of its output is compared with the CPU oracle (test infrastructure, used here
 only as the checker and as the timed CPU baseline).  One JSON line per leg; keep the output under profiles/.
 
-    python scripts/bench_configs.py [--legs touch,touch_fine,edges,hipoly,contacts,clearance] [--scale 1.0]
+    python scripts/bench_configs.py [--legs touch,touch_fine,edges,hipoly,contacts,clearance,keyconf] [--scale 1.0]
 """
 import argparse
 import json
@@ -195,15 +195,49 @@ def leg_clearance(O, scale):
             "cpu_port": {"segments_per_s": k / dtc, "threads": O.lib().orc_max_threads()}}
 
 
+def leg_keyconf(O, scale):
+    """key-configuration candidates -- SurfacePairsToSample=1024 surface-point pairs x
+    NumberOfRotations=256 spins (src/GP/pipeline/keyconf.py:117-131), built + labelled + run-filtered on the device."""
+    uw = world(pyosr.UnitWorld)
+    ow = world(O.OracleWorld)
+    rs = np.random.RandomState(6)
+
+    def sample(which, n):
+        V, F = uw._geometry(which)
+        f = F[rs.randint(0, len(F), n)]
+        a, b, c = V[f[:, 0]], V[f[:, 1]], V[f[:, 2]]
+        nrm = np.cross(b - a, c - a)
+        return (a + b + c) / 3.0, nrm / np.linalg.norm(nrm, axis=1, keepdims=True)
+
+    b, den = max(1, int(1024 * scale)), 256
+    rp, rn = sample(1, b)
+    ep, en = sample(0, b)
+    pts = np.stack([rp, rn, ep, en], axis=1)
+    (q, valid, counts), dt = timed(lambda: uw.enum_free_configurations(pts, 1e-4, den, only_median=True))
+    q_all, v_all, _ = uw.enum_free_configurations(pts, 1e-4, den)
+    m = min(b, 64)
+    tc = time.perf_counter()
+    qh = uw.enum_configuration_states(pts[:m], 1e-4, den)
+    vo = ow.is_valid_states(qh.reshape(-1, 7)).astype(bool).reshape(m, den)
+    dtc = time.perf_counter() - tc
+    return {"leg": "keyconf", "geometry": "G-org", "surface_pairs": b, "rotations": den,
+            "candidates_per_s": b * den / dt, "pairs_per_s": b / dt, "seconds": dt,
+            "valid_fraction": float(v_all.mean()), "kept_after_run_filter": int(counts.sum()),
+            "h2d_bytes": 96 * b + 16 * den, "oracle_prefix_pairs": m,
+            "states_equal_host_construction_on_prefix": bool(np.array_equal(q_all[:m], qh)),
+            "labels_equal_oracle_on_prefix": bool(np.array_equal(v_all[:m], vo)),
+            "cpu_port": {"candidates_per_s": m * den / dtc, "threads": O.lib().orc_max_threads()}}
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--legs", default="touch,touch_fine,edges,hipoly,contacts,clearance")
+    ap.add_argument("--legs", default="touch,touch_fine,edges,hipoly,contacts,clearance,keyconf")
     ap.add_argument("--scale", type=float, default=1.0)
     args = ap.parse_args()
     from oracle import oracle as O
     legs = {"touch": lambda: leg_touch(O, args.scale), "touch_fine": lambda: leg_touch(O, args.scale, fine=True),
             "edges": lambda: leg_edges(O, args.scale), "hipoly": lambda: leg_hipoly(O, args.scale),
-            "contacts": lambda: leg_contacts(O, args.scale), "clearance": lambda: leg_clearance(O, args.scale)}
+            "contacts": lambda: leg_contacts(O, args.scale), "clearance": lambda: leg_clearance(O, args.scale), "keyconf": lambda: leg_keyconf(O, args.scale)}
     for name in args.legs.split(","):
         t = time.perf_counter()
         try:
