@@ -462,6 +462,16 @@ def test_two_devices_one_handle_equal_one_device(uw_org):
     assert np.array_equal(ra["faces"], rb["faces"]) and np.array_equal(ra["seg"], rb["seg"])
     from puzzletunneldiscovery_b200 import sharding as S
     assert np.array_equal(S.sharded_map(uw2.is_valid_states, [q], np.bool_), v1)   # no process group: plain call
+    # candidate-sharded entry points: clearance statistics (K8) and key-configuration candidates (K9)
+    cq = np.ascontiguousarray(q[v1][:7])
+    cto = W.touch_rays(np.repeat(cq, 33, axis=0), 7 * 33, seed=43)[1].reshape(7, 33, 7)
+    sa, da = uw_org.clearance_stats(cq, cto, VD_TOUCH, with_distances=True)
+    sb, db = uw2.clearance_stats(cq, cto, VD_TOUCH, with_distances=True)
+    assert np.array_equal(sa, sb) and np.array_equal(da, db)
+    pts = np.random.RandomState(44).randn(9, 4, 3)
+    ka = uw_org.enum_free_configurations(pts, 1e-4, 19, only_median=True)
+    kb = uw2.enum_free_configurations(pts, 1e-4, 19, only_median=True)
+    assert all(np.array_equal(x, y) for x, y in zip(ka, kb))
 
 
 @pytest.mark.gpu
