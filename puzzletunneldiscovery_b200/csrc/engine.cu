@@ -109,6 +109,7 @@ struct osr_world {
   double rob_radius = 0.0;         // max |p| over the robot's unit-mesh vertices
   double sweep_rmax = 0.02;        // K2: largest swept radius worth a traversal (OSR_SWEEP_RMAX, unit-scene lengths)
   double sweep_rstart = 0.005;     // K2: swept radius of the first windows of a walk (OSR_SWEEP_RSTART)
+  int sweep_short_tile = 8;        // K2: steps of the exact tile after a blocked 4-step window (OSR_SWEEP_SHORT_TILE)
 
   osr::KParams params(const Slot& s) const {
     osr::KParams P;
@@ -121,6 +122,7 @@ struct osr_world {
     P.sweep_tiles = sweep_tiles;
     P.sweep_rmax = sweep_rmax;
     P.sweep_rstart = sweep_rstart;
+    P.sweep_short_tile = sweep_short_tile;
     P.counters = s.counters;
     P.work_counter = s.work;
     P.spill = s.spill;
@@ -367,6 +369,7 @@ int osr_create(osr_world** out) {
   if (const char* k3 = getenv("OSR_SWEEP_TILES")) (*out)->sweep_tiles = std::max(0, std::min(1 << 16, atoi(k3)));
   if (const char* k4 = getenv("OSR_SWEEP_RMAX")) (*out)->sweep_rmax = std::max(0.0, atof(k4));
   if (const char* k5 = getenv("OSR_SWEEP_RSTART")) (*out)->sweep_rstart = std::max(0.0, atof(k5));
+  if (const char* k6 = getenv("OSR_SWEEP_SHORT_TILE")) (*out)->sweep_short_tile = std::max(1, std::min(32, atoi(k6)));
   return OSR_OK;
 }
 

@@ -49,6 +49,7 @@ struct KParams {
   int sweep_tiles;                   // K2: largest swept window in tiles of 32 steps (0 = every step traversed)
   double sweep_rmax;                 // K2: windows whose swept radius exceeds this are not attempted
   double sweep_rstart;               // K2: swept radius of the first windows of a walk
+  int sweep_short_tile;              // K2: steps of the exact tile that follows a blocked 4-step window (1..32)
 };
 
 constexpr int STACK_CAP = 512;   // shared-memory stack entries per warp
@@ -692,6 +693,9 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB)
           }
           continue;
         }
+        // a tile entered because four steps did not clear is short: the contact is expected within them, and every
+        // pose traversed beyond the first hit is wasted
+        const int exact_n = exact_next ? P.sweep_short_tile : 32;
         exact_next = false;
         // step deltas of this tile: lane j takes the (j+1)-th value after `carry`.  The chain of fp64 adds is
         // inherently serial (the reference's running sum, rounding included), so all lanes run it; it is kept to
@@ -704,8 +708,8 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB)
           d = (d < dist) ? fmin(dist, t) : t;
           if (j == lane) mine = d;
         }
-        const bool mine_ok = mine <= dist;
-        carry = d;  // delta of slot 31 (only used when all 32 slots were valid)
+        const bool mine_ok = mine <= dist && lane < exact_n;
+        carry = __shfl_sync(FULL, mine, exact_n - 1);  // delta of the last slot (only used when all slots were valid)
         double tau = mine * inv_dist;
         if (mine_ok) {
           double s[7];
@@ -732,7 +736,7 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB)
           nposes += nalive;
           k0 += nalive;
           if (nalive > 0) prev_tau = S.tau[nalive - 1];
-          if (nalive < 32) {  // walked past dist: the whole segment is free
+          if (nalive < exact_n) {  // walked past dist: the whole segment is free
             free_tau = prev_tau;
             touch_tau = 0.0;  // the reference returns its shadowed outer `tau` (unit_world.cc:452-455,473)
             interpolate(a, b, prev_tau, lf);
