@@ -845,9 +845,65 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, 3)
     // sample points: index 0 = s2 itself, index m = interior point m/nd (m = 1..nd-1)
     const long long total = nd >= 2 ? nd : 1;
     bool valid = true;
-    for (long long base = 0; base < total && valid; base += 32) {
+    // Swept windows as in k_transit (the boolean needs no first-contact step, but the prefix order keeps the early
+    // exit): a robot point is R(q(t)) (v - dc) + scale p(t), so between t and t' it moves at most
+    // |t - t'| (scale |dp| + 2 theta (R_rob + |dc|)); the slerp of two UNIT quaternions turns at constant rate.
+    const double na2 = a[3] * a[3] + a[4] * a[4] + a[5] * a[5] + a[6] * a[6];
+    const double nb2 = b[3] * b[3] + b[4] * b[4] + b[5] * b[5] + b[6] * b[6];
+    const double dcn = sqrt(F.dc[0] * F.dc[0] + F.dc[1] * F.dc[1] + F.dc[2] * F.dc[2]);
+    const double rate = (F.scale * dtr + 2.0 * theta * (P.rob_radius + dcn)) * (1.0 + 1e-9);
+    const double step_radius = 0.5 * rate / (double)nd;
+    int ws = 0;
+    if (fabs(na2 - 1.0) < 1e-6 && fabs(nb2 - 1.0) < 1e-6 && step_radius > 0.0) {
+      const double cap = fmin(32.0 * (double)P.sweep_tiles, P.sweep_rmax / step_radius);
+      if (cap >= 4.0) {
+        ws = 4;
+        while (2.0 * ws <= cap && (double)(2 * ws) * step_radius <= P.sweep_rstart) ws *= 2;
+      }
+    }
+    const int ws_cap = ws > 0 ? (int)fmin(32.0 * (double)P.sweep_tiles, P.sweep_rmax / step_radius) : 0;
+    int nwin = 4;
+    bool exact_next = true;   // the first tile (s2 and the first interior points) is always walked
+    long long base = 0;
+    while (base < total && valid) {
+      if (ws > 0 && !exact_next) {
+        const long long m_lo = base + (long long)lane * ws;
+        const long long m_hi = min(total - 1, m_lo + ws - 1);
+        const bool mine_w = lane < nwin && m_lo < total;
+        if (mine_w) {
+          const double t_lo = (double)m_lo / (double)nd, t_hi = (double)m_hi / (double)nd;
+          const double radius = 0.5 * (t_hi - t_lo) * rate * (1.0 + 1e-9) + 1e-6;
+          double s[7];
+          ompl_point_to_unit(F, a, b, theta, 0.5 * (t_lo + t_hi), s);
+          set_pose(P, S, lane, s);
+          S.eta[lane] = __fadd_ru(S.eta[lane], __double2float_ru(0.5 * radius));
+          S.tau[lane] = radius;
+        }
+        const unsigned tried = __ballot_sync(FULL, mine_w);
+        __syncwarp();
+        const unsigned blocked = traverse_tile<MODE_SWEPT>(P, S, C, tried, lane);
+        if (C.overflow) { valid = false; break; }
+        __syncwarp();
+        const int cleared = blocked ? __ffs(blocked) - 1 : __popc(tried);
+        const long long adv = min((long long)cleared * ws, total - base);
+        base += adv;
+        nposes += (unsigned long long)adv;
+        if (!blocked) {
+          if (nwin < 32) nwin *= 2;
+          else if (2 * ws <= ws_cap) ws *= 2;
+        } else if (ws > 4) {
+          ws >>= 1;
+          nwin = 2;
+        } else {
+          exact_next = true;
+          nwin = 2;
+        }
+        continue;
+      }
+      const int exact_n = (base > 0 && ws > 0) ? P.sweep_short_tile : 32;
+      exact_next = false;
       const long long m = base + lane;
-      const bool have = m < total;
+      const bool have = m < total && lane < exact_n;
       if (have) {
         double s[7];
         ompl_point_to_unit(F, a, b, theta, m == 0 ? 1.0 : (double)m / (double)nd, s);
@@ -860,6 +916,7 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, 3)
       if (C.overflow) { valid = false; break; }
       nposes += hits ? (unsigned)__ffs(hits) : __popc(alive);
       if (hits) valid = false;
+      base += exact_n;
       __syncwarp();
     }
     if (lane == 0) {

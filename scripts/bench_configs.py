@@ -5,7 +5,7 @@ Every leg goes through the C ABI (`libosrgpu.so`) with HOST buffers, is timed by
 (copies included), and a prefix of its output is compared with the CPU oracle (test infrastructure, used here
 only as the checker and as the timed CPU baseline).  One JSON line per leg; keep the output under profiles/.
 
-    python scripts/bench_configs.py [--legs touch,touch_fine,edges,hipoly,contacts,clearance,keyconf] [--scale 1.0]
+    python scripts/bench_configs.py [--legs touch,touch_fine,edges,hipoly,contacts,clearance,keyconf,ompl_motions] [--scale 1.0]
 """
 import argparse
 import json
@@ -229,15 +229,44 @@ def leg_keyconf(O, scale):
             "cpu_port": {"candidates_per_s": m * den / dtc, "threads": O.lib().orc_max_threads()}}
 
 
+def leg_ompl(O, scale):
+    """SURVEY 8(f) N1: OmplDriver.validate_motion_pairs semantics (DiscreteMotionValidator::checkMotion, OMPL's own
+    interpolation and segment count) on the windowed k-NN edges of valid milestones, OMPL-frame rows, at the
+    pipeline's collision_resolution fallback 1e-4 (src/GP/pipeline/solve.py:265)."""
+    uw = world(pyosr.UnitWorld)
+    ow = world(O.OracleWorld)
+    nm = int((1 << 14) * scale)
+    q = W.random_states(2 * nm, seed=7)
+    q = q[uw.is_valid_states(q)][:nm]
+    fr, to = uw.knn_edges(q, k=8, window=4096)
+    a, b = uw.translate_unit_to_ompl(fr), uw.translate_unit_to_ompl(to)
+    extent, res = 150.0, 1e-4
+    uw.counters(reset=True)
+    (ok, nd), dt = timed(lambda: uw.ompl_validate_motion_pairs(a, b, extent, res, with_counts=True))
+    c = uw.counters(reset=True)
+    m = 64
+    dc = (uw.get_ompl_center(1).astype(np.float32) - uw.robot_center.astype(np.float32)).astype(np.float64) * uw.scene_scale
+    tc = time.perf_counter()
+    want, ond = ow.ompl_check_motions(a[:m], b[:m], uw.scene_scale, dc, extent, res)
+    dtc = time.perf_counter() - tc
+    return {"leg": "ompl_motions", "geometry": "G-org", "motions": len(a), "resolution": res,
+            "motions_per_s": len(a) / dt, "seconds": dt, "mean_points_per_motion": float(nd.mean()),
+            "points_per_s_reference_semantics": float(nd.sum()) / dt, "valid_fraction": float(ok.mean()),
+            "box_tests_per_point": c["bv_tests"] / 2 / max(1.0, float(nd.sum())), "oracle_prefix": m,
+            "labels_and_counts_equal_oracle_on_prefix": bool(np.array_equal(ok[:m].astype(bool), want.astype(bool)) and
+                                                             np.array_equal(nd[:m], ond)),
+            "cpu_port": {"motions_per_s": m / dtc, "points_per_s": float(ond.sum()) / dtc, "threads": O.lib().orc_max_threads()}}
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--legs", default="touch,touch_fine,edges,hipoly,contacts,clearance,keyconf")
+    ap.add_argument("--legs", default="touch,touch_fine,edges,hipoly,contacts,clearance,keyconf,ompl_motions")
     ap.add_argument("--scale", type=float, default=1.0)
     args = ap.parse_args()
     from oracle import oracle as O
     legs = {"touch": lambda: leg_touch(O, args.scale), "touch_fine": lambda: leg_touch(O, args.scale, fine=True),
             "edges": lambda: leg_edges(O, args.scale), "hipoly": lambda: leg_hipoly(O, args.scale),
-            "contacts": lambda: leg_contacts(O, args.scale), "clearance": lambda: leg_clearance(O, args.scale), "keyconf": lambda: leg_keyconf(O, args.scale)}
+            "contacts": lambda: leg_contacts(O, args.scale), "clearance": lambda: leg_clearance(O, args.scale), "keyconf": lambda: leg_keyconf(O, args.scale), "ompl_motions": lambda: leg_ompl(O, args.scale)}
     for name in args.legs.split(","):
         t = time.perf_counter()
         try:

@@ -582,6 +582,13 @@ def test_ompl_frame_validators_match_restatement(shift, oracle_mod):
     want, ond = ow.ompl_check_motions(a, b, scale, dc, extent, res)
     assert np.array_equal(nd, ond) and nd.max() > 32 and nd.min() >= 1
     assert np.array_equal(got.astype(bool), want.astype(bool)) and 0.05 < got.mean() < 0.999
+    # the planner's own resolution (collision_resolution fallback 1e-4, solve.py:265): thousands of interior points
+    # per motion, cleared in swept windows -- same booleans as the oracle's point-by-point checkMotion
+    fine = 2e-4
+    gf, nf = uw.ompl_validate_motion_pairs(a[:192], b[:192], extent, fine, with_counts=True)
+    wf, onf = ow.ompl_check_motions(a[:192], b[:192], scale, dc, extent, fine)
+    assert np.array_equal(nf, onf) and nf.max() > 1000
+    assert np.array_equal(gf.astype(bool), wf.astype(bool)) and 0.05 < gf.mean() < 0.999
     # an invalid goal fails whatever lies in between; coincident states need one check only
     bad = uw.translate_unit_to_ompl(q[~valid][:8])
     g2, n2 = uw.ompl_validate_motion_pairs(a[:8], bad, extent, res, with_counts=True)
