@@ -421,7 +421,11 @@ __device__ __forceinline__ unsigned traverse_tile(const KParams& P, WarpShared& 
       continue;
     }
     if (top > STACK_CAP - 32) {  // make room: move the oldest entries to global memory
-      if (C.nspill + SPILL_CHUNK > C.spill_cap) { C.overflow = true; break; }
+      if (C.nspill + SPILL_CHUNK > C.spill_cap) {
+        if (MODE == MODE_SWEPT) { hits = alive; C.nspill = 0; break; }   // no room: nothing proven, every window blocked
+        C.overflow = true;
+        break;
+      }
       for (int i = lane; i < SPILL_CHUNK; i += 32) C.spill[C.nspill + i] = S.stack[i];
       C.nspill += SPILL_CHUNK;
       C.n_spill++;

@@ -598,7 +598,7 @@ def test_ompl_frame_validators_match_restatement(shift, oracle_mod):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("npoint", [96, 257, 4096])
+@pytest.mark.parametrize("npoint", [96, 257, 4096, 8192])
 def test_clearance_stats_match_oracle_and_numpy(npoint, uw_wt2, ow_wt2, oracle_mod):
     """N3: calc_touch + multi_distance + [median, max, min, mean, std] per candidate (touchq_util.py:8-27,
     preprocess_key.py:275-281) reduced on the device, against the oracle's segment walk + numpy statistics.
@@ -607,13 +607,13 @@ def test_clearance_stats_match_oracle_and_numpy(npoint, uw_wt2, ow_wt2, oracle_m
     tv = np.load(os.path.join(W.assets_dir(), "alpha-1.2.org.tunnel.npz"))["TUNNEL_V"]
     free = np.concatenate([tv[:, :3] * uw_wt2.scene_scale, tv[:, 3:]], axis=1)
     m = 5 if npoint < 4096 else 2
+    mo = m if npoint < 4096 else 1          # the oracle walks a bounded prefix of the big cases
     q0 = np.ascontiguousarray(free[3:3 + m])
     fr, to = W.touch_rays(np.repeat(q0, npoint, axis=0), m * npoint, seed=71 + npoint)
     assert np.array_equal(fr.reshape(m, npoint, 7)[:, 0], q0)
     stats, dist = uw_wt2.clearance_stats(q0, to.reshape(m, npoint, 7), VD_TOUCH, with_distances=True)
     # the same reduction from the product's own segment outputs: exact
     lf = uw_wt2.transit_states_to_with_contact(fr, to, VD_TOUCH)[0]
-    mo = m if npoint < 4096 else 1          # the oracle walks a bounded prefix of the big case
     olf = ow_wt2.transit_states_to_with_contact(fr[:mo * npoint], to[:mo * npoint], VD_TOUCH)[0]
     assert _close(lf[:mo * npoint], olf)
     for c in range(m):
@@ -663,3 +663,38 @@ def test_swept_windows_leave_every_output_unchanged(which, vd, n, monkeypatch):
     assert np.array_equal(swept.is_valid_transitions(fr, to, vd), plain.is_valid_transitions(fr, to, vd))
     if vd < 1e-4:
         assert swept_boxes * 8 < plain_boxes        # and it is where the work goes away
+
+
+@pytest.mark.gpu
+def test_swept_windows_on_deep_trees(monkeypatch):
+    """Same equality on a subdivided alpha puzzle (64 512 x 36 288 triangles: trees too large for shared memory,
+    deeper work stacks): swept windows on = every step traversed, outputs bit-identical."""
+    import os
+    from puzzletunneldiscovery_b200 import pyosr
+    A = W.assets_dir()
+    eV, eF = W.load_obj_vf(os.path.join(A, "alpha_env-1.2.org.obj"))
+    rV, rF = W.load_obj_vf(os.path.join(A, "alpha-1.2.org.obj"))
+    EV, EF = W.subdivide(eV, eF, 8)
+    RV, RF = W.subdivide(rV, rF, 6)
+
+    def mk():
+        w = pyosr.UnitWorld()
+        w.set_meshes(EV, EF, RV, RF)
+        w.scaleToUnit()
+        w.angleModel(0.0, 0.0)
+        return w
+    monkeypatch.setenv("OSR_SWEEP_TILES", "0")
+    plain = mk()
+    monkeypatch.delenv("OSR_SWEEP_TILES")
+    swept = mk()
+    q = W.random_states(4096, seed=93)
+    ms = q[swept.is_valid_states(q)][:256]
+    fr, to = swept.knn_edges(ms, k=4, window=256)
+    for vd in (1.5164e-5, 2e-3):
+        a = swept.transit_states_to_with_contact(fr, to, vd, with_steps=True)
+        b = plain.transit_states_to_with_contact(fr, to, vd, with_steps=True)
+        assert all(np.array_equal(x, y) for x, y in zip(a, b))
+    fr2, to2 = W.touch_rays(ms[:32], 512, seed=94)
+    a = swept.transit_states_to_with_contact(fr2, to2, 1e-4, with_steps=True)
+    b = plain.transit_states_to_with_contact(fr2, to2, 1e-4, with_steps=True)
+    assert all(np.array_equal(x, y) for x, y in zip(a, b)) and 0 < a[2].sum() < len(fr2)
