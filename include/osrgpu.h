@@ -140,6 +140,11 @@ int osr_translate_from_unit(const osr_world* w, const double* q, int64_t n, doub
 int osr_translate_ompl_to_unit(const osr_world* w, const double* q_wlast, int64_t n, double* out);
 int osr_translate_unit_to_ompl(const osr_world* w, const double* q, int64_t n, double* out_wlast);
 
+/* Page-locked host memory for the arrays handed to the batched calls (optional: every call accepts ordinary
+ * pageable memory, but then the driver's staging copies, not PCIe, bound its throughput).  NULL on failure. */
+void* osr_host_alloc(size_t bytes);
+void osr_host_free(void* p);
+
 /* module-level state functions (lib/pyosr/module.cc:77-99; lib/osr/osr_state.cc) */
 double osr_distance(const double a[7], const double b[7]);
 /* The step deltas of the segment walk (unit_world.cc:445-470: delta <- delta < dist ? min(dist, delta + vd)

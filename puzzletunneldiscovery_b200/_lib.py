@@ -70,6 +70,8 @@ SIGNATURES = {
     "osr_translate_from_unit": (C.c_int, [C.c_void_p, c_dp, C.c_int64, c_dp]),
     "osr_translate_ompl_to_unit": (C.c_int, [C.c_void_p, c_dp, C.c_int64, c_dp]),
     "osr_translate_unit_to_ompl": (C.c_int, [C.c_void_p, c_dp, C.c_int64, c_dp]),
+    "osr_host_alloc": (C.c_void_p, [C.c_size_t]),
+    "osr_host_free": (None, [C.c_void_p]),
     "osr_distance": (C.c_double, [c_dp, c_dp]),
     "osr_walk_deltas": (C.c_int, [c_dp, C.c_double, C.c_double, C.c_int, c_dp]),
     "osr_interpolate": (None, [c_dp, c_dp, C.c_double, c_dp]),

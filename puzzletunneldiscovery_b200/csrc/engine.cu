@@ -251,6 +251,10 @@ int init_slot(osr_world* w, Slot& s, int dev) {
       CU(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
       size_t fixed = wm * osr::DFS_WARPS;
       long long budget = ((long long)max_smem - (long long)fixed) / 32;  // nodes
+      if (const char* cap = getenv("OSR_DFS_SMEM_NODES")) {                // A/B: leave more of the SM's memory to L1
+        long long c = atoll(cap);
+        if (c >= 2 && (w->env.bvh.num_nodes + w->rob.bvh.num_nodes) > budget) budget = std::min(budget, c);
+      }
       if (budget < 2) s.dfs_variant = -1;
       else {
         long long ne = w->env.bvh.num_nodes, nr = w->rob.bvh.num_nodes;
@@ -866,6 +870,21 @@ int osr_is_valid_transitions_device(osr_world* w, const double* d_from, const do
   CU(cudaSetDevice(s.dev));
   osr::SegOut O = {nullptr, nullptr, d_out, nullptr, nullptr, nullptr};
   return launch_transit(w, s, d_from, d_to, n, nullptr, 1, initial_verify_delta, 1, O);
+}
+
+// Page-locked host memory for sample / result arrays: a host call whose buffers are pageable is bounded by the
+// driver's staging copies (~10 GB/s), one on pinned buffers by PCIe.
+void* osr_host_alloc(size_t bytes) {
+  void* p = nullptr;
+  if (bytes == 0 || cudaHostAlloc(&p, bytes, cudaHostAllocPortable) != cudaSuccess) {
+    cudaGetLastError();
+    g_err = "cudaHostAlloc failed";
+    return nullptr;
+  }
+  return p;
+}
+void osr_host_free(void* p) {
+  if (p) cudaFreeHost(p);
 }
 
 void* osr_stream(osr_world* w) { return (w && !w->slots.empty()) ? (void*)w->slots[0].stream : nullptr; }

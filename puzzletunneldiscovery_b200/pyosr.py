@@ -31,6 +31,33 @@ def _states(q):
     return q
 
 
+class _PinnedBlock:
+    """Owner of one page-locked allocation; freed when the last numpy view of it goes away."""
+
+    def __init__(self, nbytes):
+        self._L = _lib.load()
+        self.ptr = self._L.osr_host_alloc(C.c_size_t(max(1, nbytes)))
+        if not self.ptr:
+            raise OsrError("osr_host_alloc(%d) failed (no CUDA device?)" % nbytes)
+
+    def __del__(self):
+        if getattr(self, "ptr", None):
+            self._L.osr_host_free(C.c_void_p(self.ptr))
+            self.ptr = None
+
+
+def pinned_empty(shape, dtype=np.float64):
+    """numpy array in page-locked host memory (osr_host_alloc): sample / result arrays built in it make the batched
+    calls run at PCIe speed instead of the driver's pageable staging speed."""
+    dtype = np.dtype(dtype)
+    shape = (shape,) if np.isscalar(shape) else tuple(shape)
+    nbytes = int(np.prod(shape, dtype=np.int64)) * dtype.itemsize
+    block = _PinnedBlock(nbytes)
+    buf = (C.c_char * max(1, nbytes)).from_address(block.ptr)
+    buf._osr_block = block          # the ctypes buffer keeps the allocation alive; numpy keeps the buffer
+    return np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape, dtype=np.int64))).reshape(shape)
+
+
 # ---- module-level functions (module.cc:77-99) ----------------------------------------------------
 def get_identity_state_vector():
     return np.array([0, 0, 0, 1, 0, 0, 0], dtype=np.float64)
@@ -311,16 +338,24 @@ class UnitWorld:
         return {k: int(getattr(c, k)) for k, _ in _lib.Counters._fields_}
 
     # ---- validity (module.cc:138-139) ------------------------------------------------------------
-    def is_valid_states(self, qs):
+    def is_valid_states(self, qs, out=None):
+        """Batched is_valid_state.  `out` (optional): a contiguous uint8 / bool array of len(qs) that receives the
+        labels in place (e.g. from pyosr.pinned_empty, so that the read-back is a pinned copy too)."""
+        n = len(qs)
+        if out is None:
+            res = np.empty(n, np.uint8)
+        else:
+            if not (isinstance(out, np.ndarray) and out.dtype.itemsize == 1 and out.shape == (n,) and
+                    out.flags.c_contiguous):
+                raise OsrError("out must be a contiguous 1-byte array of len(qs)")
+            res = out.view(np.uint8)
         if isinstance(qs, np.ndarray) and qs.dtype == np.float32 and qs.ndim == 2 and qs.shape[1] == 7:
             q = np.ascontiguousarray(qs)      # float32 samples go up as they are and are widened on the device
-            out = np.empty(len(q), np.uint8)
-            check(self._L.osr_is_valid_states_f32(self._h, _p(q, c_fp), len(q), _p(out, c_u8p)))
-            return out.astype(bool)
-        q = _states(qs)
-        out = np.empty(len(q), np.uint8)
-        check(self._L.osr_is_valid_states(self._h, _p(q, c_dp), len(q), _p(out, c_u8p)))
-        return out.astype(bool)
+            check(self._L.osr_is_valid_states_f32(self._h, _p(q, c_fp), n, _p(res, c_u8p)))
+        else:
+            q = _states(qs)
+            check(self._L.osr_is_valid_states(self._h, _p(q, c_dp), n, _p(res, c_u8p)))
+        return res.view(np.bool_) if out is not None else res.astype(bool)
 
     def is_valid_state(self, q):
         return bool(self.is_valid_states(q)[0])

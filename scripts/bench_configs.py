@@ -119,7 +119,10 @@ def leg_hipoly(O, scale):
     t_build = time.perf_counter() - t
     n = int((1 << 22) * scale)
     q = W.random_states(n, seed=3)
-    v, dt = timed(lambda: uw.is_valid_states(q))
+    _, dt_pageable = timed(lambda: uw.is_valid_states(q))
+    qp = pyosr.pinned_empty((n, 7)); qp[:] = q          # page-locked sample / label arrays (osr_host_alloc)
+    op = pyosr.pinned_empty(n, np.uint8)
+    v, dt = timed(lambda: uw.is_valid_states(qp, out=op))
     c = uw.counters(reset=True)
     ow = world(O.OracleWorld, meshes=(EV, EF, RV, RF))
     m = 1 << 16
@@ -127,7 +130,8 @@ def leg_hipoly(O, scale):
     vo = ow.is_valid_states(q[:m])
     dtc = time.perf_counter() - tc
     return {"leg": "hipoly", "geometry": "G-hi (env %d, robot %d triangles)" % (len(EF), len(RF)), "states": n,
-            "configs_per_s": n / dt, "seconds": dt, "valid_fraction": float(v.mean()),
+            "configs_per_s": n / dt, "seconds": dt, "configs_per_s_pageable_host_arrays": n / dt_pageable,
+            "valid_fraction": float(v.mean()),
             "finalize_seconds (host BVH build + upload)": t_build, "oracle_prefix": m,
             "labels_equal_oracle_on_prefix": bool(np.array_equal(v[:m], vo.astype(bool))),
             "cpu_port": {"configs_per_s": m / dtc, "threads": O.lib().orc_max_threads()}}

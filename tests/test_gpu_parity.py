@@ -698,3 +698,20 @@ def test_swept_windows_on_deep_trees(monkeypatch):
     a = swept.transit_states_to_with_contact(fr2, to2, 1e-4, with_steps=True)
     b = plain.transit_states_to_with_contact(fr2, to2, 1e-4, with_steps=True)
     assert all(np.array_equal(x, y) for x, y in zip(a, b)) and 0 < a[2].sum() < len(fr2)
+
+
+@pytest.mark.gpu
+def test_pinned_host_arrays_give_the_same_labels(uw_org):
+    """pyosr.pinned_empty (osr_host_alloc): page-locked sample / label arrays; same labels, in-place result."""
+    from puzzletunneldiscovery_b200 import pyosr
+    q = W.random_states(300001, seed=95)
+    qp = pyosr.pinned_empty((len(q), 7))
+    qp[:] = q
+    out = pyosr.pinned_empty(len(q), np.uint8)
+    out[:] = 7
+    v = uw_org.is_valid_states(qp, out=out)
+    assert v.dtype == np.bool_ and np.array_equal(v, uw_org.is_valid_states(q)) and out.max() <= 1
+    assert np.shares_memory(v, out)
+    with pytest.raises(Exception):
+        uw_org.is_valid_states(q, out=np.empty(5, np.uint8))
+    del qp, out, v      # the allocation is released with the last view
