@@ -4,6 +4,8 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <atomic>
+#include <thread>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -63,6 +65,8 @@ struct Slot {  // one GPU
   cudaEvent_t ev0 = nullptr, ev1 = nullptr, evp = nullptr, evq = nullptr;
   long long* ready = nullptr;           // device word: states uploaded so far (stream-fed validity launches)
   long long* h_ready = nullptr;         // pinned source values of the copies that advance it
+  char* stage = nullptr;                // pinned staging ring of host calls on pageable buffers
+  size_t stage_cap = 0;
   float4* env_nodes = nullptr; double* env_tris = nullptr;
   float4* rob_nodes = nullptr; double* rob_tris = nullptr;
   uint4* env_qnodes = nullptr; uint4* rob_qnodes = nullptr;  // 32-byte QNodes (qnode.h)
@@ -180,6 +184,7 @@ void free_slot(Slot& s) {
   if (s.evp) cudaEventDestroy(s.evp);
   if (s.evq) cudaEventDestroy(s.evq);
   cudaFree(s.ready);
+  if (s.stage) cudaFreeHost(s.stage);
   if (s.h_ready) cudaFreeHost(s.h_ready);
   for (auto& e : s.feed_ev) if (e) cudaEventDestroy(e);
   if (s.stream3) cudaStreamDestroy(s.stream3);
@@ -669,6 +674,93 @@ static int launch_valid_feed(osr_world* w, Slot& s, const T* d_q, int64_t n, uin
   return OSR_OK;
 }
 
+static int staging_threads() {
+  static int v = [] {
+    const char* e = getenv("OSR_STAGING_THREADS");
+    int x = e ? atoi(e) : 4;
+    return std::max(0, std::min(16, x));
+  }();
+  return v;
+}
+
+static bool is_pageable(const void* p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return true; }
+  return a.type == cudaMemoryTypeUnregistered;
+}
+
+// Stream-fed launch from PAGEABLE host memory.  cudaMemcpyAsync from pageable memory is staged by the driver on
+// the calling thread (~9 GB/s measured, and the launch behind it waits for the whole upload).  Here the kernel is
+// launched first and polls `ready`; worker threads copy the chunks into a ring of pinned staging buffers in
+// parallel and queue the DMA from there; this thread advances `ready` behind the chunks in index order.
+template <typename T>
+static int feed_pageable(osr_world* w, Slot& s, const T* q, int64_t m, int64_t ck, uint8_t* out) {
+  const int nchunks = (int)((m + ck - 1) / ck);
+  const size_t cbytes = (size_t)ck * 7 * sizeof(T);
+  const int R = std::min(nchunks, 8);
+  if (s.stage_cap < (size_t)R * cbytes) {
+    if (s.stage) cudaFreeHost(s.stage);
+    s.stage = nullptr; s.stage_cap = 0;
+    CU(cudaHostAlloc((void**)&s.stage, (size_t)R * cbytes, cudaHostAllocDefault));
+    s.stage_cap = (size_t)R * cbytes;
+  }
+  for (int c = 0; c < nchunks; c++)
+    if (!s.feed_ev[c]) CU(cudaEventCreateWithFlags(&s.feed_ev[c], cudaEventDisableTiming));
+  CU(cudaEventRecord(s.evp, s.stream));
+  CU(cudaStreamWaitEvent(s.stream2, s.evp, 0));
+  CU(cudaStreamWaitEvent(s.stream3, s.evp, 0));
+  CU(cudaMemsetAsync(s.ready, 0, sizeof(long long), s.stream3));
+  CU(cudaEventRecord(s.evq, s.stream3));
+  CU(cudaStreamWaitEvent(s.stream, s.evq, 0));          // the kernel starts behind the reset of `ready`
+  int rc = launch_valid_feed<T>(w, s, (const T*)s.in0.p, m, (uint8_t*)s.out[0].p, s.ready, 0);
+  if (rc) return rc;
+  std::atomic<int> enq[MAX_FEED_CHUNKS];
+  for (int c = 0; c < nchunks; c++) enq[c].store(0, std::memory_order_relaxed);
+  std::atomic<int> err(0);
+  const int nthreads = std::max(1, std::min(nchunks, staging_threads()));
+  auto work = [&](int t) {
+    if (cudaSetDevice(s.dev) != cudaSuccess) err.store(1);
+    for (int c = t; c < nchunks; c += nthreads) {
+      if (c >= R) {   // the staging buffer is free once the DMA of its previous chunk has completed
+        while (!enq[c - R].load(std::memory_order_acquire)) std::this_thread::yield();
+        if (cudaEventSynchronize(s.feed_ev[c - R]) != cudaSuccess) err.store(1);
+      }
+      char* st = s.stage + (size_t)(c % R) * cbytes;
+      const int64_t c0 = (int64_t)c * ck, len = std::min(ck, m - c0);
+      memcpy(st, q + 7 * c0, (size_t)len * 7 * sizeof(T));
+      if (cudaMemcpyAsync((T*)s.in0.p + 7 * c0, st, (size_t)len * 7 * sizeof(T), cudaMemcpyHostToDevice, s.stream2) != cudaSuccess ||
+          cudaEventRecord(s.feed_ev[c], s.stream2) != cudaSuccess)
+        err.store(1);
+      enq[c].store(1, std::memory_order_release);
+    }
+  };
+  std::vector<std::thread> pool;
+  for (int t = 0; t < nthreads; t++) pool.emplace_back(work, t);
+  StreamWriteValue64 wv = stream_write_value64();
+  cudaError_t ce = cudaSuccess;
+  for (int c = 0; c < nchunks; c++) {
+    while (!enq[c].load(std::memory_order_acquire)) std::this_thread::yield();
+    const int64_t upto = std::min((int64_t)(c + 1) * ck, m);
+    if (ce == cudaSuccess) ce = cudaStreamWaitEvent(s.stream3, s.feed_ev[c], 0);
+    s.h_ready[c] = upto;
+    if (ce == cudaSuccess && (!wv || wv(s.stream3, (unsigned long long)(uintptr_t)s.ready, (unsigned long long)upto, 0) != 0))
+      ce = cudaMemcpyAsync(s.ready, s.h_ready + c, sizeof(long long), cudaMemcpyHostToDevice, s.stream3);
+  }
+  for (auto& th : pool) th.join();
+  if (ce != cudaSuccess || err.load()) {
+    // the kernel may still be waiting for input that will not come: release it before reporting
+    long long all = m;
+    cudaMemcpyAsync(s.ready, &all, sizeof(long long), cudaMemcpyHostToDevice, s.stream3);
+    cudaStreamSynchronize(s.stream3);
+    cudaStreamSynchronize(s.stream);
+    return fail(OSR_ECUDA, std::string("staged upload failed: ") + cudaGetErrorString(ce != cudaSuccess ? ce : cudaGetLastError()));
+  }
+  CU(cudaMemcpyAsync(out, s.out[0].p, (size_t)m, cudaMemcpyDeviceToHost, s.stream));
+  CU(cudaEventRecord(s.evq, s.stream3));
+  CU(cudaStreamWaitEvent(s.stream, s.evq, 0));
+  return OSR_OK;
+}
+
 template <typename T>
 static int valid_states_host(osr_world* w, const T* q, int64_t n, uint8_t* out) {
   int rc = check_ready(w);
@@ -700,6 +792,11 @@ static int valid_states_host(osr_world* w, const T* q, int64_t n, uint8_t* out) 
       int64_t m = hi - lo;
       int64_t ck = std::max(chunk, (m + MAX_FEED_CHUNKS - 1) / MAX_FEED_CHUNKS);
       ck = (ck + 1023) / 1024 * 1024;
+      if (staging_threads() > 0 && m > ck && is_pageable(q + 7 * lo)) {
+        rc = feed_pageable<T>(w, s, q + 7 * lo, m, ck, out + lo);
+        if (rc) return rc;
+        continue;
+      }
       // The word is advanced from a third stream that waits on an event behind each chunk: a write queued on
       // the copy stream itself would drain the copy engine's pipeline between chunks (~20 us per chunk).
       CU(cudaEventRecord(s.evp, s.stream));
