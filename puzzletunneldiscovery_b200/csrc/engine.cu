@@ -735,7 +735,13 @@ static int feed_pageable(osr_world* w, Slot& s, const T* q, int64_t m, int64_t c
     }
   };
   std::vector<std::thread> pool;
-  for (int t = 0; t < nthreads; t++) pool.emplace_back(work, t);
+  for (int t = 0; t < nthreads; t++) {
+    try {
+      pool.emplace_back(work, t);
+    } catch (...) {   // no thread to be had: this thread stages that share itself (the DMA does not depend on `ready`)
+      work(t);
+    }
+  }
   StreamWriteValue64 wv = stream_write_value64();
   cudaError_t ce = cudaSuccess;
   for (int c = 0; c < nchunks; c++) {
