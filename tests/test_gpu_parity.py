@@ -715,3 +715,29 @@ def test_pinned_host_arrays_give_the_same_labels(uw_org):
     with pytest.raises(Exception):
         uw_org.is_valid_states(q, out=np.empty(5, np.uint8))
     del qp, out, v      # the allocation is released with the last view
+
+
+@pytest.mark.gpu
+def test_clearance_stats_edge_cases(uw_org, ow_org, oracle_mod):
+    """One and two points per candidate (median = the value / the mean of both), targets closer than one step
+    (the walk does not move: distance 0), an empty batch, and bad arguments raising like every other call."""
+    q = W.random_states(4096, seed=96)
+    cq = np.ascontiguousarray(q[uw_org.is_valid_states(q)][:3])
+    for npoint in (1, 2):
+        to = W.touch_rays(np.repeat(cq, npoint, axis=0), 3 * npoint, seed=97)[1].reshape(3, npoint, 7)
+        st, d = uw_org.clearance_stats(cq, to, VD_TOUCH, with_distances=True)
+        lf = ow_org.transit_states_to_with_contact(np.repeat(cq, npoint, axis=0), to.reshape(-1, 7), VD_TOUCH)[0]
+        od = np.array([oracle_mod.distance(cq[i // npoint], s) for i, s in enumerate(lf)]).reshape(3, npoint)
+        assert np.abs(d - od).max() < 1e-13
+        assert np.array_equal(st[:, 0], np.median(d, axis=1)) and np.array_equal(st[:, 1], d.max(1))
+        assert np.array_equal(st[:, 2], d.min(1)) and np.abs(st[:, 3] - d.mean(1)).max() < 1e-15
+        assert np.abs(st[:, 4] - d.std(1)).max() < 1e-15
+    near = np.repeat(cq[:, None, :], 4, axis=1).copy()
+    near[:, :, 0] += 1e-6                       # closer than verify_delta: transitStateTo returns `from`
+    st = uw_org.clearance_stats(cq, near, VD_TOUCH)
+    assert np.array_equal(st, np.zeros((3, 5)))
+    assert uw_org.clearance_stats(np.zeros((0, 7)), np.zeros((0, 4, 7)), VD_TOUCH).shape == (0, 5)
+    with pytest.raises(Exception):
+        uw_org.clearance_stats(cq, near, 0.0)
+    with pytest.raises(Exception):
+        uw_org.clearance_stats(cq, near[:2], VD_TOUCH)
