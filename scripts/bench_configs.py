@@ -22,6 +22,7 @@ from puzzletunneldiscovery_b200 import pyosr, workloads as W  # noqa: E402
 
 A = W.assets_dir()
 VD_TOUCH = 0.0125 / 8   # /root/reference/src/GP/condor_touch_configuration.py:35,92
+PREFIX_SCALE = 1        # --prefix-scale: multiplies the size of every oracle-checked prefix
 
 
 def world(cls, which="org", centre=None, meshes=None):
@@ -59,7 +60,7 @@ def leg_touch(O, scale, fine=False):
     n = int((1 << 12 if fine else 1 << 18) * scale)
     fr, to = W.touch_rays(fr0, n, seed=1)
     (lf, fh, isf, ft, tt, st), dt = timed(lambda: uw.transit_states_to_with_contact(fr, to, vd, with_steps=True))
-    m = min(n, 64 if fine else 2048)
+    m = min(n, (64 if fine else 2048) * PREFIX_SCALE)
     tc = time.perf_counter()
     olf, ofh, oisf, oft, ott, ocnt = ow.transit_states_to_with_contact(fr[:m], to[:m], vd, counters=True)
     dtc = time.perf_counter() - tc
@@ -92,7 +93,7 @@ def leg_edges(O, scale):
     vd = 1.51641e-5
     uw.counters(reset=True)     # the timed call runs twice (warm-up + measurement): counters below are halved
     res, dt = timed(lambda: uw.is_valid_transitions(fr, to, vd))
-    m = 256
+    m = min(len(fr), 256 * PREFIX_SCALE)
     tc = time.perf_counter()
     ores, ocnt = ow.is_valid_transitions(fr[:m], to[:m], vd, counters=True)
     dtc = time.perf_counter() - tc
@@ -248,7 +249,7 @@ def leg_ompl(O, scale):
     uw.counters(reset=True)
     (ok, nd), dt = timed(lambda: uw.ompl_validate_motion_pairs(a, b, extent, res, with_counts=True))
     c = uw.counters(reset=True)
-    m = 64
+    m = min(len(a), 64 * PREFIX_SCALE)
     dc = (uw.get_ompl_center(1).astype(np.float32) - uw.robot_center.astype(np.float32)).astype(np.float64) * uw.scene_scale
     tc = time.perf_counter()
     want, ond = ow.ompl_check_motions(a[:m], b[:m], uw.scene_scale, dc, extent, res)
@@ -266,7 +267,10 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--legs", default="touch,touch_fine,edges,hipoly,contacts,clearance,keyconf,ompl_motions")
     ap.add_argument("--scale", type=float, default=1.0)
+    ap.add_argument("--prefix-scale", type=int, default=1)
     args = ap.parse_args()
+    global PREFIX_SCALE
+    PREFIX_SCALE = max(1, args.prefix_scale)
     from oracle import oracle as O
     legs = {"touch": lambda: leg_touch(O, args.scale), "touch_fine": lambda: leg_touch(O, args.scale, fine=True),
             "edges": lambda: leg_edges(O, args.scale), "hipoly": lambda: leg_hipoly(O, args.scale),
