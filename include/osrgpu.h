@@ -202,11 +202,15 @@ int osr_rasterize_barycentric(osr_world* w, const float* uv, const float* bary, 
  * OmplDriver::validateStates (lib/pyse3ompl/ompldriver.cc:566-589) = isValid after translateOMPLStateToUnitState;
  * OmplDriver::validateMotionPairs (:592-621) = DiscreteMotionValidator::checkMotion
  * (third-party/ompl.app/ompl/src/ompl/base/src/DiscreteMotionValidator.cpp:96-150): out[i]=1 iff s2 and every
- * interior point m/nd of OMPL's SE(3) interpolation are valid, nd = max(ceil(|dt| / (resolution*trans_extent)),
- * ceil(acos|q1.q2| / (resolution*pi/2))).  trans_extent = diagonal of the planner's translation bounds (OMPL
- * frame); resolution = the state-validity-checking resolution (OmplDriver::setCDRes).  nd_out optional. */
-int osr_ompl_validate_states(osr_world* w, const double* q_ompl, int64_t n, uint8_t* out);
-int osr_ompl_check_motions(osr_world* w, const double* q0, const double* q1, int64_t n, double trans_extent,
+ * interior point m/nd of OMPL's SE(3) interpolation are valid, nd = max(ceil(|dt| / (resolution*extent)),
+ * ceil(acos|q1.q2| / (resolution*pi/2))).  "Valid" is FCLStateValidityChecker::isValid
+ * (third-party/ompl.app/src/omplapp/geometry/detail/FCLStateValidityChecker.h:103): satisfiesBounds AND collision
+ * free.  bounds = {lo x y z, hi x y z} of the planner's RealVectorBounds (OmplDriver::setBounds, OMPL frame);
+ * extent = its diagonal (RealVectorStateSpace::getMaximumExtent); the SO(3) part of satisfiesBounds is
+ * |norm(q) - 1| < 1e-9.  osr_ompl_validate_states accepts bounds = NULL (collision only); check_motions needs them.
+ * resolution = the state-validity-checking resolution (OmplDriver::setCDRes).  nd_out optional. */
+int osr_ompl_validate_states(osr_world* w, const double* q_ompl, int64_t n, const double* bounds, uint8_t* out);
+int osr_ompl_check_motions(osr_world* w, const double* q0, const double* q1, int64_t n, const double* bounds,
                            double resolution, uint8_t* out, int64_t* nd_out);
 
 /* Device-resident variants (pointers on the handle's first device).  Launch only; the caller

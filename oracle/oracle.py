@@ -73,8 +73,9 @@ def lib():
     L.orc_contact_multiplicity.argtypes = [_dp]
     L.orc_surface_map.argtypes = [_dp, _ip, C.c_longlong, _dp, _ip, C.c_longlong, C.c_longlong, _ip, _dp]
     L.orc_surface_map.restype = C.c_longlong
-    L.orc_ompl_check_motions.argtypes = [C.c_void_p, _dp, _dp, C.c_longlong, C.c_double, _dp, C.c_double, C.c_double,
-                                         _u8p, _llp, C.c_int]
+    L.orc_ompl_check_motions.argtypes = [C.c_void_p, _dp, _dp, C.c_longlong, C.c_double, _dp, _dp, C.c_double,
+                                         C.c_double, _u8p, _llp, C.c_int]
+    L.orc_ompl_validate_states.argtypes = [C.c_void_p, _dp, C.c_longlong, C.c_double, _dp, _dp, _u8p]
     ref = os.path.join(_HERE, "_ref", "libmoller97d.so")
     if os.path.exists(ref):
         _MOLLER = C.CDLL(ref)
@@ -267,13 +268,33 @@ class OracleWorld:
                                         _ptr(cnt, _llp), threads)
         return (out, cnt) if counters else out
 
-    def ompl_check_motions(self, q0, q1, scale, dc, trans_extent, resolution, threads=0):
-        """DiscreteMotionValidator::checkMotion per OMPL-frame row pair -> (valid uint8[N], nd int64[N])."""
+    @staticmethod
+    def _bounds(bounds):
+        if bounds is None:
+            return None
+        return np.ascontiguousarray(np.concatenate([np.asarray(bounds[0], np.float64).reshape(3),
+                                                    np.asarray(bounds[1], np.float64).reshape(3)]))
+
+    def ompl_validate_states(self, q, scale, dc, bounds=None):
+        """OmplDriver::validateStates: satisfiesBounds && collision free per OMPL-frame row -> uint8[N]."""
+        q = _states(q)
+        dc = np.ascontiguousarray(dc, dtype=np.float64)
+        b = self._bounds(bounds)
+        out = np.zeros(len(q), np.uint8)
+        self.L.orc_ompl_validate_states(self.h, _ptr(q, _dp), len(q), float(scale), _ptr(dc, _dp), _ptr(b, _dp),
+                                        _ptr(out, _u8p))
+        return out
+
+    def ompl_check_motions(self, q0, q1, scale, dc, bounds, resolution, threads=0):
+        """DiscreteMotionValidator::checkMotion per OMPL-frame row pair -> (valid uint8[N], nd int64[N]).
+        bounds = (mins, maxs) of the translation; the segment length is resolution x their diagonal."""
         q0 = _states(q0); q1 = _states(q1)
         dc = np.ascontiguousarray(dc, dtype=np.float64)
+        b = self._bounds(bounds)
+        extent = float(np.sqrt(((b[3:] - b[:3]) ** 2).sum()))
         out = np.zeros(len(q0), np.uint8); nd = np.zeros(len(q0), np.int64)
         self.L.orc_ompl_check_motions(self.h, _ptr(q0, _dp), _ptr(q1, _dp), len(q0), float(scale), _ptr(dc, _dp),
-                                      float(resolution * trans_extent), float(resolution * 0.5 * np.pi),
+                                      _ptr(b, _dp), float(resolution * extent), float(resolution * 0.5 * np.pi),
                                       _ptr(out, _u8p), _ptr(nd, _llp), threads)
         return out, nd
 

@@ -1006,8 +1006,33 @@ static void ompl_to_unit(const double* o, double scale, const double* dc, double
   u[0] = scale * o[0] - rx; u[1] = scale * o[1] - ry; u[2] = scale * o[2] - rz;
   u[3] = w; u[4] = x; u[5] = y; u[6] = z;
 }
+// SpaceInformation::satisfiesBounds for SE(3): RealVectorStateSpace (spaces/src/RealVectorStateSpace.cpp:200-208)
+// and SO3StateSpace (spaces/src/SO3StateSpace.cpp:175-179, 211-214).  bounds = lo[3] hi[3]; null = no bounds test.
+static bool ompl_in_bounds(const double* bounds, const double* o) {
+  if (!bounds) return true;
+  const double eps = std::numeric_limits<double>::epsilon();
+  for (int k = 0; k < 3; k++)
+    if (o[k] - eps > bounds[3 + k] || o[k] + eps < bounds[k]) return false;
+  double n2 = o[3] * o[3] + o[4] * o[4] + o[5] * o[5] + o[6] * o[6];
+  double nrm = (std::fabs(n2 - 1.0) > eps) ? std::sqrt(n2) : 1.0;
+  return std::fabs(nrm - 1.0) < 1e-9;
+}
+// FCLStateValidityChecker::isValid (omplapp/geometry/detail/FCLStateValidityChecker.h:103)
+static bool ompl_state_valid(World* w, const double* bounds, const double* o, double scale, const double* dc) {
+  if (!ompl_in_bounds(bounds, o)) return false;
+  double u[7];
+  ompl_to_unit(o, scale, dc, u);
+  return w->is_valid(u);
+}
+// OmplDriver::validateStates (lib/pyse3ompl/ompldriver.cc:566-589): si->isValid per row
+void orc_ompl_validate_states(void* h, const double* q, long long N, double scale, const double* dc,
+                              const double* bounds, uint8_t* out) {
+  World* w = (World*)h;
+  for (long long i = 0; i < N; i++) out[i] = ompl_state_valid(w, bounds, q + 7 * i, scale, dc) ? 1 : 0;
+}
 void orc_ompl_check_motions(void* h, const double* q0, const double* q1, long long N, double scale, const double* dc,
-                            double seg_trans, double seg_rot, uint8_t* out, long long* nd_out, int threads) {
+                            const double* bounds, double seg_trans, double seg_rot, uint8_t* out, long long* nd_out,
+                            int threads) {
   World* w = (World*)h;
 #ifdef _OPENMP
   int nt = threads > 0 ? threads : omp_get_max_threads();
@@ -1022,9 +1047,7 @@ void orc_ompl_check_motions(void* h, const double* q0, const double* q1, long lo
     long long n1 = (long long)std::ceil(dtr / seg_trans), n2 = (long long)std::ceil(theta / seg_rot);
     long long nd = n1 > n2 ? n1 : n2;
     if (nd_out) nd_out[i] = nd;
-    double u[7];
-    ompl_to_unit(b, scale, dc, u);
-    bool result = w->is_valid(u);
+    bool result = ompl_state_valid(w, bounds, b, scale, dc);
     if (result && nd >= 2) {
       std::vector<std::pair<long long, long long>> pos;
       size_t head = 0;
@@ -1042,8 +1065,7 @@ void orc_ompl_check_motions(void* h, const double* q0, const double* q1, long lo
         } else {
           for (int k = 0; k < 4; k++) o[3 + k] = a[3 + k];
         }
-        ompl_to_unit(o, scale, dc, u);
-        if (!w->is_valid(u)) { result = false; break; }
+        if (!ompl_state_valid(w, bounds, o, scale, dc)) { result = false; break; }
         head++;
         if (x.first < mid) pos.emplace_back(x.first, mid - 1);
         if (x.second > mid) pos.emplace_back(mid + 1, x.second);

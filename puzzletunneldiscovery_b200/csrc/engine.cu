@@ -329,13 +329,19 @@ int check_ready(osr_world* w) {
   return OSR_OK;
 }
 
+thread_local bool g_feed_timed_out = false;   // set when a stream-fed K1 launch gave up waiting for its input
 int check_device_error(osr_world* w, Slot& s) {
   int flag = 0;
   CU(cudaMemcpyAsync(&flag, s.err, sizeof(int), cudaMemcpyDeviceToHost, s.stream));
   CU(cudaStreamSynchronize(s.stream));
   if (flag) {
     cudaMemsetAsync(s.err, 0, sizeof(int), s.stream);
-    if (flag == 2) return fail(OSR_ECUDA, "validity kernel timed out waiting for its input upload");
+    if (flag == 2) {
+      g_feed_timed_out = true;
+      return fail(OSR_ECUDA, "validity kernel timed out waiting for its input upload");
+    }
+    if (flag == 3)
+      return fail(OSR_EINVAL, "verify_delta <= 0 on a segment of non-zero length (the reference's walk never ends)");
     return fail(OSR_EOVERFLOW, "device traversal stack spill area exhausted");
   }
   (void)w;
@@ -539,6 +545,29 @@ int osr_get_counters(osr_world* w, osr_counters* out, int reset) {
 }
 
 // ---- launch helpers ---------------------------------------------------------------------------
+// How long a stream-fed K1 launch waits for an upload before it gives up (the host then re-runs the call with
+// every copy queued in front of the launch).  Generous: the wait only ends early when something is wrong.
+static unsigned long long feed_timeout_ns() {
+  static unsigned long long v = [] {
+    const char* e = getenv("OSR_FEED_TIMEOUT_S");
+    double sec = e ? atof(e) : 20.0;
+    if (!(sec > 0.0)) sec = 20.0;
+    return (unsigned long long)(sec * 1e9);
+  }();
+  return v;
+}
+// Tools that serialise launches (CUDA_LAUNCH_BLOCKING, or an injected profiler / sanitizer that replays kernels)
+// would make a kernel launched BEFORE its uploads are queued wait for input that cannot arrive.
+static bool launches_may_block() {
+  static bool v = [] {
+    const char* lb = getenv("CUDA_LAUNCH_BLOCKING");
+    if (lb && atoi(lb) != 0) return true;
+    const char* inj = getenv("CUDA_INJECTION64_PATH");
+    if (inj && *inj) return true;
+    return getenv("OSR_FEED_SAFE") != nullptr;
+  }();
+  return v;
+}
 static osr::DfsParams dfs_params(const osr_world* w, const Slot& s) {
   osr::DfsParams P;
   P.env_q = s.env_qnodes; P.rob_q = s.rob_qnodes;
@@ -553,6 +582,7 @@ static osr::DfsParams dfs_params(const osr_world* w, const Slot& s) {
   P.error_flag = s.err;
   P.ready = nullptr;
   P.ready_floor = 0;
+  P.feed_timeout_ns = feed_timeout_ns();
   return P;
 }
 
@@ -767,12 +797,11 @@ static int feed_pageable(osr_world* w, Slot& s, const T* q, int64_t m, int64_t c
   return OSR_OK;
 }
 
+// `safe`: every upload is queued in front of the launch and the kernel starts behind the last one (it never
+// polls) -- the form that cannot starve under launch-serialising tools, a time-sliced GPU or a slow source.
 template <typename T>
-static int valid_states_host(osr_world* w, const T* q, int64_t n, uint8_t* out) {
-  int rc = check_ready(w);
-  if (rc) return rc;
-  if (n < 0 || (n > 0 && (!q || !out))) return fail(OSR_EINVAL, "bad arguments");
-  if (n == 0) return OSR_OK;
+static int valid_states_host_impl(osr_world* w, const T* q, int64_t n, uint8_t* out, bool safe) {
+  int rc;
   std::lock_guard<std::mutex> lk(w->mu);
   int parts = (int)w->slots.size();
   const int64_t chunk = host_chunk_states();
@@ -798,7 +827,7 @@ static int valid_states_host(osr_world* w, const T* q, int64_t n, uint8_t* out) 
       int64_t m = hi - lo;
       int64_t ck = std::max(chunk, (m + MAX_FEED_CHUNKS - 1) / MAX_FEED_CHUNKS);
       ck = (ck + 1023) / 1024 * 1024;
-      if (staging_threads() > 0 && m > ck && is_pageable(q + 7 * lo)) {
+      if (!safe && staging_threads() > 0 && m > ck && is_pageable(q + 7 * lo)) {
         rc = feed_pageable<T>(w, s, q + 7 * lo, m, ck, out + lo);
         if (rc) return rc;
         continue;
@@ -821,7 +850,8 @@ static int valid_states_host(osr_world* w, const T* q, int64_t n, uint8_t* out) 
         if (!wv || wv(s.stream3, (unsigned long long)(uintptr_t)s.ready, (unsigned long long)(c0 + len), 0) != 0)
           CU(cudaMemcpyAsync(s.ready, s.h_ready + c, sizeof(long long), cudaMemcpyHostToDevice, s.stream3));
       }
-      static const bool wait_all = getenv("OSR_FEED_WAIT_ALL") != nullptr;  // probe: kernel starts after the last chunk
+      static const bool wait_all_env = getenv("OSR_FEED_WAIT_ALL") != nullptr;  // probe: kernel starts after the last chunk
+      const bool wait_all = wait_all_env || safe;
       CU(cudaStreamWaitEvent(s.stream, s.feed_ev[wait_all ? c - 1 : 0], 0));
       rc = launch_valid_feed<T>(w, s, (const T*)s.in0.p, m, (uint8_t*)s.out[0].p, s.ready,
                                 (long long)(wait_all ? m : std::min(ck, m)));  // the launch waits for that event
@@ -858,6 +888,24 @@ static int valid_states_host(osr_world* w, const T* q, int64_t n, uint8_t* out) 
     if (rc) return rc;
   }
   return OSR_OK;
+}
+
+template <typename T>
+static int valid_states_host(osr_world* w, const T* q, int64_t n, uint8_t* out) {
+  int rc = check_ready(w);
+  if (rc) return rc;
+  if (n < 0 || (n > 0 && (!q || !out))) return fail(OSR_EINVAL, "bad arguments");
+  if (n == 0) return OSR_OK;
+  g_feed_timed_out = false;
+  rc = valid_states_host_impl<T>(w, q, n, out, launches_may_block());
+  if (rc == OSR_ECUDA && g_feed_timed_out) {   // the fed kernel starved: same call, nothing to wait for
+    g_feed_timed_out = false;
+    for (auto& s : w->slots) {
+      if (cudaSetDevice(s.dev) == cudaSuccess) cudaStreamSynchronize(s.stream);
+    }
+    rc = valid_states_host_impl<T>(w, q, n, out, true);
+  }
+  return rc;
 }
 
 extern "C" {
@@ -936,6 +984,10 @@ int osr_transit_states_to_with_contact(osr_world* w, const double* from, const d
   if (n < 0 || (n > 0 && (!from || !to || !vd)) || (vd_count != 1 && vd_count != n))
     return fail(OSR_EINVAL, "bad arguments");
   if (n == 0) return OSR_OK;
+  // verify_delta < 0 never terminates in the reference (unit_world.cc:445-470); 0 is legal only on zero-length
+  // segments (the kernel reports those that are not); NaN falls through the reference's comparisons and is passed on
+  for (int64_t i = 0; i < vd_count; i++)
+    if (vd[i] < 0.0) return fail(OSR_EINVAL, "verify_delta must not be negative");
   std::lock_guard<std::mutex> lk(w->mu);
   return transit_host(w, from, to, n, vd, vd_count, 0.0, 0, last_free, first_hit, is_free, free_tau, touch_tau, steps);
 }
@@ -945,6 +997,7 @@ int osr_is_valid_transitions(osr_world* w, const double* from, const double* to,
   int rc = check_ready(w);
   if (rc) return rc;
   if (n < 0 || (n > 0 && (!from || !to || !out))) return fail(OSR_EINVAL, "bad arguments");
+  if (initial_verify_delta < 0.0) return fail(OSR_EINVAL, "verify_delta must not be negative");
   if (n == 0) return OSR_OK;
   std::lock_guard<std::mutex> lk(w->mu);
   return transit_host(w, from, to, n, nullptr, 1, initial_verify_delta, 1, nullptr, nullptr, out, nullptr, nullptr,
@@ -956,6 +1009,7 @@ int osr_transit_states_device(osr_world* w, const double* d_from, const double* 
                               double* d_touch_tau, int64_t* d_steps) {
   int rc = check_ready(w);
   if (rc) return rc;
+  if (vd < 0.0) return fail(OSR_EINVAL, "verify_delta must not be negative");
   if (n <= 0) return n == 0 ? OSR_OK : fail(OSR_EINVAL, "bad n");
   std::lock_guard<std::mutex> lk(w->mu);
   Slot& s = w->slots[0];
@@ -967,6 +1021,7 @@ int osr_is_valid_transitions_device(osr_world* w, const double* d_from, const do
                                     double initial_verify_delta, uint8_t* d_out) {
   int rc = check_ready(w);
   if (rc) return rc;
+  if (initial_verify_delta < 0.0) return fail(OSR_EINVAL, "verify_delta must not be negative");
   if (n <= 0) return n == 0 ? OSR_OK : fail(OSR_EINVAL, "bad n");
   std::lock_guard<std::mutex> lk(w->mu);
   Slot& s = w->slots[0];
@@ -994,9 +1049,10 @@ void* osr_stream(osr_world* w) { return (w && !w->slots.empty()) ? (void*)w->slo
 int osr_sync(osr_world* w) {
   int rc = check_ready(w);
   if (rc) return rc;
-  for (auto& s : w->slots) {
+  for (auto& s : w->slots) {   // also surfaces the device error flag of launch-only (_device) calls
     CU(cudaSetDevice(s.dev));
-    CU(cudaStreamSynchronize(s.stream));
+    rc = check_device_error(w, s);
+    if (rc) return rc;
   }
   return OSR_OK;
 }
@@ -1498,23 +1554,43 @@ int osr_rasterize_barycentric(osr_world* w, const float* uv, const float* bary, 
 }
 
 // ---- OMPL-frame batched validators (OmplDriver::validateStates / validateMotionPairs, ompldriver.cc:566-621) ----
-int osr_ompl_validate_states(osr_world* w, const double* q_ompl, int64_t n, uint8_t* out) {
+static int ompl_bounds_ok(const double* bounds) {
+  if (!bounds) return 0;
+  for (int k = 0; k < 3; k++)
+    if (!(bounds[3 + k] >= bounds[k])) return 0;
+  return 1;
+}
+int osr_ompl_validate_states(osr_world* w, const double* q_ompl, int64_t n, const double* bounds, uint8_t* out) {
   int rc = check_ready(w);
   if (rc) return rc;
-  if (n < 0 || (n > 0 && (!q_ompl || !out))) return fail(OSR_EINVAL, "bad arguments");
+  if (n < 0 || (n > 0 && (!q_ompl || !out)) || (bounds && !ompl_bounds_ok(bounds)))
+    return fail(OSR_EINVAL, "bad arguments");
   if (n == 0) return OSR_OK;
   std::vector<double> u((size_t)n * 7);
   rc = osr_translate_ompl_to_unit(w, q_ompl, n, u.data());
   if (rc) return rc;
-  return osr_is_valid_states(w, u.data(), n, out);
+  rc = osr_is_valid_states(w, u.data(), n, out);
+  if (rc || !bounds) return rc;
+  // FCLStateValidityChecker::isValid = si_->satisfiesBounds(state) && collision free
+  for (int64_t i = 0; i < n; i++)
+    if (out[i] && !osr::ompl_satisfies_bounds(bounds, bounds + 3, q_ompl + 7 * i)) out[i] = 0;
+  return OSR_OK;
 }
 
-int osr_ompl_check_motions(osr_world* w, const double* q0, const double* q1, int64_t n, double trans_extent,
+int osr_ompl_check_motions(osr_world* w, const double* q0, const double* q1, int64_t n, const double* bounds,
                            double resolution, uint8_t* out, int64_t* nd_out) {
   int rc = check_ready(w);
   if (rc) return rc;
-  if (n < 0 || (n > 0 && (!q0 || !q1 || !out)) || !(trans_extent > 0.0) || !(resolution > 0.0))
+  if (n < 0 || (n > 0 && (!q0 || !q1 || !out)) || !ompl_bounds_ok(bounds) || !(resolution > 0.0))
     return fail(OSR_EINVAL, "bad arguments");
+  // RealVectorStateSpace::getMaximumExtent (spaces/src/RealVectorStateSpace.cpp:167-176)
+  double trans_extent = 0.0;
+  for (int k = 0; k < 3; k++) {
+    const double d = bounds[3 + k] - bounds[k];
+    trans_extent += d * d;
+  }
+  trans_extent = std::sqrt(trans_extent);
+  if (!(trans_extent > 0.0)) return fail(OSR_EINVAL, "translation bounds have no extent");
   const double ident[7] = {0, 0, 0, 1, 0, 0, 0};
   if (memcmp(w->perturb, ident, sizeof(ident)) != 0)
     return fail(OSR_EINVAL, "OMPL-frame motion checks need the identity perturbation");
@@ -1523,6 +1599,7 @@ int osr_ompl_check_motions(osr_world* w, const double* q0, const double* q1, int
   osr::OmplFrame F;
   F.scale = (double)w->scene_scale;
   for (int k = 0; k < 3; k++) F.dc[k] = (double)(w->ompl_centre[k] - w->centre[k]) * (double)w->scene_scale;
+  for (int k = 0; k < 3; k++) { F.lo[k] = bounds[k]; F.hi[k] = bounds[3 + k]; }
   F.seg_trans = resolution * trans_extent;
   F.seg_rot = resolution * (0.5 * 3.14159265358979323846);
   int parts = (int)w->slots.size();

@@ -607,7 +607,17 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB)
     double lf[7], fh[7];
 #pragma unroll
     for (int k = 0; k < 7; k++) { lf[k] = a[k]; fh[k] = b[k]; }
-    if (!(vd >= dist)) {
+    // A NaN distance or verify_delta fails both `verify_delta >= dist` and `delta <= dist` of the reference
+    // (unit_world.cc:443-447): its loop body never runs and it returns (from, from, false, 0, 0).  With
+    // verify_delta <= 0 the reference's walk never ends; here that is an argument error (error flag 3, same tuple).
+    const bool nan_walk = !(dist == dist) || !(vd == vd);
+    const bool bad_vd = !nan_walk && !(vd >= dist) && !(vd > 0.0);
+    if (nan_walk || bad_vd) {
+#pragma unroll
+      for (int k = 0; k < 7; k++) fh[k] = a[k];
+      touch_tau = 0.0;
+      if (bad_vd && lane == 0) atomicExch(P.error_flag, 3);
+    } else if (!(vd >= dist)) {
       const double inv_dist = 1.0 / dist;
       double carry = 0.0;       // delta of the last step of the previous tile (0 before the first)
       double prev_tau = 0.0;    // tau of that step
@@ -658,6 +668,7 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB)
           }
           const unsigned tried = __ballot_sync(FULL, mine_w);   // a prefix of the lanes
           __syncwarp();
+          if (tried == 0) { exact_next = true; continue; }      // cannot happen for finite inputs; never spin
           const unsigned blocked = traverse_tile<MODE_SWEPT>(P, S, C, tried, lane);
           if (C.overflow) { done = true; break; }
           __syncwarp();
@@ -789,7 +800,31 @@ struct OmplFrame {
   double dc[3];       // (ompl centre - centre) * scale
   double seg_trans;   // resolution * maximum extent of the translation bounds
   double seg_rot;     // resolution * pi/2
+  double lo[3], hi[3];  // RealVectorBounds of the translation (OmplDriver::setBounds, ompldriver.cc:680-685)
 };
+
+// SpaceInformation::satisfiesBounds of an OMPL-frame SE(3) row x y z qx qy qz qw, the first half of
+// FCLStateValidityChecker::isValid (third-party/ompl.app/src/omplapp/geometry/detail/FCLStateValidityChecker.h:103):
+// RealVectorStateSpace::satisfiesBounds (spaces/src/RealVectorStateSpace.cpp:200-208, machine-epsilon slack) and
+// SO3StateSpace::satisfiesBounds (spaces/src/SO3StateSpace.cpp:175-179, 211-214: |norm - 1| < 1e-9).
+OSR_HD bool ompl_satisfies_bounds(const double* lo, const double* hi, const double* o) {
+  const double eps = 2.220446049250313e-16;
+  for (int k = 0; k < 3; k++)
+    if (o[k] - eps > hi[k] || o[k] + eps < lo[k]) return false;
+  const double n2 = o[3] * o[3] + o[4] * o[4] + o[5] * o[5] + o[6] * o[6];
+  const double nrm = (fabs(n2 - 1.0) > eps) ? sqrt(n2) : 1.0;
+  return fabs(nrm - 1.0) < 1e-9;
+}
+// Both end points so far inside the bounds (and so close to unit norm) that no interpolated point can fail
+// satisfiesBounds whatever the rounding of the lerp / slerp: such motions skip the per-point bounds test.
+OSR_HD bool ompl_safely_inside(const double* lo, const double* hi, const double* o) {
+  for (int k = 0; k < 3; k++) {
+    const double m = 1e-12 * (1.0 + fabs(lo[k]) + fabs(hi[k]));
+    if (!(o[k] >= lo[k] + m && o[k] <= hi[k] - m)) return false;
+  }
+  const double n2 = o[3] * o[3] + o[4] * o[4] + o[5] * o[5] + o[6] * o[6];
+  return fabs(n2 - 1.0) < 1e-10;
+}
 
 __device__ __forceinline__ double ompl_arc_length(const double* a, const double* b) {
   double dq = fabs(a[3] * b[3] + a[4] * b[4] + a[5] * b[5] + a[6] * b[6]);
@@ -797,31 +832,38 @@ __device__ __forceinline__ double ompl_arc_length(const double* a, const double*
   return acos(dq);
 }
 
-// OMPL-frame interpolation at t, then the unit-frame state (w-first) of the result
-__device__ __forceinline__ void ompl_point_to_unit(const OmplFrame& F, const double* a, const double* b, double theta,
-                                                   double t, double* s) {
-  double p[3], q[4];  // q = x y z w
+// OMPL-frame interpolation at t (RealVectorStateSpace lerp x SO3StateSpace::interpolate): row x y z qx qy qz qw
+__device__ __forceinline__ void ompl_point(const double* a, const double* b, double theta, double t, double* o) {
 #pragma unroll
-  for (int k = 0; k < 3; k++) p[k] = a[k] + (b[k] - a[k]) * t;
+  for (int k = 0; k < 3; k++) o[k] = a[k] + (b[k] - a[k]) * t;
   if (theta > 2.220446049250313e-16) {
     double d = 1.0 / sin(theta), s0 = sin((1.0 - t) * theta), s1 = sin(t * theta);
     double dq = a[3] * b[3] + a[4] * b[4] + a[5] * b[5] + a[6] * b[6];
     if (dq < 0) s1 = -s1;
 #pragma unroll
-    for (int k = 0; k < 4; k++) q[k] = (a[3 + k] * s0 + b[3 + k] * s1) * d;
+    for (int k = 0; k < 4; k++) o[3 + k] = (a[3 + k] * s0 + b[3 + k] * s1) * d;
   } else {
 #pragma unroll
-    for (int k = 0; k < 4; k++) q[k] = a[3 + k];
+    for (int k = 0; k < 4; k++) o[3 + k] = a[3 + k];
   }
-  double w = q[3], x = q[0], y = q[1], z = q[2];
+}
+// the unit-frame state (w-first) of an OMPL-frame row (translateOMPLStateToUnitState, identity perturbation)
+__device__ __forceinline__ void ompl_row_to_unit(const OmplFrame& F, const double* o, double* s) {
+  double w = o[6], x = o[3], y = o[4], z = o[5];
   quat_normalize(w, x, y, z);
   // Eigen quaternion * vector: v + w (2 u x v) + u x (2 u x v)
   double uvx = 2.0 * (y * F.dc[2] - z * F.dc[1]), uvy = 2.0 * (z * F.dc[0] - x * F.dc[2]),
          uvz = 2.0 * (x * F.dc[1] - y * F.dc[0]);
   double rx = F.dc[0] + w * uvx + (y * uvz - z * uvy), ry = F.dc[1] + w * uvy + (z * uvx - x * uvz),
          rz = F.dc[2] + w * uvz + (x * uvy - y * uvx);
-  s[0] = F.scale * p[0] - rx; s[1] = F.scale * p[1] - ry; s[2] = F.scale * p[2] - rz;
+  s[0] = F.scale * o[0] - rx; s[1] = F.scale * o[1] - ry; s[2] = F.scale * o[2] - rz;
   s[3] = w; s[4] = x; s[5] = y; s[6] = z;
+}
+__device__ __forceinline__ void ompl_point_to_unit(const OmplFrame& F, const double* a, const double* b, double theta,
+                                                   double t, double* s) {
+  double o[7];
+  ompl_point(a, b, theta, t, o);
+  ompl_row_to_unit(F, o, s);
 }
 
 __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, 3)
@@ -857,8 +899,19 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, 3)
     const double dcn = sqrt(F.dc[0] * F.dc[0] + F.dc[1] * F.dc[1] + F.dc[2] * F.dc[2]);
     const double rate = (F.scale * dtr + 2.0 * theta * (P.rob_radius + dcn)) * (1.0 + 1e-9);
     const double step_radius = 0.5 * rate / (double)nd;
+    // FCLStateValidityChecker::isValid = satisfiesBounds && collision free, for s2 and every interior point.
+    // Motions whose end points are safely inside need no per-point bounds test (the lerp stays inside, the
+    // slerp of two unit quaternions stays unit); the others are walked point by point with the literal test.
+    const bool safe = ompl_safely_inside(F.lo, F.hi, a) && ompl_safely_inside(F.lo, F.hi, b);
+    if (!ompl_satisfies_bounds(F.lo, F.hi, b)) {   // checkMotion tests s2 first (DiscreteMotionValidator.cpp:101)
+      if (lane == 0) {
+        out[pr] = 0;
+        if (nd_out) nd_out[pr] = nd;
+      }
+      continue;
+    }
     int ws = 0;
-    if (fabs(na2 - 1.0) < 1e-6 && fabs(nb2 - 1.0) < 1e-6 && step_radius > 0.0) {
+    if (safe && fabs(na2 - 1.0) < 1e-6 && fabs(nb2 - 1.0) < 1e-6 && step_radius > 0.0) {
       const double cap = fmin(32.0 * (double)P.sweep_tiles, P.sweep_rmax / step_radius);
       if (cap >= 4.0) {
         ws = 4;
@@ -907,19 +960,30 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, 3)
       const int exact_n = (base > 0 && ws > 0) ? P.sweep_short_tile : 32;
       exact_next = false;
       const long long m = base + lane;
-      const bool have = m < total && lane < exact_n;
+      bool have = m < total && lane < exact_n;
+      bool oob = false;
       if (have) {
-        double s[7];
-        ompl_point_to_unit(F, a, b, theta, m == 0 ? 1.0 : (double)m / (double)nd, s);
-        if (m == 0) ompl_point_to_unit(F, b, b, 0.0, 0.0, s);   // s2 exactly, not its slerp image
-        set_pose(P, S, lane, s);
+        double o[7], s[7];
+        if (m == 0) {   // s2 exactly, not its slerp image
+#pragma unroll
+          for (int k = 0; k < 7; k++) o[k] = b[k];
+        } else {
+          ompl_point(a, b, theta, (double)m / (double)nd, o);
+          if (!safe) oob = !ompl_satisfies_bounds(F.lo, F.hi, o);
+        }
+        if (!oob) {
+          ompl_row_to_unit(F, o, s);
+          set_pose(P, S, lane, s);
+        }
       }
+      const unsigned oobm = __ballot_sync(FULL, have && oob);
+      if (oobm) have = have && lane < __ffs(oobm) - 1;   // nothing behind an out-of-bounds point matters
       unsigned alive = __ballot_sync(FULL, have);
       __syncwarp();
       unsigned hits = traverse_tile<MODE_SEGMENT>(P, S, C, alive, lane);
       if (C.overflow) { valid = false; break; }
       nposes += hits ? (unsigned)__ffs(hits) : __popc(alive);
-      if (hits) valid = false;
+      if (hits | oobm) valid = false;
       base += exact_n;
       __syncwarp();
     }

@@ -38,6 +38,7 @@ struct DfsParams {
   // copies queued behind each chunk of the input on the copy stream (engine.cu: osr_is_valid_states)
   const long long* ready;
   long long ready_floor;  // states certainly resident when the kernel starts (the launch is ordered behind them)
+  unsigned long long feed_timeout_ns;  // give up waiting for an upload after this long (%globaltimer; OSR_FEED_TIMEOUT_S)
 };
 
 constexpr int DFS_WARPS = 12;   // 3 per scheduler: 4 would need <= 128 registers (16 K registers per SM sub-partition)
@@ -219,12 +220,23 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
           // out-of-line call here costs the whole traversal loop its convergence (+25 % instructions, +8 % time).
           const long long need = min((long long)base + 32, n);
           long long seen = __shfl_sync(FULL, (long long)M.ready_seen, 0);
+          unsigned long long t0 = 0;   // the wait is bounded in TIME (a poll count depends on the clock and on tools)
           for (int spins = 0; seen < need; spins++) {
             long long v;
             asm volatile("ld.acquire.sys.global.s64 %0, [%1];" : "=l"(v) : "l"(P.ready) : "memory");
             seen = __shfl_sync(FULL, v, 0);
             if (seen >= need) { M.ready_seen = (int)min(seen, 0x7fffffffLL); break; }
-            if (spins > (1 << 22)) { atomicExch(P.error_flag, 2); base = (unsigned long long)n; break; }   // gave up
+            if ((spins & 255) == 255) {
+              unsigned long long now;
+              asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+              now = __shfl_sync(FULL, now, 0);
+              if (t0 == 0) t0 = now;
+              else if (now - t0 > P.feed_timeout_ns) {   // gave up: the host re-runs the call without the feed
+                atomicExch(P.error_flag, 2);
+                base = (unsigned long long)n;
+                break;
+              }
+            }
             __nanosleep(1000);
           }
           __syncwarp();

@@ -50,11 +50,12 @@ struct SegArgs {
 // Results of one segment (all lanes compute the same values; lane 0 / lanes 0..6 store them).
 __device__ __forceinline__ void seg_store(const SegArgs& A, long long seg, const double* ab, bool free_flag,
                                        double free_tau, double touch_tau, long long steps, int mode, int lane) {
-  // mode 0: lf = from, fh = to (vd >= dist);  1: hit at the first step (lf = from);  2: hit later;  3: all free
+  // mode 0: lf = from, fh = to (vd >= dist);  1: hit at the first step (lf = from);  2: hit later;  3: all free;
+  // 4: lf = fh = from (NaN distance / verify_delta: the reference's loop body never runs)
   double lf[7], fh[7];
-  if (mode == 0) {
+  if (mode == 0 || mode == 4) {
 #pragma unroll
-    for (int k = 0; k < 7; k++) { lf[k] = ab[k]; fh[k] = ab[7 + k]; }
+    for (int k = 0; k < 7; k++) { lf[k] = ab[k]; fh[k] = ab[(mode == 0 ? 7 : 0) + k]; }
   } else if (mode == 3) {
     interpolate(ab, ab + 7, free_tau, lf);
 #pragma unroll
@@ -180,6 +181,11 @@ __global__ void __launch_bounds__(WARPS * 32, 1) k_transit_dfs(DfsParams P, SegA
       if (A.transition_mode) vd = fmin(dist / 2.0, vd);
       if (vd >= dist) {  // unit_world.cc:445-447
         seg_store(A, seg, M.ab, false, 0.0, 1.0, 0, 0, lane);
+        continue;
+      }
+      if (!(dist == dist) || !(vd == vd) || !(vd > 0.0)) {   // see k_transit: NaN walk / verify_delta <= 0
+        if (dist == dist && vd == vd && lane == 0) atomicExch(P.error_flag, 3);
+        seg_store(A, seg, M.ab, false, 0.0, 0.0, 0, 4, lane);
         continue;
       }
       have_seg = true; walk_done = false; first = true;

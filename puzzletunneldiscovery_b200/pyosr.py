@@ -401,7 +401,8 @@ class UnitWorld:
         q = _states(from_state)[0]
         aa = np.asarray(aa, dtype=np.float64)
         ang = np.linalg.norm(aa)
-        axis = aa / ang
+        # Eigen 3.3 normalized() leaves a zero vector unchanged: a pure translation (aa = 0) is the identity rotation
+        axis = aa / ang if ang > 0 else aa
         qa = np.concatenate([[np.cos(0.5 * ang)], np.sin(0.5 * ang) * axis])
         w0, x0, y0, z0 = qa
         w1, x1, y1, z1 = q[3:7]
@@ -499,10 +500,12 @@ class UnitWorld:
         to_state = np.concatenate([trans, _quat_normalized(rot)])
         cur = np.float32(verify_delta)
         while True:
+            if cur == 0.0:   # verify_delta vanished: the reference would now walk forever (unit_world.cc:445-470)
+                return state.copy(), False, 0.0
             free_state, done, prog = self.transit_state_to(state, to_state, float(cur))
             if not self.is_valid_state(free_state):
                 raise OsrError("SAN check failed, invalid state from transitStateTo")
-            if prog > 0.0 or cur == 0.0:
+            if prog > 0.0:
                 return free_state, done, prog
             cur = np.float32(cur / np.float32(2.0))
 
@@ -593,21 +596,34 @@ class UnitWorld:
                 return qs[-1]
 
     # ---- OMPL-frame batched validators (lib/pyse3ompl/pyse3ompl.cc:77-81) --------------------------
-    def ompl_validate_states(self, qs):
-        """OmplDriver.validate_states: int32[N], rows x y z qx qy qz qw in the OMPL frame."""
+    @staticmethod
+    def _ompl_bounds(bounds):
+        """(lo[3], hi[3]) of the planner's RealVectorBounds (OmplDriver.set_bounds) -> float64[6]."""
+        if bounds is None:
+            return None
+        b = np.ascontiguousarray(np.concatenate([np.asarray(bounds[0], np.float64).reshape(3),
+                                                 np.asarray(bounds[1], np.float64).reshape(3)]))
+        return b
+
+    def ompl_validate_states(self, qs, bounds=None):
+        """OmplDriver.validate_states: int32[N], rows x y z qx qy qz qw in the OMPL frame.  `bounds` = (mins, maxs)
+        as given to OmplDriver.set_bounds: a state outside them is invalid (FCLStateValidityChecker::isValid);
+        None = collision only."""
         q = _states(qs)
         out = np.empty(len(q), np.uint8)
-        check(self._L.osr_ompl_validate_states(self._h, _p(q, c_dp), len(q), _p(out, c_u8p)))
+        b = self._ompl_bounds(bounds)
+        check(self._L.osr_ompl_validate_states(self._h, _p(q, c_dp), len(q), _p(b, c_dp), _p(out, c_u8p)))
         return out.astype(np.int32)
 
-    def ompl_validate_motion_pairs(self, qs0, qs1, trans_extent, resolution, with_counts=False):
-        """OmplDriver.validate_motion_pairs under OMPL's DiscreteMotionValidator: int32[min(N0, N1)]."""
+    def ompl_validate_motion_pairs(self, qs0, qs1, bounds, resolution, with_counts=False):
+        """OmplDriver.validate_motion_pairs under OMPL's DiscreteMotionValidator: int32[min(N0, N1)].
+        `bounds` = (mins, maxs) of OmplDriver.set_bounds, `resolution` = OmplDriver.set_cdres."""
         a = _states(qs0); b = _states(qs1)
         n = min(len(a), len(b))
         a = np.ascontiguousarray(a[:n]); b = np.ascontiguousarray(b[:n])
         out = np.empty(n, np.uint8)
         nd = np.empty(n, np.int64) if with_counts else None
-        check(self._L.osr_ompl_check_motions(self._h, _p(a, c_dp), _p(b, c_dp), n, float(trans_extent),
+        check(self._L.osr_ompl_check_motions(self._h, _p(a, c_dp), _p(b, c_dp), n, _p(self._ompl_bounds(bounds), c_dp),
                                              float(resolution), _p(out, c_u8p), _p(nd, c_i64p)))
         return (out.astype(np.int32), nd) if with_counts else out.astype(np.int32)
 

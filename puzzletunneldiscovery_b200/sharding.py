@@ -63,10 +63,19 @@ def sharded_map(evaluate, arrays, out_dtype, group=None, cost=None):
     world, rank = dist.get_world_size(group), dist.get_rank(group)
     ranges = balanced_ranges(cost, world) if cost is not None else [task_chunk(n, world, r) for r in range(world)]
     lo, hi = ranges[rank]
-    local = np.asarray(evaluate(*[a[lo:hi] for a in arrays]), dtype=out_dtype) if hi > lo else np.zeros(0, out_dtype)
-    trailing = local.shape[1:]
-    if hi > lo and len(local) != hi - lo:
+    local = np.asarray(evaluate(*[a[lo:hi] for a in arrays]), dtype=out_dtype) if hi > lo else None
+    if local is not None and len(local) != hi - lo:
         raise ValueError("evaluate returned %d rows for a range of %d" % (len(local), hi - lo))
+    # A rank whose range is empty (n < world, or a cost-balanced cut) has nothing to infer the row shape from:
+    # the ranks agree on it first, so that every rank pads to the same tensor shape.
+    shapes = [None] * world
+    dist.all_gather_object(shapes, None if local is None else tuple(local.shape[1:]), group=group)
+    known = [t for t in shapes if t is not None]
+    if len(set(known)) > 1:
+        raise ValueError("ranks disagree on the row shape of the result: %r" % (sorted(set(known)),))
+    trailing = known[0] if known else ()
+    if local is None:
+        local = np.zeros((0,) + trailing, out_dtype)
     longest = max(h - l for l, h in ranges)
     backend = dist.get_backend(group)
     dev = torch.device("cuda", torch.cuda.current_device()) if backend == "nccl" else torch.device("cpu")

@@ -245,7 +245,11 @@ def leg_ompl(O, scale):
     q = q[uw.is_valid_states(q)][:nm]
     fr, to = uw.knn_edges(q, k=8, window=4096)
     a, b = uw.translate_unit_to_ompl(fr), uw.translate_unit_to_ompl(to)
-    extent, res = 150.0, 1e-4
+    # planner bounds (OmplDriver.set_bounds): a cube around the milestones whose diagonal is 150 OMPL units
+    mid = 0.5 * (np.minimum(a[:, :3].min(axis=0), b[:, :3].min(axis=0)) + np.maximum(a[:, :3].max(axis=0), b[:, :3].max(axis=0)))
+    half = 0.5 * 150.0 / np.sqrt(3.0)
+    extent, res = (mid - half, mid + half), 1e-4
+    assert (a[:, :3] > extent[0]).all() and (b[:, :3] < extent[1]).all()
     uw.counters(reset=True)
     (ok, nd), dt = timed(lambda: uw.ompl_validate_motion_pairs(a, b, extent, res, with_counts=True))
     c = uw.counters(reset=True)

@@ -577,7 +577,11 @@ def test_ompl_frame_validators_match_restatement(shift, oracle_mod):
     a, b = uw.translate_unit_to_ompl(fr), uw.translate_unit_to_ompl(to)
     scale = uw.scene_scale
     dc = (uw.get_ompl_center(1).astype(np.float32) - uw.robot_center.astype(np.float32)).astype(np.float64) * scale
-    extent, res = 150.0, 0.01
+    # translation bounds of the planner (OmplDriver.set_bounds); every milestone lies inside them here
+    lo = np.floor(np.minimum(a[:, :3].min(axis=0), qo[:, :3].min(axis=0))) - 1.0
+    extent = (lo, lo + np.array([90.0, 80.0, 90.0]))
+    assert (qo[:, :3].max(axis=0) < extent[1] - 1.0).all()
+    res = 0.01
     got, nd = uw.ompl_validate_motion_pairs(a, b, extent, res, with_counts=True)
     want, ond = ow.ompl_check_motions(a, b, scale, dc, extent, res)
     assert np.array_equal(nd, ond) and nd.max() > 32 and nd.min() >= 1
@@ -595,6 +599,37 @@ def test_ompl_frame_validators_match_restatement(shift, oracle_mod):
     assert not g2.any()
     g3, n3 = uw.ompl_validate_motion_pairs(a[:8], a[:8], extent, res, with_counts=True)
     assert g3.all() and (n3 == 0).all()
+    # FCLStateValidityChecker::isValid = satisfiesBounds && collision free: bounds that cut through the milestones
+    # (translation), goals whose quaternion is off the unit sphere by more than 1e-9, start states outside the bounds
+    # (checkMotion never tests s1, but the interior points next to it are outside too), NaN rows
+    mid = np.median(a[:, :3], axis=0)
+    tight = (extent[0], np.array([mid[0], extent[1][1], extent[1][2]]))
+    gs = uw.ompl_validate_states(qo, tight).astype(bool)
+    ws = ow.ompl_validate_states(qo, scale, dc, tight).astype(bool)
+    inside = qo[:, 0] <= mid[0]
+    assert np.array_equal(gs, ws) and np.array_equal(gs, valid & inside) and 0 < gs.sum() < valid.sum()
+    assert np.array_equal(uw.ompl_validate_states(qo, extent).astype(bool), valid)
+    gt, nt = uw.ompl_validate_motion_pairs(a, b, tight, res, with_counts=True)
+    wt, ont = ow.ompl_check_motions(a, b, scale, dc, tight, res)
+    assert np.array_equal(nt, ont) and np.array_equal(gt.astype(bool), wt.astype(bool))
+    assert not gt[b[:, 0] > mid[0] + 1e-6].any()                       # a goal outside the bounds is invalid
+    straddle = (b[:, 0] < mid[0] - 1e-6) & (nt >= 2) & (a[:, 0] + (b[:, 0] - a[:, 0]) / np.maximum(nt, 1) > mid[0] + 1e-6)
+    assert straddle.any() and not gt[straddle].any()                   # interior points next to s1 are outside
+    assert gt.sum() < got.sum() and gt.any()
+    b_off = b[:64].copy(); b_off[::2, 3:7] *= 1.0 + 1e-8             # every other goal fails the SO(3) norm test
+    go = uw.ompl_validate_motion_pairs(a[:64], b_off, extent, res)
+    wo, _ = ow.ompl_check_motions(a[:64], b_off, scale, dc, extent, res)
+    assert np.array_equal(go.astype(bool), wo.astype(bool)) and not go[::2].any()
+    assert np.array_equal(go[1::2], got[:64][1::2])
+    a_off = a[:64].copy(); a_off[::2, 3:7] *= 1.0 + 1e-8             # start states are not tested, interior points are
+    ga = uw.ompl_validate_motion_pairs(a_off, b[:64], extent, res)
+    wa, _ = ow.ompl_check_motions(a_off, b[:64], scale, dc, extent, res)
+    assert np.array_equal(ga.astype(bool), wa.astype(bool))
+    b_nan = b[:8].copy(); b_nan[0, 0] = np.nan; b_nan[1, 4] = np.nan; b_nan[2, :3] = np.inf
+    gn = uw.ompl_validate_motion_pairs(a[:8], b_nan, extent, res)
+    assert not gn[:3].any() and np.array_equal(gn[3:], got[3:8])
+    with pytest.raises(RuntimeError):
+        uw.ompl_validate_motion_pairs(a[:8], b[:8], (extent[1], extent[0]), res)   # hi < lo
 
 
 @pytest.mark.gpu
@@ -741,3 +776,73 @@ def test_clearance_stats_edge_cases(uw_org, ow_org, oracle_mod):
         uw_org.clearance_stats(cq, near, 0.0)
     with pytest.raises(Exception):
         uw_org.clearance_stats(cq, near[:2], VD_TOUCH)
+
+
+@pytest.mark.timeout(120)
+def test_transit_state_by_pure_translation(uw_org, ow_org):
+    """transit_state_by with a zero angle-axis (what aapath-walker / rlsampler pass for translation actions):
+    Eigen's normalized() leaves the zero vector alone and AngleAxis(0, 0) is the identity rotation
+    (unit_world.cc:489-506), so the target is the translated state -- not a NaN state."""
+    q = W.random_states(4096, seed=71)
+    free = q[uw_org.is_valid_states(q)][:16]
+    for s in free[:6]:
+        tr = np.array([0.03, -0.02, 0.01])
+        got = uw_org.transit_state_by(s, tr, np.zeros(3), VD_TOUCH)
+        to = np.concatenate([s[:3] + tr, s[3:7]])
+        want = uw_org.transit_state_to(s, to, VD_TOUCH)
+        assert np.isfinite(got[0]).all() and np.array_equal(got[0], want[0]) and got[1:] == want[1:]
+        olf, ofh, oisf, oft, ott = ow_org.transit_states_to_with_contact(s[None], to[None], VD_TOUCH)
+        assert np.array_equal(got[0], olf[0]) and got[1] == bool(oisf[0])
+        # a rotation action still rotates
+        rot = uw_org.transit_state_by(s, np.zeros(3), np.array([0.0, 0.0, 0.05]), VD_TOUCH)
+        assert np.isfinite(rot[0]).all()
+
+
+@pytest.mark.timeout(120)
+def test_degenerate_walks_return_instead_of_hanging(uw_org, ow_org):
+    """NaN states / NaN verify_delta fall through both comparisons of the reference's walk (unit_world.cc:443-447):
+    its loop body never runs and it returns (from, from, false, 0, 0) -- the kernel must do the same instead of
+    spinning in its window loop.  verify_delta <= 0 on a segment of non-zero length never ends in
+    the reference; here it is an argument error.  Neighbouring segments of the same batch are unaffected."""
+    q = W.random_states(4096, seed=72)
+    free = q[uw_org.is_valid_states(q)][:64]
+    fr, to = W.touch_rays(free, 64, seed=73)
+    base = uw_org.transit_states_to_with_contact(fr, to, VD_TOUCH, with_steps=True)
+    fr2, to2 = fr.copy(), to.copy()
+    to2[0, 3:7] = np.nan          # what a 0/0 axis used to produce
+    fr2[1, 0] = np.nan
+    to2[2, :] = np.nan
+    to2[3, 1] = np.inf            # infinite distance: the first step is a NaN pose, reported as the first hit
+    got = uw_org.transit_states_to_with_contact(fr2, to2, VD_TOUCH, with_steps=True)
+    want = ow_org.transit_states_to_with_contact(fr2[:3], to2[:3], VD_TOUCH)
+    for i in range(3):
+        assert np.array_equal(got[0][i], fr2[i], equal_nan=True) and np.array_equal(got[1][i], fr2[i], equal_nan=True)
+        assert not got[2][i] and got[3][i] == 0.0 and got[4][i] == 0.0 and got[5][i] == 0
+        assert np.array_equal(want[0][i], fr2[i], equal_nan=True) and np.array_equal(want[1][i], fr2[i], equal_nan=True)
+        assert not want[2][i] and want[3][i] == 0.0 and want[4][i] == 0.0
+    assert not got[2][3] and got[5][3] == 1
+    for k in range(6):
+        assert np.array_equal(np.asarray(got[k])[4:], np.asarray(base[k])[4:])
+    # per-segment verify_delta with a NaN entry
+    vd = np.full(64, VD_TOUCH); vd[5] = np.nan
+    gv = uw_org.transit_states_to_with_contact(fr, to, vd, with_steps=True)
+    assert np.array_equal(gv[0][5], fr[5]) and np.array_equal(gv[1][5], fr[5]) and not gv[2][5] and gv[5][5] == 0
+    assert np.array_equal(gv[5][6:], base[5][6:])
+    assert not uw_org.is_valid_transitions(fr2[:3], to2[:3], VD_TOUCH).any()
+    # verify_delta <= 0
+    for bad in (0.0, -1e-3):
+        with pytest.raises(RuntimeError):
+            uw_org.transit_states_to_with_contact(fr, to, bad)
+        with pytest.raises(RuntimeError):
+            uw_org.is_valid_transitions(fr, to, bad)
+    # ... but 0 on zero-length segments is the reference's `verify_delta >= dist` early return
+    z = uw_org.transit_states_to_with_contact(fr[:4], fr[:4], 0.0)
+    assert not z[2].any() and (z[4] == 1.0).all() and np.array_equal(z[1], fr[:4])
+    assert not uw_org.is_valid_transitions(fr[:4], fr[:4], VD_TOUCH).any()
+    # the engine still works afterwards (error flag cleared)
+    again = uw_org.transit_states_to_with_contact(fr, to, VD_TOUCH, with_steps=True)
+    for k in range(6):
+        assert np.array_equal(np.asarray(again[k]), np.asarray(base[k]))
+    # discrete actions whose verify_delta underflows to 0 return instead of walking forever
+    s, done, prog = uw_org.transit_state(free[0], 0, 0.01, 0.0)
+    assert np.array_equal(s, free[0]) and not done and prog == 0.0

@@ -72,10 +72,22 @@ def _worker(rank, world, port, q, fr, to, ret):
     taus = S.sharded_map(lambda a, b: np.stack(ow.transit_states_to_with_contact(a, b, 0.05, threads=1)[3:5], axis=1),
                          [fr, to], np.float64, cost=cost)
     t = S.max_over_ranks(1.0 + rank)
+    # a rank with an EMPTY range and 2-D rows: one segment over two ranks; all the cost on the last
+    # segment, so the first rank's cost-balanced range is everything but it ... and the degenerate n < world case
+    lf1 = S.sharded_map(lambda a, b: ow.transit_states_to_with_contact(a, b, 0.05, threads=1)[0], [fr[:1], to[:1]],
+                        np.float64)
+    skew = np.zeros(len(fr)); skew[-1] = 1.0
+    lf2 = S.sharded_map(lambda a, b: ow.transit_states_to_with_contact(a, b, 0.05, threads=1)[0], [fr, to],
+                        np.float64, cost=skew)
+    empty = S.sharded_map(lambda a: a, [np.zeros((0, 7))], np.float64)
     if rank == 0:
         ret["labels"] = labels
         ret["taus"] = taus
         ret["t"] = t
+        ret["lf1"] = lf1
+        ret["lf2"] = lf2
+        ret["empty_shape"] = tuple(empty.shape)
+        ret["ranges_skew"] = S.balanced_ranges(skew, world)
     dist.barrier()
     dist.destroy_process_group()
 
@@ -100,5 +112,9 @@ def test_world_size_2_gloo_shards_equal_single_process(oracle_mod):
     ref = ow.transit_states_to_with_contact(fr, to, 0.05)
     assert np.array_equal(ret["taus"][:, 0], ref[3]) and np.array_equal(ret["taus"][:, 1], ref[4])
     assert ret["t"] == 2.0                      # max over ranks
+    assert ret["lf1"].shape == (1, 7) and np.array_equal(ret["lf1"], ref[0][:1])
+    assert any(h == l for l, h in ret["ranges_skew"])      # one rank really had nothing to do
+    assert ret["lf2"].shape == (len(fr), 7) and np.array_equal(ret["lf2"], ref[0])
+    assert ret["empty_shape"][0] == 0
     # no process group: plain call
     assert np.array_equal(S.sharded_map(lambda x: ow.is_valid_states(x), [q], np.uint8), ret["labels"])
