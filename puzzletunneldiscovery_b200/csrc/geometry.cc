@@ -139,13 +139,91 @@ struct BuildNode {
   uint16_t eh[3];  // ... and extents fitted to the exact rotation of that quaternion, rounded up to fp16
 };
 
+// Builder options (development switches; the defaults are the measured best, see DESIGN.md "BVH quality").
+//   OSR_BVH_REFINE  0: covariance (PCA) frame as FCL's BVFitter   1: + local search minimising the box AREA   2: ... VOLUME
+//   OSR_BVH_SPLIT   0: mean of centroids on the longest axis (FCL SPLIT_METHOD_MEAN)   1: surface-area sweep in the box frame
+static int env_int(const char* name, int dflt) {
+  const char* e = getenv(name);
+  return e ? atoi(e) : dflt;
+}
+
 struct Builder {
   const UnitModel& m;
   std::vector<BuildNode> nodes;
   std::vector<int> prims;
   std::vector<Vec3> cent;
   int depth = 0;
+  int max_depth = 64;
+  const int opt_refine = env_int("OSR_BVH_REFINE", 1);
+  const int opt_split = env_int("OSR_BVH_SPLIT", 1);
   explicit Builder(const UnitModel& mm) : m(mm) {}
+
+  // half extents of the points `pts` in the orthonormal frame ax -> cost (area or volume of the box)
+  static double frame_cost(const std::vector<Vec3>& pts, const Vec3 ax[3], int kind) {
+    double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+    for (const Vec3& p : pts)
+      for (int a = 0; a < 3; a++) {
+        double pr = dot(ax[a], p);
+        lo[a] = std::min(lo[a], pr); hi[a] = std::max(hi[a], pr);
+      }
+    double e0 = hi[0] - lo[0], e1 = hi[1] - lo[1], e2 = hi[2] - lo[2];
+    return kind == 2 ? e0 * e1 * e2 : e0 * e1 + e1 * e2 + e0 * e2;
+  }
+  static void rotate_frame(const Vec3 in[3], int about, double ang, Vec3 out[3]) {
+    const int i = (about + 1) % 3, j = (about + 2) % 3;
+    const double c = std::cos(ang), s = std::sin(ang);
+    out[about] = in[about];
+    out[i] = {c * in[i].x + s * in[j].x, c * in[i].y + s * in[j].y, c * in[i].z + s * in[j].z};
+    out[j] = {c * in[j].x - s * in[i].x, c * in[j].y - s * in[i].y, c * in[j].z - s * in[i].z};
+  }
+  // Local search over orientations from the covariance frame: rotate about each box axis by +-step, keep what
+  // shrinks the box, halve the step.  Large nodes are searched on their extreme points along 96 fixed directions
+  // (the final extents are always taken over every vertex, so containment never depends on the search).
+  void refine_frame(int first, int n, Vec3 ax[3]) const {
+    std::vector<Vec3> pts;
+    pts.reserve((size_t)3 * n);
+    for (int i = 0; i < n; i++)
+      for (int k = 0; k < 3; k++) pts.push_back(vert(prims[first + i], k));
+    if (pts.size() > 768) {
+      std::vector<Vec3> ex;
+      for (int d = 0; d < 96; d++) {
+        // Fibonacci directions on the half sphere (both extremes are taken per direction)
+        double z = (d + 0.5) / 96.0, r = std::sqrt(std::max(0.0, 1.0 - z * z)), ph = 2.399963229728653 * d;
+        Vec3 dir = {r * std::cos(ph), r * std::sin(ph), z};
+        size_t imin = 0, imax = 0;
+        double vmin = 1e300, vmax = -1e300;
+        for (size_t i = 0; i < pts.size(); i++) {
+          double pr = dot(dir, pts[i]);
+          if (pr < vmin) { vmin = pr; imin = i; }
+          if (pr > vmax) { vmax = pr; imax = i; }
+        }
+        ex.push_back(pts[imin]); ex.push_back(pts[imax]);
+      }
+      pts.swap(ex);
+    }
+    double best = frame_cost(pts, ax, opt_refine);
+    for (double step = 0.4; step > 0.004; step *= 0.5) {
+      bool improved = true;
+      for (int it = 0; improved && it < 32; it++) {
+        improved = false;
+        for (int about = 0; about < 3; about++)
+          for (int sg = -1; sg <= 1; sg += 2) {
+            Vec3 cand[3];
+            rotate_frame(ax, about, sg * step, cand);
+            double c = frame_cost(pts, cand, opt_refine);
+            if (c < best * (1.0 - 1e-9)) { best = c; ax[0] = cand[0]; ax[1] = cand[1]; ax[2] = cand[2]; improved = true; }
+          }
+      }
+    }
+    // re-orthonormalise (rounding of the accumulated rotations)
+    double l0 = std::sqrt(dot(ax[0], ax[0]));
+    ax[0] = {ax[0].x / l0, ax[0].y / l0, ax[0].z / l0};
+    double d01 = dot(ax[0], ax[1]);
+    ax[1] = {ax[1].x - d01 * ax[0].x, ax[1].y - d01 * ax[0].y, ax[1].z - d01 * ax[0].z};
+    double l1 = std::sqrt(dot(ax[1], ax[1]));
+    ax[1] = {ax[1].x / l1, ax[1].y / l1, ax[1].z / l1};
+    ax[2] = cross(ax[0], ax[1]);
+  }
 
   Vec3 vert(int t, int k) const {
     const double* p = &m.tris[(size_t)9 * t + 3 * k];
@@ -197,6 +275,7 @@ struct Builder {
     a1 = {a1.x / l1, a1.y / l1, a1.z / l1};
     Vec3 a2 = cross(a0, a1);
     Vec3 ax[3] = {a0, a1, a2};
+    if (opt_refine > 0 && n > 1) refine_frame(first, n, ax);
     for (int k = 0; k < 3; k++) {
       nd.axis[3 * k] = (float)ax[k].x; nd.axis[3 * k + 1] = (float)ax[k].y; nd.axis[3 * k + 2] = (float)ax[k].z;
       ax[k] = {(double)nd.axis[3 * k], (double)nd.axis[3 * k + 1], (double)nd.axis[3 * k + 2]};
@@ -275,6 +354,64 @@ struct Builder {
     for (int a = 0; a < 3; a++) nd.eh[a] = float_to_half_bits_up(ext[a] * (1.0 + 1e-5) + 4e-6 * lever + 1e-9);
   }
 
+  // Surface-area sweep in the node's own box frame: triangles sorted by centroid along each box axis, cost of a cut
+  // = area(box of the left part) * count + area(box of the right part) * count with both boxes axis-aligned in that
+  // frame; the cut must leave both sides small enough for the depth budget.  Reorders prims[first, first+n).
+  int sweep_split(int first, int n, int id, int lvl) {
+    const BuildNode& nd = nodes[id];
+    Vec3 ax[3];
+    for (int k = 0; k < 3; k++) ax[k] = {(double)nd.axis[3 * k], (double)nd.axis[3 * k + 1], (double)nd.axis[3 * k + 2]};
+    const int room = max_depth - lvl - 1;                       // levels left below the children
+    const long long cap = room >= 30 ? (1LL << 30) : (1LL << std::max(0, room));
+    const int kmin = (int)std::max<long long>(1, n - cap), kmax = (int)std::min<long long>(n - 1, cap);
+    if (kmin > kmax) return -1;
+    struct Box { double lo[3], hi[3]; };
+    std::vector<Box> tb(n);
+    std::vector<double> key(n);
+    std::vector<int> idx(n), best_order;
+    for (int i = 0; i < n; i++) {
+      Box& b = tb[i];
+      for (int a = 0; a < 3; a++) { b.lo[a] = 1e300; b.hi[a] = -1e300; }
+      for (int k = 0; k < 3; k++) {
+        Vec3 p = vert(prims[first + i], k);
+        for (int a = 0; a < 3; a++) {
+          double pr = dot(ax[a], p);
+          b.lo[a] = std::min(b.lo[a], pr); b.hi[a] = std::max(b.hi[a], pr);
+        }
+      }
+    }
+    auto area = [](const Box& b) {
+      double e0 = b.hi[0] - b.lo[0], e1 = b.hi[1] - b.lo[1], e2 = b.hi[2] - b.lo[2];
+      return e0 * e1 + e1 * e2 + e0 * e2;
+    };
+    auto grow = [](Box& b, const Box& o) {
+      for (int a = 0; a < 3; a++) { b.lo[a] = std::min(b.lo[a], o.lo[a]); b.hi[a] = std::max(b.hi[a], o.hi[a]); }
+    };
+    double best = 1e300;
+    int best_k = -1;
+    std::vector<double> right(n + 1);
+    for (int a = 0; a < 3; a++) {
+      for (int i = 0; i < n; i++) { idx[i] = i; key[i] = dot(ax[a], cent[prims[first + i]]); }
+      std::sort(idx.begin(), idx.end(), [&](int x, int y) { return key[x] < key[y] || (key[x] == key[y] && x < y); });
+      Box acc;
+      for (int d = 0; d < 3; d++) { acc.lo[d] = 1e300; acc.hi[d] = -1e300; }
+      right[n] = 0;
+      for (int i = n - 1; i >= 1; i--) { grow(acc, tb[idx[i]]); right[i] = area(acc); }
+      for (int d = 0; d < 3; d++) { acc.lo[d] = 1e300; acc.hi[d] = -1e300; }
+      for (int k = 1; k < n; k++) {
+        grow(acc, tb[idx[k - 1]]);
+        if (k < kmin || k > kmax) continue;
+        double c = area(acc) * k + right[k] * (n - k);
+        if (c < best) { best = c; best_k = k; best_order = idx; }
+      }
+    }
+    if (best_k < 0) return -1;
+    std::vector<int> tmp(n);
+    for (int i = 0; i < n; i++) tmp[i] = prims[first + best_order[i]];
+    std::copy(tmp.begin(), tmp.end(), prims.begin() + first);
+    return best_k;
+  }
+
   int build(int first, int n, int lvl) {
     depth = std::max(depth, lvl);
     int id = (int)nodes.size();
@@ -294,16 +431,20 @@ struct Builder {
       for (int a = 1; a < 3; a++) if (nodes[id].ext[a] > nodes[id].ext[la]) la = a;
       sv = {(double)nodes[id].axis[3 * la], (double)nodes[id].axis[3 * la + 1], (double)nodes[id].axis[3 * la + 2]};
     }
+    int c1 = -1;
+    if (opt_split == 1 && n > 2) c1 = sweep_split(first, n, id, lvl);
+    if (c1 < 0) {
     double mean = 0;
     for (int i = 0; i < n; i++) mean += dot(sv, cent[prims[first + i]]);
     mean /= n;
     auto mid = std::partition(prims.begin() + first, prims.begin() + first + n,
                               [&](int t) { return dot(sv, cent[t]) <= mean; });
-    int c1 = (int)(mid - (prims.begin() + first));
+    c1 = (int)(mid - (prims.begin() + first));
     if (c1 < n / 8 + (n < 8 ? 1 : 0) || n - c1 < n / 8 + (n < 8 ? 1 : 0) || c1 == 0 || c1 == n) {
       c1 = n / 2;
       std::nth_element(prims.begin() + first, prims.begin() + first + c1, prims.begin() + first + n,
                        [&](int a, int b) { return dot(sv, cent[a]) < dot(sv, cent[b]); });
+    }
     }
     int l = build(first, c1, lvl + 1);
     int r = build(first + c1, n - c1, lvl + 1);
@@ -325,6 +466,11 @@ void build_gpu_bvh(UnitModel& m) {
     b.cent[t] = {(p0.x + p1.x + p2.x) / 3, (p0.y + p1.y + p2.y) / 3, (p0.z + p1.z + p2.z) / 3};
   }
   b.nodes.reserve(2 * (size_t)n);
+  {
+    int lg = 0;
+    while ((1LL << lg) < n) lg++;
+    b.max_depth = lg + 3;   // the sweep split may unbalance the tree by at most this much (traversal stack depth)
+  }
   b.build(0, n, 0);
   // breadth-first renumbering with sibling pairs adjacent
   int N = (int)b.nodes.size();

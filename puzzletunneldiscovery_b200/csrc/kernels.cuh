@@ -461,8 +461,9 @@ __device__ __forceinline__ unsigned traverse_tile(const KParams& P, WarpShared& 
           lf = make_entry(pose, (unsigned)(-(l1 + 1)), (unsigned)(-(l2 + 1)));
         } else {
           expand = true;
-          float s1 = a3.x * a3.x + a3.y * a3.y + a3.z * a3.z;
-          float s2 = b3.x * b3.x + b3.y * b3.y + b3.z * b3.z;
+          // descent rule: split the box of larger volume (FCL compares extent^2; labels do not depend on it)
+          float s1 = a3.x * a3.y * a3.z;
+          float s2 = b3.x * b3.y * b3.z;
           if (l2 < 0 || (l1 >= 0 && s1 > s2)) {  // descend the env node
             c0 = make_entry(pose, (unsigned)l1, n2);
             c1 = make_entry(pose, (unsigned)l1 + 1u, n2);

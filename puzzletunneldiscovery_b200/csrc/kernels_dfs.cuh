@@ -43,27 +43,31 @@ struct DfsParams {
 
 constexpr int DFS_WARPS = 12;   // 3 per scheduler: 4 would need <= 128 registers (16 K registers per SM sub-partition)
 constexpr int DFS_THREADS = DFS_WARPS * 32;
-constexpr int LEAFQ_CAP = 64;    // >= LEAF_FLUSH - 1 + 32 (at most one new pair per lane and iteration)
+constexpr int LEAFQ_CAP = 96;    // >= LEAF_FLUSH - 1 + 64 (at most two new pairs per lane and iteration)
 constexpr int REQ_CAP = 64;
 constexpr int LEAF_FLUSH = 16;   // drain the triangle-pair queue once it holds this many pairs
 constexpr int RE_FLUSH = 8;      // same for the queue of pairs awaiting the exact fp64 predicate
 constexpr int WAIT_FLUSH = 4;    // ... or once this many lanes have nothing left but queued pairs
 constexpr int REFILL_MIN = 1;    // pull new poses once this many lanes are idle
 
-// work-stack entry = one (environment node, robot node) pair still to be box-tested; bit 31 / 63 marks a
-// valid entry so that 0 means "none"
+// work-stack entry = one OVERLAPPING (environment node, robot node) pair still to be expanded, stored as
+// (first child of the node that gets split, the other node, which tree is split); 0 means "none".
 template <typename E> struct TaskCodec;
-template <> struct TaskCodec<uint32_t> {  // valid:1 | robot node:15 | environment node:16
-  static __device__ __forceinline__ uint32_t make(unsigned n1, unsigned n2) { return 0x80000000u | (n2 << 16) | n1; }
-  static __device__ __forceinline__ unsigned env(uint32_t e) { return e & 0xffffu; }
-  static __device__ __forceinline__ unsigned rob(uint32_t e) { return (e >> 16) & 0x7fffu; }
-};
-template <> struct TaskCodec<unsigned long long> {  // valid:1 | robot node:31 | environment node:32
-  static __device__ __forceinline__ unsigned long long make(unsigned n1, unsigned n2) {
-    return 0x8000000000000000ull | ((unsigned long long)n2 << 32) | n1;
+template <> struct TaskCodec<uint32_t> {  // valid:1 | other node:15 | split-env:1 | first child:15
+  static __device__ __forceinline__ uint32_t make(unsigned child, unsigned other, bool split_env) {
+    return 0x80000000u | (other << 16) | (split_env ? 0x8000u : 0u) | child;
   }
-  static __device__ __forceinline__ unsigned env(unsigned long long e) { return (unsigned)e; }
-  static __device__ __forceinline__ unsigned rob(unsigned long long e) { return (unsigned)(e >> 32) & 0x7fffffffu; }
+  static __device__ __forceinline__ unsigned child(uint32_t e) { return e & 0x7fffu; }
+  static __device__ __forceinline__ unsigned other(uint32_t e) { return (e >> 16) & 0x7fffu; }
+  static __device__ __forceinline__ bool split_env(uint32_t e) { return (e & 0x8000u) != 0; }
+};
+template <> struct TaskCodec<unsigned long long> {  // valid:1 | other node:31 | split-env:1 | first child:31
+  static __device__ __forceinline__ unsigned long long make(unsigned child, unsigned other, bool split_env) {
+    return 0x8000000000000000ull | ((unsigned long long)other << 32) | (split_env ? 0x80000000ull : 0ull) | child;
+  }
+  static __device__ __forceinline__ unsigned child(unsigned long long e) { return (unsigned)e & 0x7fffffffu; }
+  static __device__ __forceinline__ unsigned other(unsigned long long e) { return (unsigned)(e >> 32) & 0x7fffffffu; }
+  static __device__ __forceinline__ bool split_env(unsigned long long e) { return ((unsigned)e & 0x80000000u) != 0; }
 };
 
 template <typename E, int DEPTH>
@@ -117,6 +121,68 @@ __device__ __forceinline__ void load_pair_exact_r(const double* __restrict__ Pt,
       qo[v][k] = w - p1[k];
     }
   }
+}
+
+// Descent rule and entry of an overlapping pair (A = environment node ia, B = robot node ib): a leaf is never
+// split; otherwise the box of larger volume is.
+template <typename E>
+__device__ __forceinline__ E expand_entry(const QNode& A, const QNode& B, unsigned ia, unsigned ib, float volA, float volB) {
+  typedef TaskCodec<E> TC;
+  if (B.link < 0 || (A.link >= 0 && volA > volB)) return TC::make((unsigned)A.link, ib, true);
+  return TC::make((unsigned)B.link, ia, false);
+}
+
+// One expansion step of a lane: the pair in `cur` is known to overlap; its two child pairs (the split node's
+// children against the other node) are box-tested together -- two independent tests per lane and iteration hide
+// each other's latency -- triangle pairs are reported to the caller, and of two overlapping child pairs the one
+// that overlaps DEEPER is expanded next while the other goes on the lane's stack.
+template <typename E, bool ALL_SMEM, typename STACK>
+__device__ __forceinline__ void dfs_expand_step(E& cur, int& sp, const int sb, STACK& stack, const int lane,
+                                                const uint4* sm_env, const uint4* sm_rob, const DfsParams& P,
+                                                const BoxPose& bp, bool& lf0, unsigned& ta0, unsigned& tb0, bool& lf1,
+                                                unsigned& ta1, unsigned& tb1) {
+  typedef TaskCodec<E> TC;
+  const unsigned c = TC::child(cur), o = TC::other(cur);
+  const bool se = TC::split_env(cur);
+  const unsigned ia0 = se ? c : o, ia1 = se ? c + 1u : o, ib0 = se ? o : c, ib1 = se ? o : c + 1u;
+  const QNode A0 = load_qnode<ALL_SMEM>(sm_env, P.env_q, P.env_smem_nodes, ia0);
+  const QNode A1 = load_qnode<ALL_SMEM>(sm_env, P.env_q, P.env_smem_nodes, ia1);
+  const QNode B0 = load_qnode<ALL_SMEM>(sm_rob, P.rob_q, P.rob_smem_nodes, ib0);
+  const QNode B1 = load_qnode<ALL_SMEM>(sm_rob, P.rob_q, P.rob_smem_nodes, ib1);
+  float s0, s1, va0, vb0, va1, vb1;
+  const bool ov0 = obb_overlap_q2(A0, B0, bp, s0, va0, vb0);
+  const bool ov1 = obb_overlap_q2(A1, B1, bp, s1, va1, vb1);
+  E e0 = 0, e1 = 0;
+  if (ov0) {
+    if (A0.link < 0 && B0.link < 0) { lf0 = true; ta0 = (unsigned)(-(A0.link + 1)); tb0 = (unsigned)(-(B0.link + 1)); }
+    else e0 = expand_entry<E>(A0, B0, ia0, ib0, va0, vb0);
+  }
+  if (ov1) {
+    if (A1.link < 0 && B1.link < 0) { lf1 = true; ta1 = (unsigned)(-(A1.link + 1)); tb1 = (unsigned)(-(B1.link + 1)); }
+    else e1 = expand_entry<E>(A1, B1, ia1, ib1, va1, vb1);
+  }
+  if (e0 != 0 && e1 != 0) {
+    const bool second_first = s1 > s0;
+    stack[sp][lane] = second_first ? e0 : e1;
+    sp++;
+    cur = second_first ? e1 : e0;
+  } else {
+    E nxt = e0 != 0 ? e0 : e1;
+    if (nxt == 0 && sp > sb) { sp--; nxt = stack[sp][lane]; }
+    cur = nxt;
+  }
+}
+
+// The entry a pose starts from once its root boxes are known to overlap (0 when both roots are leaves: the only
+// triangle pair then goes straight to the pair queue).
+template <typename E>
+__device__ __forceinline__ E root_entry(const uint4* env_q, const uint4* rob_q) {
+  QNode A = load_qnode<false>(nullptr, env_q, 0, 0u), B = load_qnode<false>(nullptr, rob_q, 0, 0u);
+  if (A.link < 0 && B.link < 0) return 0;
+  float ea0, ea1, ea2, eb0, eb1, eb2, spare;
+  unpack_half2(A.e01, ea0, ea1); unpack_half2(A.e2x, ea2, spare);
+  unpack_half2(B.e01, eb0, eb1); unpack_half2(B.e2x, eb2, spare);
+  return expand_entry<E>(A, B, 0u, 0u, ea0 * ea1 * ea2, eb0 * eb1 * eb2);
 }
 
 // ---- pose sources -----------------------------------------------------------------------------------
@@ -173,7 +239,8 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
   const int lane = threadIdx.x & 31;
   const unsigned ltmask = (1u << lane) - 1u;
   ValiditySource<T> src = {q, n, out};
-  const bool root_leafpair = ((int)sm_env[0].w < 0) && ((int)sm_rob[0].w < 0);  // two single-triangle meshes
+  const E root_task = root_entry<E>(P.env_q, P.rob_q);
+  const bool root_leafpair = root_task == 0;  // two single-triangle meshes
 
   // lane state
   BoxPose bp;
@@ -246,22 +313,35 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
           long long i = (long long)base + lane;
           bool have = i < n;
           unsigned hm = __ballot_sync(FULL, have);
+          // the root box test runs here, 32 poses at a time: poses separated at the root are free and never
+          // occupy a lane; the others are compacted into the buffer of prepared poses
+          bool keep = false;
+          BoxPose np;
           if (have) {
             Rigid rel; double qd[4];
             src.exact_pose(P, (int)i, rel, qd);
-            BoxPose np;
             make_box_pose(rel, P.env_quat, qd, P.r_rob, np);
-#pragma unroll
-            for (int k = 0; k < 4; k++) M.pend[k][lane] = np.q[k];
-#pragma unroll
-            for (int k = 0; k < 9; k++) M.pend[4 + k][lane] = np.R[k];
-#pragma unroll
-            for (int k = 0; k < 3; k++) M.pend[13 + k][lane] = np.t[k];
-            M.pend[16][lane] = np.eta;
-            M.pend_idx[lane] = (int)i;
+            const QNode RA = load_qnode<ALL_SMEM>(sm_env, P.env_q, P.env_smem_nodes, 0u);
+            const QNode RB = load_qnode<ALL_SMEM>(sm_rob, P.rob_q, P.rob_smem_nodes, 0u);
+            float sl, va, vb;
+            keep = obb_overlap_q2(RA, RB, np, sl, va, vb);
+            n_bv++;
+            if (!keep) src.result((int)i, false);
           }
-          pend_n = __popc(hm);
-          nposes += pend_n;
+          const unsigned km = __ballot_sync(FULL, keep);
+          if (keep) {
+            const int slot = __popc(km & ltmask);
+#pragma unroll
+            for (int k = 0; k < 4; k++) M.pend[k][slot] = np.q[k];
+#pragma unroll
+            for (int k = 0; k < 9; k++) M.pend[4 + k][slot] = np.R[k];
+#pragma unroll
+            for (int k = 0; k < 3; k++) M.pend[13 + k][slot] = np.t[k];
+            M.pend[16][slot] = np.eta;
+            M.pend_idx[slot] = (int)i;
+          }
+          pend_n = __popc(km);
+          nposes += __popc(hm);
           __syncwarp();
         }
       }
@@ -280,7 +360,7 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
           tag = M.pend_idx[slot];
           fl = F_HAS; sp = 0; sb = 0;
           epoch = (epoch + 1) & 0x7ffu;
-          cur = root_leafpair ? 0 : TC::make(0, 0);
+          cur = root_task;
         }
         pend_n -= min(pend_n, __popc(idle));
         if (root_leafpair) {  // degenerate meshes: the only pair goes straight to the pair queue
@@ -336,8 +416,8 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
     // of new triangle pairs on top)
     const bool any_cur = __any_sync(FULL, cur != 0);
     if (any_cur && !draining_leaf && !draining_re) {
-      bool lf0 = false;
-      unsigned ta0 = 0, tb0 = 0;
+      bool lf0 = false, lf1 = false;
+      unsigned ta0 = 0, tb0 = 0, ta1 = 0, tb1 = 0;
 #ifdef OSR_DFS_STATS
       st_iters++;
       st_active += __popc(__ballot_sync(FULL, cur != 0));
@@ -345,32 +425,15 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
       st_idle += __popc(__ballot_sync(FULL, !(fl & F_HAS)));
 #endif
       if (cur != 0) {
-        unsigned n1 = TC::env(cur), n2 = TC::rob(cur);
-        QNode A = load_qnode<ALL_SMEM>(sm_env, P.env_q, P.env_smem_nodes, n1);
-        QNode B = load_qnode<ALL_SMEM>(sm_rob, P.rob_q, P.rob_smem_nodes, n2);
-        float sa, sb_;
-        bool ov = obb_overlap_q(A, B, bp, sa, sb_);
-        n_bv++;
-        E nxt = 0;
-        if (ov) {
-          if (A.link < 0 && B.link < 0) { lf0 = true; ta0 = (unsigned)(-(A.link + 1)); tb0 = (unsigned)(-(B.link + 1)); }
-          else if (B.link < 0 || (A.link >= 0 && sa > sb_)) {  // descend the environment node
-            nxt = TC::make((unsigned)A.link, n2);
-            M.stack[sp][lane] = TC::make((unsigned)A.link + 1u, n2);
-            sp++;
-          } else {
-            nxt = TC::make(n1, (unsigned)B.link);
-            M.stack[sp][lane] = TC::make(n1, (unsigned)B.link + 1u);
-            sp++;
-          }
-        }
-        if (nxt == 0 && sp > sb) { sp--; nxt = M.stack[sp][lane]; }
-        cur = nxt;
+        dfs_expand_step<E, ALL_SMEM>(cur, sp, sb, M.stack, lane, sm_env, sm_rob, P, bp, lf0, ta0, tb0, lf1, ta1, tb1);
+        n_bv += 2;
       }
-      unsigned m0 = __ballot_sync(FULL, lf0);
-      if (m0) {  // queue the triangle pairs found
-        if (lf0) { M.leafq[nleaf + __popc(m0 & ltmask)] = leaf_entry(lane, epoch, ta0, tb0); fl |= F_PL; }
-        nleaf += __popc(m0);
+      const unsigned m0 = __ballot_sync(FULL, lf0), m1 = __ballot_sync(FULL, lf1);
+      if (m0 | m1) {  // queue the triangle pairs found
+        if (lf0) M.leafq[nleaf + __popc(m0 & ltmask)] = leaf_entry(lane, epoch, ta0, tb0);
+        if (lf1) M.leafq[nleaf + __popc(m0) + __popc(m1 & ltmask)] = leaf_entry(lane, epoch, ta1, tb1);
+        if (lf0 | lf1) fl |= F_PL;
+        nleaf += __popc(m0) + __popc(m1);
         __syncwarp();
       }
       since_flush++;

@@ -147,7 +147,8 @@ __global__ void __launch_bounds__(WARPS * 32, 1) k_transit_dfs(DfsParams P, SegA
 
   const int lane = threadIdx.x & 31;
   const unsigned ltmask = (1u << lane) - 1u;
-  const bool root_leafpair = ((int)__ldg(P.env_q).w < 0) && ((int)__ldg(P.rob_q).w < 0);
+  const E root_task = root_entry<E>(P.env_q, P.rob_q);
+  const bool root_leafpair = root_task == 0;
 
   // lane state
   BoxPose bp;
@@ -237,7 +238,16 @@ __global__ void __launch_bounds__(WARPS * 32, 1) k_transit_dfs(DfsParams P, SegA
           kstep = pend_base + (unsigned)slot;
           fl = F_HAS; sp = 0;
           epoch = (epoch + 1) & 0x7ffu;
-          cur = root_leafpair ? 0 : TC::make(0, 0);
+          // the root box test (the traversal only holds pairs known to overlap): a step whose root boxes are
+          // apart is a finished free step
+          cur = 0;
+          if (!root_leafpair) {
+            const QNode RA = load_qnode<ALL_SMEM>(sm_env, P.env_q, P.env_smem_nodes, 0u);
+            const QNode RB = load_qnode<ALL_SMEM>(sm_rob, P.rob_q, P.rob_smem_nodes, 0u);
+            float sl, va, vb;
+            if (obb_overlap_q2(RA, RB, bp, sl, va, vb)) cur = root_task;
+            n_bv++;
+          }
         }
         int taken = min(pend_n, __popc(idle));
         pend_taken += taken; pend_n -= taken;
@@ -264,35 +274,18 @@ __global__ void __launch_bounds__(WARPS * 32, 1) k_transit_dfs(DfsParams P, SegA
     // (3) one box test per lane: the pair on top of the lane's stack (as in K1)
     const bool any_cur = __any_sync(FULL, cur != 0);
     if (any_cur && !draining_leaf && !draining_re) {
-      bool lf0 = false;
-      unsigned ta0 = 0, tb0 = 0;
+      bool lf0 = false, lf1 = false;
+      unsigned ta0 = 0, tb0 = 0, ta1 = 0, tb1 = 0;
       if (cur != 0) {
-        unsigned n1 = TC::env(cur), n2 = TC::rob(cur);
-        QNode Na = load_qnode<ALL_SMEM>(sm_env, P.env_q, P.env_smem_nodes, n1);
-        QNode Nb = load_qnode<ALL_SMEM>(sm_rob, P.rob_q, P.rob_smem_nodes, n2);
-        float sa, sb_;
-        bool ov = obb_overlap_q(Na, Nb, bp, sa, sb_);
-        n_bv++;
-        E nxt = 0;
-        if (ov) {
-          if (Na.link < 0 && Nb.link < 0) { lf0 = true; ta0 = (unsigned)(-(Na.link + 1)); tb0 = (unsigned)(-(Nb.link + 1)); }
-          else if (Nb.link < 0 || (Na.link >= 0 && sa > sb_)) {  // descend the environment node
-            nxt = TC::make((unsigned)Na.link, n2);
-            M.stack[sp][lane] = TC::make((unsigned)Na.link + 1u, n2);
-            sp++;
-          } else {
-            nxt = TC::make(n1, (unsigned)Nb.link);
-            M.stack[sp][lane] = TC::make(n1, (unsigned)Nb.link + 1u);
-            sp++;
-          }
-        }
-        if (nxt == 0 && sp > 0) { sp--; nxt = M.stack[sp][lane]; }
-        cur = nxt;
+        dfs_expand_step<E, ALL_SMEM>(cur, sp, 0, M.stack, lane, sm_env, sm_rob, P, bp, lf0, ta0, tb0, lf1, ta1, tb1);
+        n_bv += 2;
       }
-      unsigned m0 = __ballot_sync(FULL, lf0);
-      if (m0) {
-        if (lf0) { M.leafq[nleaf + __popc(m0 & ltmask)] = leaf_entry(lane, epoch, ta0, tb0); fl |= F_PL; }
-        nleaf += __popc(m0);
+      const unsigned m0 = __ballot_sync(FULL, lf0), m1 = __ballot_sync(FULL, lf1);
+      if (m0 | m1) {
+        if (lf0) M.leafq[nleaf + __popc(m0 & ltmask)] = leaf_entry(lane, epoch, ta0, tb0);
+        if (lf1) M.leafq[nleaf + __popc(m0) + __popc(m1 & ltmask)] = leaf_entry(lane, epoch, ta1, tb1);
+        if (lf0 | lf1) fl |= F_PL;
+        nleaf += __popc(m0) + __popc(m1);
         __syncwarp();
       }
       since_flush++;
