@@ -4,7 +4,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_SO = os.path.join(_HERE, "libosrgpu.so")
+# OSR_LIB selects a development build of the same library (build.py --variant) for A/B runs
+_SO = os.environ.get("OSR_LIB") or os.path.join(_HERE, "libosrgpu.so")
 _L = None
 
 c_dp = C.POINTER(C.c_double)

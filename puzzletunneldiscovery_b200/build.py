@@ -26,6 +26,20 @@ def stale():
     return any(os.path.getmtime(os.path.join(CSRC, d)) > t for d in DEPS)
 
 
+def build_variant(tag, defines):
+    """Development builds for A/B runs (scripts/k1_variants.sh): libosrgpu_<tag>.so with extra -D flags, selected at
+    run time with OSR_LIB=<path>.  Not part of the product build."""
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    out = os.path.join(HERE, "libosrgpu_%s.so" % tag)
+    cmd = [nvcc] + NVCC_FLAGS + ["-D" + d for d in defines] + ["-ccbin", "g++", "-o", out] + \
+          [os.path.join(CSRC, s) for s in SOURCES]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if r.returncode != 0:
+        sys.stderr.write(r.stdout)
+        raise RuntimeError("nvcc failed building " + out)
+    return out
+
+
 def build(force=False, verbose=False):
     if not force and not stale():
         return OUT
@@ -42,4 +56,7 @@ def build(force=False, verbose=False):
 
 
 if __name__ == "__main__":
-    build(force=True, verbose=True)
+    if len(sys.argv) > 2 and sys.argv[1] == "--variant":   # build.py --variant TAG DEFINE [DEFINE ...]
+        print(build_variant(sys.argv[2], sys.argv[3:]))
+    else:
+        build(force=True, verbose=True)

@@ -7,7 +7,11 @@
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <atomic>
+#include <chrono>
+#include <cstdio>
 #include <fstream>
+#include <future>
 #include <limits>
 #include <queue>
 #include <sstream>
@@ -142,6 +146,13 @@ struct BuildNode {
 // Builder options (development switches; the defaults are the measured best, see DESIGN.md "BVH quality").
 //   OSR_BVH_REFINE  0: covariance (PCA) frame as FCL's BVFitter   1: + local search minimising the box AREA   2: ... VOLUME
 //   OSR_BVH_SPLIT   0: mean of centroids on the longest axis (FCL SPLIT_METHOD_MEAN)   1: surface-area sweep in the box frame
+static std::atomic<long long> g_t_refine{0}, g_t_sweep{0}, g_t_fit{0};
+struct ScopedNs {
+  std::atomic<long long>& acc;
+  std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+  explicit ScopedNs(std::atomic<long long>& a) : acc(a) {}
+  ~ScopedNs() { acc += std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now() - t0).count(); }
+};
 static int env_int(const char* name, int dflt) {
   const char* e = getenv(name);
   return e ? atoi(e) : dflt;
@@ -154,6 +165,7 @@ struct Builder {
   std::vector<Vec3> cent;
   int depth = 0;
   int max_depth = 64;
+  int par_levels = 5;   // levels whose left subtree is built by another thread (<= 2^5 threads in flight)
   const int opt_refine = env_int("OSR_BVH_REFINE", 1);
   const int opt_split = env_int("OSR_BVH_SPLIT", 1);
   explicit Builder(const UnitModel& mm) : m(mm) {}
@@ -180,6 +192,7 @@ struct Builder {
   // shrinks the box, halve the step.  Large nodes are searched on their extreme points along 96 fixed directions
   // (the final extents are always taken over every vertex, so containment never depends on the search).
   void refine_frame(int first, int n, Vec3 ax[3]) const {
+    ScopedNs tm(g_t_refine);
     std::vector<Vec3> pts;
     pts.reserve((size_t)3 * n);
     for (int i = 0; i < n; i++)
@@ -202,9 +215,9 @@ struct Builder {
       pts.swap(ex);
     }
     double best = frame_cost(pts, ax, opt_refine);
-    for (double step = 0.4; step > 0.004; step *= 0.5) {
+    for (double step = 0.4; step > 0.01; step *= 0.5) {
       bool improved = true;
-      for (int it = 0; improved && it < 32; it++) {
+      for (int it = 0; improved && it < 12; it++) {
         improved = false;
         for (int about = 0; about < 3; about++)
           for (int sg = -1; sg <= 1; sg += 2) {
@@ -234,6 +247,7 @@ struct Builder {
   // derived from the exact (fp64) projections on the rounded axes and rounded outwards, so the
   // fp32 box is a superset of the fp64 triangles.
   void fit(int first, int n, BuildNode& nd) {
+    ScopedNs tm(g_t_fit);
     double S1[3] = {0, 0, 0}, S2[3][3] = {{0}};
     for (int i = 0; i < n; i++)
       for (int k = 0; k < 3; k++) {
@@ -357,8 +371,8 @@ struct Builder {
   // Surface-area sweep in the node's own box frame: triangles sorted by centroid along each box axis, cost of a cut
   // = area(box of the left part) * count + area(box of the right part) * count with both boxes axis-aligned in that
   // frame; the cut must leave both sides small enough for the depth budget.  Reorders prims[first, first+n).
-  int sweep_split(int first, int n, int id, int lvl) {
-    const BuildNode& nd = nodes[id];
+  int sweep_split(int first, int n, const BuildNode& nd, int lvl) {
+    ScopedNs tm(g_t_sweep);
     Vec3 ax[3];
     for (int k = 0; k < 3; k++) ax[k] = {(double)nd.axis[3 * k], (double)nd.axis[3 * k + 1], (double)nd.axis[3 * k + 2]};
     const int room = max_depth - lvl - 1;                       // levels left below the children
@@ -368,7 +382,7 @@ struct Builder {
     struct Box { double lo[3], hi[3]; };
     std::vector<Box> tb(n);
     std::vector<double> key(n);
-    std::vector<int> idx(n), best_order;
+    std::vector<int> idx(n), order[3];
     for (int i = 0; i < n; i++) {
       Box& b = tb[i];
       for (int a = 0; a < 3; a++) { b.lo[a] = 1e300; b.hi[a] = -1e300; }
@@ -388,7 +402,7 @@ struct Builder {
       for (int a = 0; a < 3; a++) { b.lo[a] = std::min(b.lo[a], o.lo[a]); b.hi[a] = std::max(b.hi[a], o.hi[a]); }
     };
     double best = 1e300;
-    int best_k = -1;
+    int best_k = -1, best_axis = -1;
     std::vector<double> right(n + 1);
     for (int a = 0; a < 3; a++) {
       for (int i = 0; i < n; i++) { idx[i] = i; key[i] = dot(ax[a], cent[prims[first + i]]); }
@@ -402,53 +416,67 @@ struct Builder {
         grow(acc, tb[idx[k - 1]]);
         if (k < kmin || k > kmax) continue;
         double c = area(acc) * k + right[k] * (n - k);
-        if (c < best) { best = c; best_k = k; best_order = idx; }
+        if (c < best) { best = c; best_k = k; best_axis = a; }
       }
+      order[a] = idx;
     }
     if (best_k < 0) return -1;
+    const std::vector<int>& best_order = order[best_axis];
     std::vector<int> tmp(n);
     for (int i = 0; i < n; i++) tmp[i] = prims[first + best_order[i]];
     std::copy(tmp.begin(), tmp.end(), prims.begin() + first);
     return best_k;
   }
 
-  int build(int first, int n, int lvl) {
-    depth = std::max(depth, lvl);
-    int id = (int)nodes.size();
-    nodes.emplace_back();
-    {
-      BuildNode nd;
-      fit(first, n, nd);
-      fit_q(first, n, nd);
-      nodes[id] = nd;
-    }
-    if (n == 1) { nodes[id].tri = prims[first]; return id; }
-    // split along the box's longest axis at the mean centroid; fall back to the median when
-    // the mean split is badly unbalanced (keeps the depth, hence the traversal stack, small)
-    Vec3 sv = {(double)nodes[id].axis[0], (double)nodes[id].axis[1], (double)nodes[id].axis[2]};
-    {
-      int la = 0;
-      for (int a = 1; a < 3; a++) if (nodes[id].ext[a] > nodes[id].ext[la]) la = a;
-      sv = {(double)nodes[id].axis[3 * la], (double)nodes[id].axis[3 * la + 1], (double)nodes[id].axis[3 * la + 2]};
-    }
+  // Builds the subtree over prims[first, first+n) into `out` (child ids are indices into `out`); returns its root id.
+  // Subtrees operate on disjoint ranges of `prims`, so the first levels hand their left child to another thread.
+  int build(std::vector<BuildNode>& out, int& max_lvl, int first, int n, int lvl) {
+    max_lvl = std::max(max_lvl, lvl);
+    int id = (int)out.size();
+    out.emplace_back();
+    BuildNode nd;
+    fit(first, n, nd);
+    fit_q(first, n, nd);
+    if (n == 1) { nd.tri = prims[first]; out[id] = nd; return id; }
     int c1 = -1;
-    if (opt_split == 1 && n > 2) c1 = sweep_split(first, n, id, lvl);
+    if (opt_split == 1 && n > 2) c1 = sweep_split(first, n, nd, lvl);
     if (c1 < 0) {
-    double mean = 0;
-    for (int i = 0; i < n; i++) mean += dot(sv, cent[prims[first + i]]);
-    mean /= n;
-    auto mid = std::partition(prims.begin() + first, prims.begin() + first + n,
-                              [&](int t) { return dot(sv, cent[t]) <= mean; });
-    c1 = (int)(mid - (prims.begin() + first));
-    if (c1 < n / 8 + (n < 8 ? 1 : 0) || n - c1 < n / 8 + (n < 8 ? 1 : 0) || c1 == 0 || c1 == n) {
-      c1 = n / 2;
-      std::nth_element(prims.begin() + first, prims.begin() + first + c1, prims.begin() + first + n,
-                       [&](int a, int b) { return dot(sv, cent[a]) < dot(sv, cent[b]); });
+      // split along the box's longest axis at the mean centroid (FCL SPLIT_METHOD_MEAN); fall back to the median
+      // when the mean split is badly unbalanced (keeps the depth, hence the traversal stack, small)
+      int la = 0;
+      for (int a = 1; a < 3; a++) if (nd.ext[a] > nd.ext[la]) la = a;
+      Vec3 sv = {(double)nd.axis[3 * la], (double)nd.axis[3 * la + 1], (double)nd.axis[3 * la + 2]};
+      double mean = 0;
+      for (int i = 0; i < n; i++) mean += dot(sv, cent[prims[first + i]]);
+      mean /= n;
+      auto mid = std::partition(prims.begin() + first, prims.begin() + first + n,
+                                [&](int t) { return dot(sv, cent[t]) <= mean; });
+      c1 = (int)(mid - (prims.begin() + first));
+      if (c1 < n / 8 + (n < 8 ? 1 : 0) || n - c1 < n / 8 + (n < 8 ? 1 : 0) || c1 == 0 || c1 == n) {
+        c1 = n / 2;
+        std::nth_element(prims.begin() + first, prims.begin() + first + c1, prims.begin() + first + n,
+                         [&](int a, int b) { return dot(sv, cent[a]) < dot(sv, cent[b]); });
+      }
     }
+    if (lvl < par_levels && n >= 4096) {
+      std::vector<BuildNode> lsub;
+      int llvl = 0;
+      std::future<int> fut = std::async(std::launch::async, [&, first, c1, lvl] { return build(lsub, llvl, first, c1, lvl + 1); });
+      int r = build(out, max_lvl, first + c1, n - c1, lvl + 1);
+      int lroot = fut.get();
+      const int off = (int)out.size();
+      for (BuildNode b : lsub) {
+        if (b.left >= 0) { b.left += off; b.right += off; }
+        out.push_back(b);
+      }
+      max_lvl = std::max(max_lvl, llvl);
+      nd.left = lroot + off; nd.right = r;
+    } else {
+      int l = build(out, max_lvl, first, c1, lvl + 1);
+      int r = build(out, max_lvl, first + c1, n - c1, lvl + 1);
+      nd.left = l; nd.right = r;
     }
-    int l = build(first, c1, lvl + 1);
-    int r = build(first + c1, n - c1, lvl + 1);
-    nodes[id].left = l; nodes[id].right = r;
+    out[id] = nd;
     return id;
   }
 };
@@ -471,7 +499,12 @@ void build_gpu_bvh(UnitModel& m) {
     while ((1LL << lg) < n) lg++;
     b.max_depth = lg + 3;   // the sweep split may unbalance the tree by at most this much (traversal stack depth)
   }
-  b.build(0, n, 0);
+  auto t_start = std::chrono::steady_clock::now();
+  b.build(b.nodes, b.depth, 0, n, 0);
+  if (getenv("OSR_BVH_VERBOSE"))
+    fprintf(stderr, "[bvh] %d triangles, depth %d: %.2f s wall; thread-seconds fit %.2f (of which refine %.2f), sweep split %.2f\n", n,
+            b.depth, std::chrono::duration<double>(std::chrono::steady_clock::now() - t_start).count(), g_t_fit.load() * 1e-9,
+            g_t_refine.load() * 1e-9, g_t_sweep.load() * 1e-9);
   // breadth-first renumbering with sibling pairs adjacent
   int N = (int)b.nodes.size();
   std::vector<int> order;   // new index -> build id

@@ -41,14 +41,31 @@ struct DfsParams {
   unsigned long long feed_timeout_ns;  // give up waiting for an upload after this long (%globaltimer; OSR_FEED_TIMEOUT_S)
 };
 
+// Tunables (the -D overrides exist for the A/B builds of scripts/k1_variants.sh; defaults = measured best)
+#ifndef OSR_LEAF_FLUSH
+#define OSR_LEAF_FLUSH 16
+#endif
+#ifndef OSR_RE_FLUSH
+#define OSR_RE_FLUSH 8
+#endif
+#ifndef OSR_WAIT_FLUSH
+#define OSR_WAIT_FLUSH 12
+#endif
+#ifndef OSR_PAUSE_ON_LEAF
+#define OSR_PAUSE_ON_LEAF 2
+#endif
 constexpr int DFS_WARPS = 12;   // 3 per scheduler: 4 would need <= 128 registers (16 K registers per SM sub-partition)
 constexpr int DFS_THREADS = DFS_WARPS * 32;
 constexpr int LEAFQ_CAP = 96;    // >= LEAF_FLUSH - 1 + 64 (at most two new pairs per lane and iteration)
 constexpr int REQ_CAP = 64;
-constexpr int LEAF_FLUSH = 16;   // drain the triangle-pair queue once it holds this many pairs
-constexpr int RE_FLUSH = 8;      // same for the queue of pairs awaiting the exact fp64 predicate
-constexpr int WAIT_FLUSH = 4;    // ... or once this many lanes have nothing left but queued pairs
+constexpr int LEAF_FLUSH = OSR_LEAF_FLUSH;   // drain the triangle-pair queue once it holds this many pairs
+constexpr int RE_FLUSH = OSR_RE_FLUSH;       // same for the queue of pairs awaiting the exact fp64 predicate
+constexpr int WAIT_FLUSH = OSR_WAIT_FLUSH;   // ... or once this many lanes have nothing left but queued pairs
 constexpr int REFILL_MIN = 1;    // pull new poses once this many lanes are idle
+// 0: a lane keeps traversing while its triangle pairs wait in a queue; 1: it pauses while pairs wait for the fp32
+// filter (with depth-ordered expansion the first pair found is usually the hit); 2: also while pairs wait for fp64
+constexpr int PAUSE_ON_LEAF = OSR_PAUSE_ON_LEAF;
+constexpr unsigned PAUSE_MASK = PAUSE_ON_LEAF == 2 ? 12u : (PAUSE_ON_LEAF == 1 ? 4u : 0u);   // F_PL | F_PR bits
 
 // work-stack entry = one OVERLAPPING (environment node, robot node) pair still to be expanded, stored as
 // (first child of the node that gets split, the other node, which tree is split); 0 means "none".
@@ -414,17 +431,18 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
     // (3) one box test per lane: the pair on top of the lane's stack; an overlapping pair is replaced by its
     // two child pairs (not while a queue is being drained: the queues' capacity assumes at most one iteration
     // of new triangle pairs on top)
-    const bool any_cur = __any_sync(FULL, cur != 0);
+    const bool runnable = cur != 0 && !(fl & PAUSE_MASK);
+    const bool any_cur = __any_sync(FULL, runnable);
     if (any_cur && !draining_leaf && !draining_re) {
       bool lf0 = false, lf1 = false;
       unsigned ta0 = 0, tb0 = 0, ta1 = 0, tb1 = 0;
 #ifdef OSR_DFS_STATS
       st_iters++;
-      st_active += __popc(__ballot_sync(FULL, cur != 0));
-      st_wait += __popc(__ballot_sync(FULL, (fl & F_HAS) && cur == 0));
+      st_active += __popc(__ballot_sync(FULL, runnable));
+      st_wait += __popc(__ballot_sync(FULL, (fl & F_HAS) && !runnable));
       st_idle += __popc(__ballot_sync(FULL, !(fl & F_HAS)));
 #endif
-      if (cur != 0) {
+      if (runnable) {
         dfs_expand_step<E, ALL_SMEM>(cur, sp, sb, M.stack, lane, sm_env, sm_rob, P, bp, lf0, ta0, tb0, lf1, ta1, tb1);
         n_bv += 2;
       }
@@ -449,11 +467,11 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
       else if (!__any_sync(FULL, (fl & F_HAS) != 0) && exhausted && pend_n == 0) break;
     } else {
       if (nleaf > 0) {
-        unsigned waiting = __ballot_sync(FULL, (fl & (F_HAS | F_PL)) == (F_HAS | F_PL) && cur == 0);
+        unsigned waiting = __ballot_sync(FULL, (fl & (F_HAS | F_PL)) == (F_HAS | F_PL) && (cur == 0 || (fl & PAUSE_MASK)));
         do_leaf = nleaf >= LEAF_FLUSH || __popc(waiting) >= WAIT_FLUSH || since_flush > 1024;
       }
       if (!do_leaf && nre > 0) {
-        unsigned waiting = __ballot_sync(FULL, (fl & (F_HAS | F_PL | F_PR)) == (F_HAS | F_PR) && cur == 0);
+        unsigned waiting = __ballot_sync(FULL, (fl & (F_HAS | F_PL | F_PR)) == (F_HAS | F_PR) && (cur == 0 || (fl & PAUSE_MASK)));
         do_re = nre >= RE_FLUSH || __popc(waiting) >= WAIT_FLUSH || re_age > 1024;
       }
     }
