@@ -154,6 +154,12 @@ double osr_distance(const double a[7], const double b[7]);
  * last executed step, *last_valid = delta of the last valid step (the input delta when there is none). */
 int osr_walk_deltas(double* delta, double verify_delta, double dist, int nsteps, double* last_valid);
 
+/* Host build of the kernels' triangle-pair predicates (csrc/sat17.h), n pairs of 18 doubles P1 P2 P3 Q1 Q2 Q3 with Q
+ * already in P's frame (what Intersect::intersect_Triangle sees after Q' = R Q + T, intersect-inl.h:598-617):
+ * filter[i] = fp32 SAT-17 filter (0 separated, 1 intersecting, 2 undecided), exact[i] = fp64 SAT-17 in the reference's
+ * operation order (the label).  Either output may be NULL.  Needs no device. */
+int osr_triangle_pair_predicates(const double* tris, int64_t n, uint8_t* filter, uint8_t* exact);
+
 void osr_interpolate(const double a[7], const double b[7], double tau, double out[7]);
 void osr_apply(const double from[7], const double tr[3], const double aa[3], double out[7]);
 

@@ -75,6 +75,7 @@ SIGNATURES = {
     "osr_host_free": (None, [C.c_void_p]),
     "osr_distance": (C.c_double, [c_dp, c_dp]),
     "osr_walk_deltas": (C.c_int, [c_dp, C.c_double, C.c_double, C.c_int, c_dp]),
+    "osr_triangle_pair_predicates": (C.c_int, [c_dp, C.c_int64, c_u8p, c_u8p]),
     "osr_interpolate": (None, [c_dp, c_dp, C.c_double, c_dp]),
     "osr_apply": (None, [c_dp, c_dp, c_dp, c_dp]),
     "osr_is_valid_states_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),

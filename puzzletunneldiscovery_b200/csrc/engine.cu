@@ -1204,6 +1204,28 @@ int osr_walk_deltas(double* delta, double verify_delta, double dist, int nsteps,
   return valid;
 }
 
+// Host build of the two triangle-pair predicates of the traversal kernels (sat17.h), for the parity tests:
+// the vertices are taken relative to P1 and rounded to fp32 exactly as the kernels do.
+int osr_triangle_pair_predicates(const double* tris, int64_t n, uint8_t* filter, uint8_t* exact) {
+  if (n < 0 || (n > 0 && !tris)) return fail(OSR_EINVAL, "bad arguments");
+  for (int64_t i = 0; i < n; i++) {
+    const double* t = tris + 18 * i;
+    osr::TriPair<double> td;
+    for (int k = 0; k < 3; k++) {
+      td.p2[k] = t[3 + k] - t[k]; td.p3[k] = t[6 + k] - t[k];
+      td.q1[k] = t[9 + k] - t[k]; td.q2[k] = t[12 + k] - t[k]; td.q3[k] = t[15 + k] - t[k];
+    }
+    osr::TriPair<float> tf;
+    for (int k = 0; k < 3; k++) {
+      tf.p2[k] = (float)td.p2[k]; tf.p3[k] = (float)td.p3[k];
+      tf.q1[k] = (float)td.q1[k]; tf.q2[k] = (float)td.q2[k]; tf.q3[k] = (float)td.q3[k];
+    }
+    if (filter) filter[i] = (uint8_t)osr::sat17_filter_c(tf);
+    if (exact) exact[i] = osr::sat17_exact_c(td) ? 1 : 0;
+  }
+  return OSR_OK;
+}
+
 // ---- visibility (batched isValidTransition) -----------------------------------------------------
 static int visibility_common(osr_world* w, const double* q0, int64_t m, int unit0, const double* q1, int64_t n,
                              int unit1, double vmag, int8_t* out, bool pairwise) {
