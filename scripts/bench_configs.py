@@ -25,8 +25,8 @@ VD_TOUCH = 0.0125 / 8   # /root/reference/src/GP/condor_touch_configuration.py:3
 PREFIX_SCALE = 1        # --prefix-scale: multiplies the size of every oracle-checked prefix
 
 
-def world(cls, which="org", centre=None, meshes=None):
-    w = cls()
+def world(cls, which="org", centre=None, meshes=None, devices=None):
+    w = cls(devices=devices) if devices is not None else cls()
     if meshes is not None:
         w.set_meshes(*meshes)
     else:
@@ -68,7 +68,25 @@ def leg_touch(O, scale, fine=False):
     same = bool((isf[:m] == oisf.astype(bool)).all() and (st[:m] == ocnt[:, 0]).all() and
                 np.abs(tt[:m] - ott).max() < 1e-12 and np.abs(ft[:m] - oft).max() < 1e-12 and
                 np.abs(fh[:m] - ofh).max() < 1e-12)
+    # size-independent properties on the WHOLE batch (the reference's own invariant, unit_world.cc:325-326, and the
+    # structure of its return tuple): last_free is a valid state, first_hit of a blocked walk is not, a blocked walk
+    # stops strictly after its last free tau, a free one ends at tau = 1 with the shadowed touch_tau = 0
+    lf_ok = uw.is_valid_states(lf)
+    blocked = ~isf
+    walked = st > 0
+    props = {"last_free_states_all_valid": bool(lf_ok.all()),
+             "first_hit_states_of_blocked_walks_all_invalid": bool((~uw.is_valid_states(fh[blocked & walked])).all()),
+             "blocked_walks_have_free_tau_lt_touch_tau": bool((ft[blocked & walked] < tt[blocked & walked]).all()),
+             "free_walks_end_at_tau_1": bool((np.abs(ft[isf] - 1.0) <= 2.3e-16).all() and (tt[isf] == 0.0).all()),
+             "label_checksum": int(np.dot(isf.astype(np.int64), np.arange(1, n + 1, dtype=np.int64) % 1000003)),
+             "steps_checksum": int(st.sum())}
+    half = n // 2     # the same batch evaluated as two halves gives the same rows (no dependence on batch layout)
+    h1 = uw.transit_states_to_with_contact(fr[:half], to[:half], vd, with_steps=True)
+    h2 = uw.transit_states_to_with_contact(fr[half:], to[half:], vd, with_steps=True)
+    props["two_half_batches_equal_the_whole"] = bool(np.array_equal(np.concatenate([h1[5], h2[5]]), st) and
+                                                      np.array_equal(np.concatenate([h1[0], h2[0]]), lf))
     return {"leg": "touch_fine" if fine else "touch", "geometry": "G-wt2", "segments": n, "verify_delta": vd,
+            "properties_full_size": props,
             "segments_per_s": n / dt, "validity_checks_per_s": float(st.sum()) / dt,
             "mean_steps_per_segment": float(st.mean()), "free_fraction": float(isf.mean()), "seconds": dt,
             "oracle_prefix": m, "same_first_contact_step_as_oracle_on_prefix": same,
@@ -98,7 +116,18 @@ def leg_edges(O, scale):
     ores, ocnt = ow.is_valid_transitions(fr[:m], to[:m], vd, counters=True)
     dtc = time.perf_counter() - tc
     c = uw.counters(reset=True)
+    # full-size properties: a random subset re-evaluated on its own gives the same labels; an edge reversed end for
+    # end is walked at different taus but between the same two valid milestones, so the two directions may only
+    # disagree when a contact lies inside one verify_delta of the path (reported, not asserted)
+    rs = np.random.RandomState(11)
+    sub = rs.choice(len(fr), min(len(fr), 1 << 16), replace=False)
+    again = uw.is_valid_transitions(fr[sub], to[sub], vd)
+    rev = uw.is_valid_transitions(to[sub], fr[sub], vd)
+    props = {"subset_relabelled_alone_equal": bool(np.array_equal(again, res[sub])),
+             "reversed_edges_disagree_fraction": float((rev != res[sub]).mean()),
+             "label_checksum": int(np.dot(res.astype(np.int64), np.arange(1, len(res) + 1, dtype=np.int64) % 1000003))}
     return {"leg": "edges", "geometry": "G-org", "milestones": len(q), "edges": len(fr), "verify_delta": vd,
+            "properties_full_size": props,
             "edges_per_s": len(fr) / dt, "seconds": dt, "valid_edge_fraction": float(res.mean()),
             "gpu_knn_seconds": t_knn, "knn_edges_per_s": len(fr) / t_knn,
             "knn_first_window_equals_host_restatement": bool(same_edges), "oracle_prefix": m,
@@ -109,31 +138,55 @@ def leg_edges(O, scale):
                          "threads": O.lib().orc_max_threads()}}
 
 
-def leg_hipoly(O, scale):
-    """Config 4: validity on the subdivided alpha puzzle (robot 100 800 x env 487 872 triangles)."""
+def leg_hipoly(O, scale, device_counts=(1,)):
+    """Config 4: validity on the subdivided alpha puzzle (robot 100 800 x env 487 872 triangles), one
+    handle driving 1 / 2 / 4 / 8 GPUs of the box (strong scaling: the same batch, geometry replicated, index ranges
+    per device, host gather)."""
+    import torch
     eV, eF = W.load_obj_vf(os.path.join(A, "alpha_env-1.2.org.obj"))
     rV, rF = W.load_obj_vf(os.path.join(A, "alpha-1.2.org.obj"))
     EV, EF = W.subdivide(eV, eF, 22)
     RV, RF = W.subdivide(rV, rF, 10)
-    t = time.perf_counter()
-    uw = world(pyosr.UnitWorld, meshes=(EV, EF, RV, RF))
-    t_build = time.perf_counter() - t
     n = int((1 << 22) * scale)
     q = W.random_states(n, seed=3)
-    _, dt_pageable = timed(lambda: uw.is_valid_states(q))
     qp = pyosr.pinned_empty((n, 7)); qp[:] = q          # page-locked sample / label arrays (osr_host_alloc)
     op = pyosr.pinned_empty(n, np.uint8)
-    v, dt = timed(lambda: uw.is_valid_states(qp, out=op))
-    c = uw.counters(reset=True)
-    ow = world(O.OracleWorld, meshes=(EV, EF, RV, RF))
+    navail = torch.cuda.device_count()
+    # the robot frame's origin is the mean of the mesh vertices (Scene::mean_of_vertices_), which subdivision moves:
+    # G-hi is pinned to the centre of the original mesh so that the same states mean the same poses on both
+    u0 = world(pyosr.UnitWorld)
+    centre = u0.robot_center
+    scaling = []
+    v = None
+    for nd in device_counts:
+        if nd > navail:
+            continue
+        t = time.perf_counter()
+        uw = world(pyosr.UnitWorld, centre=centre, meshes=(EV, EF, RV, RF), devices=list(range(nd)))
+        t_build = time.perf_counter() - t
+        vv, dt = timed(lambda: uw.is_valid_states(qp, out=op), reps=2)
+        row = {"gpus": nd, "configs_per_s": n / dt, "seconds": dt, "finalize_seconds (host BVH build + upload)": t_build}
+        if nd == 1:
+            _, dt_pageable = timed(lambda: uw.is_valid_states(q))
+            row["configs_per_s_pageable_host_arrays"] = n / dt_pageable
+            c = uw.counters(reset=True)
+            v = np.array(vv, copy=True)
+        else:
+            row["labels_equal_one_gpu"] = bool(np.array_equal(np.asarray(vv), v))
+        scaling.append(row)
+        del uw
+    # the subdivided meshes describe the same surfaces: labels on G-hi equal the labels of the same states on the
+    # original 1 008-triangle meshes except where the rounding of the new vertices decides (counted)
+    v_org = u0.is_valid_states(qp)
+    ow = world(O.OracleWorld, centre=centre, meshes=(EV, EF, RV, RF))
     m = 1 << 16
     tc = time.perf_counter()
     vo = ow.is_valid_states(q[:m])
     dtc = time.perf_counter() - tc
     return {"leg": "hipoly", "geometry": "G-hi (env %d, robot %d triangles)" % (len(EF), len(RF)), "states": n,
-            "configs_per_s": n / dt, "seconds": dt, "configs_per_s_pageable_host_arrays": n / dt_pageable,
-            "valid_fraction": float(v.mean()),
-            "finalize_seconds (host BVH build + upload)": t_build, "oracle_prefix": m,
+            "configs_per_s": scaling[0]["configs_per_s"], "seconds": scaling[0]["seconds"],
+            "strong_scaling_one_handle": scaling, "valid_fraction": float(v.mean()),
+            "labels_differing_from_G-org_same_states": int((v != v_org).sum()), "oracle_prefix": m,
             "labels_equal_oracle_on_prefix": bool(np.array_equal(v[:m], vo.astype(bool))),
             "cpu_port": {"configs_per_s": m / dtc, "threads": O.lib().orc_max_threads()}}
 
@@ -149,7 +202,7 @@ def leg_contacts(O, scale):
     fr, to = W.touch_rays(fr0, ns, seed=4)
     lf, fh, isf, ft, tt = uw.transit_states_to_with_contact(fr, to, VD_TOUCH)
     hit = fh[~isf]
-    cap = 1 << 21
+    cap = max(1 << 21, 24 * len(hit))
     r, dt = timed(lambda: uw.intersecting_segments_batch(hit, cap=cap, with_bary=True))
     m = min(len(hit), 1024)
     tc = time.perf_counter()
@@ -165,7 +218,19 @@ def leg_contacts(O, scale):
     b = canon(off, faces, segs, cop)
     same_faces = bool(a.shape == b.shape and np.array_equal(a[:, :3], b[:, :3]) and np.array_equal(a[:, 9], b[:, 9]))
     err = float(np.abs(a[:, 3:9] - b[:, 3:9]).max()) if same_faces and k else None
+    # full-size properties: every first-hit state has at least one row; a random subset of states re-evaluated alone
+    # yields the same rows; both surface points of a row (barycentrics on each triangle) are the segment midpoint
+    cnt = np.diff(r["offsets"])
+    rs = np.random.RandomState(12)
+    sub = np.sort(rs.choice(len(hit), min(len(hit), 4096), replace=False))
+    r2 = uw.intersecting_segments_batch(hit[sub], cap=cap, with_bary=True)
+    rows_sub = np.concatenate([np.arange(r["offsets"][i], r["offsets"][i + 1]) for i in sub]) if len(sub) else np.zeros(0, int)
+    props = {"every_first_hit_state_has_a_contact_row": bool((cnt > 0).all()), "no_overflow": bool(r["total"] <= cap),
+             "subset_states_alone_give_the_same_rows": bool(np.array_equal(np.diff(r2["offsets"]), cnt[sub]) and
+                                                             np.array_equal(r2["faces"][:r2["total"]], r["faces"][rows_sub]) and
+                                                             np.array_equal(r2["seg"][:r2["total"]], r["seg"][rows_sub]))}
     return {"leg": "contacts", "geometry": "G-wt2", "states": int(len(hit)), "contact_rows": int(r["total"]),
+            "properties_full_size": props,
             "contacts_per_s": r["total"] / dt, "states_per_s": len(hit) / dt, "seconds": dt,
             "rows_per_state": r["total"] / max(1, len(hit)), "oracle_prefix_states": m,
             "rows_equal_oracle_on_prefix": same_faces, "max_abs_segment_error_on_prefix": err,
@@ -272,13 +337,21 @@ def main():
     ap.add_argument("--legs", default="touch,touch_fine,edges,hipoly,contacts,clearance,keyconf,ompl_motions")
     ap.add_argument("--scale", type=float, default=1.0)
     ap.add_argument("--prefix-scale", type=int, default=1)
+    ap.add_argument("--full", action="store_true",
+                    help="BASELINE.json's sizes: 2^20 touch segments (2^16 at recommended_cres), 4 Mi milestones / 3.3e7 "
+                         "k-NN edges, 2^24 states on G-hi, >= 2^20 contact rows")
+    ap.add_argument("--devices", default="1", help="device counts of the hipoly leg, e.g. 1,2,4,8")
     args = ap.parse_args()
     global PREFIX_SCALE
     PREFIX_SCALE = max(1, args.prefix_scale)
     from oracle import oracle as O
-    legs = {"touch": lambda: leg_touch(O, args.scale), "touch_fine": lambda: leg_touch(O, args.scale, fine=True),
-            "edges": lambda: leg_edges(O, args.scale), "hipoly": lambda: leg_hipoly(O, args.scale),
-            "contacts": lambda: leg_contacts(O, args.scale), "clearance": lambda: leg_clearance(O, args.scale), "keyconf": lambda: leg_keyconf(O, args.scale), "ompl_motions": lambda: leg_ompl(O, args.scale)}
+    mult = {"touch": 4, "touch_fine": 16, "edges": 64, "hipoly": 4, "contacts": 2} if args.full else {}
+    sc = lambda leg: args.scale * mult.get(leg, 1)
+    devs = tuple(int(x) for x in args.devices.split(","))
+    legs = {"touch": lambda: leg_touch(O, sc("touch")), "touch_fine": lambda: leg_touch(O, sc("touch_fine"), fine=True),
+            "edges": lambda: leg_edges(O, sc("edges")), "hipoly": lambda: leg_hipoly(O, sc("hipoly"), devs),
+            "contacts": lambda: leg_contacts(O, sc("contacts")), "clearance": lambda: leg_clearance(O, args.scale),
+            "keyconf": lambda: leg_keyconf(O, args.scale), "ompl_motions": lambda: leg_ompl(O, args.scale)}
     for name in args.legs.split(","):
         t = time.perf_counter()
         try:
