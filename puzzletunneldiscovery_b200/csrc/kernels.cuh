@@ -50,15 +50,22 @@ struct KParams {
   double sweep_rmax;                 // K2: windows whose swept radius exceeds this are not attempted
   double sweep_rstart;               // K2: swept radius of the first windows of a walk
   int sweep_short_tile;              // K2: steps of the exact tile that follows a blocked 4-step window (1..32)
+  int sweep_resolve;                 // K2: most exact (triangle pair, step) tests spent on one window whose swept
+                                     //     traversal left pairs that are not provably clear (0 = such windows are blocked)
+  double sweep_keep_rmax;            // K2: ... and only windows whose swept radius stays below this keep pairs at all
 };
 
 constexpr int STACK_CAP = 512;   // shared-memory stack entries per warp
 constexpr int SPILL_CHUNK = 256; // entries moved per spill / refill
 constexpr unsigned FULL = 0xffffffffu;
+// K2: most triangle pairs a swept traversal keeps for exact per-step tests of one window.  Kept small: shared memory
+// per block decides how much of the SM's 256 KB is left as L1 for the node and triangle reads.
+constexpr int SURV_CAP = 128;
 
 struct __align__(16) WarpShared {
   unsigned long long stack[STACK_CAP];
   unsigned long long leafq[64];
+  unsigned long long surv[SURV_CAP];  // (window, env triangle, robot triangle) not separated by more than the window's radius
   double Rd[12][32];  // per pose: R (row-major 9) + t (3), fp64, robot in env frame
   float Rf[12][32];   // same rounded to fp32
   float eta[32];      // per-pose absolute inflation of box extents
@@ -168,42 +175,6 @@ __device__ __forceinline__ void axis_gaps(const T* ax, const Tri6<T>& t, T& g1, 
   g2 = mnQ - mxP;
 }
 
-// Swept windows of K2: true when one of the 11 face-normal / edge x edge axes separates the two triangles by MORE
-// than r (projection gap > r |axis|).  Then the triangles stay strictly apart, along that fixed direction, however
-// the points of one of them move by at most r.  fp64; the caller's r carries an absolute slack far above rounding.
-__device__ __noinline__ bool tri_gap_clear(const Tri6<double>& t, double r) {
-  double e0[3], e1[3], e2[3], f0[3], f1[3], f2[3], ax[3], g1, g2;
-#pragma unroll
-  for (int k = 0; k < 3; k++) {
-    e0[k] = t.p2[k]; e1[k] = t.p3[k] - t.p2[k]; e2[k] = -t.p3[k];
-    f0[k] = t.q2[k] - t.q1[k]; f1[k] = t.q3[k] - t.q2[k]; f2[k] = t.q1[k] - t.q3[k];
-  }
-  const double rr = r * r * (1.0 + 1e-9);
-  crossT(e0, e1, ax);
-  axis_gaps(ax, t, g1, g2);
-  double g = fmax(g1, g2);
-  if (g > 0.0 && g * g > rr * dotT(ax, ax)) return true;
-  crossT(f0, f1, ax);
-  axis_gaps(ax, t, g1, g2);
-  g = fmax(g1, g2);
-  if (g > 0.0 && g * g > rr * dotT(ax, ax)) return true;
-#pragma unroll 1
-  for (int a = 0; a < 9; a++) {
-    const int i = a / 3, j = a - 3 * i;
-    double u[3], w[3];
-#pragma unroll
-    for (int k = 0; k < 3; k++) {
-      u[k] = i == 0 ? e0[k] : (i == 1 ? e1[k] : e2[k]);
-      w[k] = j == 0 ? f0[k] : (j == 1 ? f1[k] : f2[k]);
-    }
-    crossT(u, w, ax);
-    axis_gaps(ax, t, g1, g2);
-    g = fmax(g1, g2);
-    if (g > 0.0 && g * g > rr * dotT(ax, ax)) return true;
-  }
-  return false;
-}
-
 // Exact restatement (fp64, reference operation order) -> true iff no axis separates.
 __device__ __noinline__ bool sat17_exact(const Tri6<double>& t) {
   double e1[3] = {t.p2[0], t.p2[1], t.p2[2]};                                  // p2 - p1
@@ -289,6 +260,85 @@ __device__ __forceinline__ int sat17_filter(const Tri6<float>& t) {
   return unsure ? 2 : 1;
 }
 
+// Edge vectors of both triangles and the a-th of the 11 "quadratic" axes (0: n1 = e1 x e2, 1: m1 = f1 x f2,
+// 2 + 3 i + j: e_i x f_j -- the order of intersect-inl.h:745-777), operands picked with selects.
+struct TriEdgesF {
+  float e[3][3], f[3][3];
+  __device__ __forceinline__ void set(const Tri6<float>& t) {
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+      e[0][k] = t.p2[k]; e[1][k] = t.p3[k] - t.p2[k]; e[2][k] = -t.p3[k];
+      f[0][k] = t.q2[k] - t.q1[k]; f[1][k] = t.q3[k] - t.q2[k]; f[2][k] = t.q1[k] - t.q3[k];
+    }
+  }
+  __device__ __forceinline__ void axis(unsigned a, float* ax) const {
+    const unsigned b = a >= 2u ? a - 2u : 0u;
+    const unsigned i = b / 3u, j = b - 3u * i;
+    float u[3], w[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+      const float ei = i == 0 ? e[0][k] : (i == 1 ? e[1][k] : e[2][k]);
+      const float fj = j == 0 ? f[0][k] : (j == 1 ? f[1][k] : f[2][k]);
+      u[k] = a == 0 ? e[0][k] : (a == 1 ? f[0][k] : ei);
+      w[k] = a == 0 ? e[1][k] : (a == 1 ? f[1][k] : fj);
+    }
+    crossT(u, w, ax);
+  }
+};
+
+// Swept windows of K2, fp32: true when one of the 11 quadratic axes separates the two triangles by MORE than r.
+// The triangles are the fp64 values rounded to fp32; whatever direction the rounded cross product has, it is a
+// valid direction to project on, so only the projections carry error: each within 7 u L |axis| of the exact one
+// (input rounding + three products and two sums), the gap within 18 u L |axis| -- r is raised by 32 u L.  A pair
+// that is not certainly clear is simply not clear (conservative; nothing is re-tested in fp64).  On `false`, best =
+// the axis whose gap at this pose is largest relative to its length (15: no axis separates here) -- the first axis
+// worth testing at the neighbouring poses (test_kept_pairs).
+__device__ __noinline__ bool tri_gap_clear_f(const Tri6<float>& t, float r, unsigned& best) {
+  float L = 0.f;
+#pragma unroll
+  for (int k = 0; k < 3; k++) {
+    L = fmaxf(L, fmaxf(fabsf(t.p2[k]), fabsf(t.p3[k])));
+    L = fmaxf(L, fmaxf(fabsf(t.q1[k]), fmaxf(fabsf(t.q2[k]), fabsf(t.q3[k]))));
+  }
+  const float rp = r + 32.f * 5.9604645e-08f * L;
+  const float rr = rp * rp * 1.00001f;
+  TriEdgesF E;
+  E.set(t);
+  float best_g2 = 0.f, best_n2 = 1.f;
+  best = 15u;
+#pragma unroll 1
+  for (unsigned a = 0; a < 11u; a++) {
+    float ax[3], g1, g2;
+    E.axis(a, ax);
+    axis_gaps(ax, t, g1, g2);
+    const float g = fmaxf(g1, g2), n2 = dotT(ax, ax);
+    if (g > 0.f && n2 > 1e-30f) {
+      const float gg = g * g;
+      if (gg > rr * n2) return true;
+      if (gg * best_n2 > best_g2 * n2) { best_g2 = gg; best_n2 = n2; best = a; }
+    }
+  }
+  return false;
+}
+
+// One axis of the fp32 filter: true when quadratic axis a certainly separates (same arithmetic and bound as
+// sat17_filter for that axis, so the exact fp64 SAT-17 finds the same axis separating and reports "disjoint").
+__device__ __forceinline__ bool sat17_axis_separates(const Tri6<float>& t, unsigned a) {
+  float L = 0.f;
+#pragma unroll
+  for (int k = 0; k < 3; k++) {
+    L = fmaxf(L, fmaxf(fabsf(t.p2[k]), fabsf(t.p3[k])));
+    L = fmaxf(L, fmaxf(fabsf(t.q1[k]), fmaxf(fabsf(t.q2[k]), fabsf(t.q3[k]))));
+  }
+  const float Eq = 640.f * 5.9604645e-08f * L * L * L + 1e-37f;
+  TriEdgesF E;
+  E.set(t);
+  float ax[3], g1, g2;
+  E.axis(a, ax);
+  axis_gaps(ax, t, g1, g2);
+  return (g1 > Eq) | (g2 > Eq);
+}
+
 // Robot triangle into the env frame with the reference's operation order
 // (intersect-inl.h:598-617: Q' = R*Q + T; then :738-743 everything minus P1).
 __device__ __forceinline__ void load_pair_exact(const double* __restrict__ P, const double* __restrict__ Q,
@@ -339,6 +389,9 @@ struct WarpCtx {
   int nspill;
   unsigned n_bv, n_leaf, n_fp64, n_spill;
   bool overflow;
+  int nsurv;       // MODE_SWEPT_KEEP: pairs kept for window keep_win (the first surv_limit of them are in WarpShared::surv)
+  int surv_limit;  // ... pairs the window may keep before it counts as blocked (<= SURV_CAP)
+  int keep_win;    // ... the earliest window that kept a pair (32: none)
 };
 
 __device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }
@@ -353,7 +406,7 @@ struct ContactRec {
 
 __device__ __forceinline__ unsigned contact_multiplicity_dev(const double* P, const double* Q, const double* Rd);
 
-enum { MODE_VALID = 0, MODE_SEGMENT = 1, MODE_CONTACTS = 2, MODE_SWEPT = 3 };
+enum { MODE_VALID = 0, MODE_SEGMENT = 1, MODE_CONTACTS = 2, MODE_SWEPT = 3, MODE_SWEPT_KEEP = 4 };
 
 // alive: bit p set = pose p takes part.  Returns the mask of poses with at least one
 // intersecting triangle pair.  MODE_SEGMENT: once pose p hits, poses >= p are abandoned (only
@@ -361,7 +414,13 @@ enum { MODE_VALID = 0, MODE_SEGMENT = 1, MODE_CONTACTS = 2, MODE_SWEPT = 3 };
 // intersecting pair is appended to `recs`.  MODE_SWEPT: the poses are the mid poses of consecutive windows of a
 // segment walk, S.eta carries each window's swept radius (boxes) and S.tau the radius itself (triangles); a pose
 // "hits" as soon as one triangle pair is NOT separated by more than the radius along one of its 11 face / edge-edge
-// axes, and then it and all later windows are abandoned.
+// axes, and then it and all later windows are abandoned.  MODE_SWEPT_KEEP: the EARLIEST window with such pairs is
+// not blocked by them: they are KEPT (WarpShared::surv) so that the caller can run the exact predicate on them at
+// every step of that window.  Every triangle pair that intersects at some step of a window is among the pairs kept
+// for it (it lies within the window's radius of intersecting at the mid pose), so those tests decide each step of
+// the window without another traversal.  The windows behind the keeping one are blocked (the walk will be at a
+// contact or needs a fresh traversal there anyway); the keeping window itself blocks only when it keeps more than
+// C.surv_limit pairs.
 template <int MODE>
 __device__ __forceinline__ unsigned traverse_tile(const KParams& P, WarpShared& S, WarpCtx& C, unsigned alive,
                                                   int lane, int state_base = 0, ContactRec* recs = nullptr,
@@ -398,8 +457,19 @@ __device__ __forceinline__ unsigned traverse_tile(const KParams& P, WarpShared& 
         const double* tq = P.rob.tris + (size_t)9 * entry_n2(e);
         Tri6<double> td;
         load_pair_exact(tp, tq, &S.Rd[0][pose], td);
-        if (MODE == MODE_SWEPT) hit = !tri_gap_clear(td, S.tau[pose]);
-        else hit = tri_pair_intersect(td, C.n_fp64);
+        if (MODE == MODE_SWEPT || MODE == MODE_SWEPT_KEEP) {
+          Tri6<float> tf;
+#pragma unroll
+          for (int k = 0; k < 3; k++) {
+            tf.p2[k] = (float)td.p2[k]; tf.p3[k] = (float)td.p3[k];
+            tf.q1[k] = (float)td.q1[k]; tf.q2[k] = (float)td.q2[k]; tf.q3[k] = (float)td.q3[k];
+          }
+          unsigned best;
+          hit = !tri_gap_clear_f(tf, __double2float_ru(S.tau[pose]), best);
+          if (MODE == MODE_SWEPT_KEEP) e |= (unsigned long long)best << 28;   // triangle ids stay below 2^27
+        } else {
+          hit = tri_pair_intersect(td, C.n_fp64);
+        }
         if (MODE == MODE_CONTACTS && hit) {
           unsigned long long slot = atomicAdd(rec_count, 1ull);
           if (slot < rec_cap) {
@@ -412,17 +482,35 @@ __device__ __forceinline__ unsigned traverse_tile(const KParams& P, WarpShared& 
           }
         }
       }
-      unsigned hm = __reduce_or_sync(FULL, hit ? (1u << pose) : 0u);
+      unsigned hm;
+      if (MODE == MODE_SWEPT_KEEP) {
+        hm = 0;
+        if (__any_sync(FULL, hit)) {
+          const int pmin = __reduce_min_sync(FULL, hit ? (int)pose : 32);
+          if (pmin < C.keep_win) { C.keep_win = pmin; C.nsurv = 0; }   // an earlier window takes over the list
+          const bool mine = hit && (int)pose == C.keep_win;
+          const unsigned mm = __ballot_sync(FULL, mine);
+          if (mine) {
+            const int pos = C.nsurv + __popc(mm & ltmask);
+            if (pos < C.surv_limit) S.surv[pos] = e;
+          }
+          C.nsurv += __popc(mm);
+          if (C.nsurv > C.surv_limit) hm = 1u << C.keep_win;       // too many pairs to test one by one
+          else if (C.keep_win < 31) hm = 2u << C.keep_win;
+        }
+      } else {
+        hm = __reduce_or_sync(FULL, hit ? (1u << pose) : 0u);
+      }
       hits |= hm;
       if (MODE == MODE_VALID) dead |= hm;
-      else if (MODE == MODE_SEGMENT || MODE == MODE_SWEPT) { if (hm) dead |= FULL << (__ffs(hm) - 1); }
+      else if (MODE == MODE_SEGMENT || MODE == MODE_SWEPT || MODE == MODE_SWEPT_KEEP) { if (hm) dead |= FULL << (__ffs(hm) - 1); }
       __syncwarp();
-      if (MODE == MODE_SWEPT && (dead & alive) == alive) { C.nspill = 0; break; }   // every window abandoned
+      if ((MODE == MODE_SWEPT || MODE == MODE_SWEPT_KEEP) && (dead & alive) == alive) { C.nspill = 0; break; }   // every window abandoned
       continue;
     }
     if (top > STACK_CAP - 32) {  // make room: move the oldest entries to global memory
       if (C.nspill + SPILL_CHUNK > C.spill_cap) {
-        if (MODE == MODE_SWEPT) { hits = alive; C.nspill = 0; break; }   // no room: nothing proven, every window blocked
+        if (MODE == MODE_SWEPT || MODE == MODE_SWEPT_KEEP) { hits = alive; C.nspill = 0; break; }   // no room: nothing proven, every window blocked
         C.overflow = true;
         break;
       }
@@ -508,6 +596,9 @@ __device__ __forceinline__ void ctx_init(const KParams& P, WarpCtx& C) {
   C.nspill = 0;
   C.n_bv = C.n_leaf = C.n_fp64 = C.n_spill = 0;
   C.overflow = false;
+  C.nsurv = 0;
+  C.surv_limit = 0;
+  C.keep_win = 32;
 }
 __device__ __forceinline__ void ctx_flush(const KParams& P, WarpCtx& C, unsigned long long poses, int lane) {
   unsigned bv = __reduce_add_sync(FULL, C.n_bv), lf = __reduce_add_sync(FULL, C.n_leaf),
@@ -577,6 +668,44 @@ struct SegOut {
   double* touch_tau;   // [n] or null
   long long* steps;    // [n] or null
 };
+
+// ---------------------------------------------------------------------------------------------
+// Swept windows that keep pairs (MODE_SWEPT_KEEP): helpers of k_transit.
+// ---------------------------------------------------------------------------------------------
+// Exact SAT-17 of the ncur kept pairs (S.surv) at each of the 2^cs_log2 step poses of the current chunk (pose slot p =
+// step p; `alive` = slots that hold a step).  Work item i = pair (i >> cs_log2) at pose (i & (cs - 1)), 32 items per
+// pass, so a 4-step window still fills the warp.  Returns the mask of steps with an intersecting pair; steps behind
+// a known hit are not tested (only the first colliding step matters, unit_world.cc:452-458).
+__device__ __forceinline__ unsigned test_kept_pairs(const KParams& P, WarpShared& S, WarpCtx& C, int ncur, int cs_log2,
+                                                    unsigned alive, int lane) {
+  unsigned hits = 0;
+  const int total = ncur << cs_log2;
+  const unsigned cmask = (1u << cs_log2) - 1u;
+  for (int base = 0; base < total; base += 32) {
+    const int i = base + lane;
+    const unsigned pose = (unsigned)i & cmask;
+    const bool act = i < total && (alive >> pose & 1u) && !(hits & (0xffffffffu >> (31u - pose)));
+    bool hit = false;
+    if (act) {
+      C.n_leaf++;
+      const unsigned long long e = S.surv[i >> cs_log2];
+      const unsigned axis = ((unsigned)e >> 28) & 15u;
+      Tri6<double> td;
+      load_pair_exact(P.env.tris + (size_t)9 * (entry_n1(e) & 0x0fffffffu), P.rob.tris + (size_t)9 * entry_n2(e),
+                      &S.Rd[0][pose], td);
+      // the axis that separated the pair best at the window's mid pose usually still separates it at this step
+      Tri6<float> tf;
+#pragma unroll
+      for (int k = 0; k < 3; k++) {
+        tf.p2[k] = (float)td.p2[k]; tf.p3[k] = (float)td.p3[k];
+        tf.q1[k] = (float)td.q1[k]; tf.q2[k] = (float)td.q2[k]; tf.q3[k] = (float)td.q3[k];
+      }
+      if (!(axis < 11u && sat17_axis_separates(tf, axis))) hit = tri_pair_intersect(td, C.n_fp64);
+    }
+    hits |= __reduce_or_sync(FULL, hit ? (1u << pose) : 0u);
+  }
+  return hits;
+}
 
 // transition_mode: vd := min(dist/2, vd) (isValidTransition)
 template <int MINB>  // resident blocks per SM the register allocation is capped for
@@ -649,8 +778,43 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB)
       int nb = 4;                  // windows per traversal
       int fails = 0;
       bool exact_next = false;     // the next tile is known not to clear
+      // What the last swept traversal left to consume, in walk order: pend_clear windows of pws steps that kept no
+      // pair (free: stepped over), then, if pend_keep, one window whose steps are decided by the exact predicate on
+      // exactly the pairs it kept (res_left = its steps still to decide, ncur = its pairs in S.surv).
+      int pend_clear = 0, pws = 0, res_left = 0, ncur = 0;
+      bool pend_keep = false;
       while (!done) {
-        if (ws > 0 && !exact_next && (fails < 1 || ((k0 >> 5) & 7) == 0)) {
+        int exact_n;
+        bool listed = false;
+        if (res_left > 0) {
+          exact_n = min(32, res_left);
+          listed = true;
+        } else if (pend_clear > 0) {
+          const int ns = pend_clear * pws;
+          pend_clear = 0;
+          double d = carry, last = carry;
+          const int valid = advance_chain(d, vd, dist, ns, last);   // the reference's running sum, rounding included
+          carry = d;
+          nposes += valid;
+          k0 += valid;
+          if (valid > 0) prev_tau = last * inv_dist;
+          if (valid < ns) {  // walked past dist: the whole segment is free
+            free_tau = prev_tau;
+            touch_tau = 0.0;
+            interpolate(a, b, prev_tau, lf);
+#pragma unroll
+            for (int k = 0; k < 7; k++) fh[k] = lf[k];
+            steps = k0;
+            free_flag = true;
+            done = true;
+          }
+          continue;
+        } else if (pend_keep) {
+          pend_keep = false;
+          ncur = C.nsurv;
+          res_left = pws;
+          continue;
+        } else if (ws > 0 && !exact_next && (fails < 1 || ((k0 >> 5) & 7) == 0)) {
           // window `lane` holds the steps whose delta lies in (carry + lane w, carry + (lane + 1) w], w = ws vd,
           // up to the rounding of the running sum (< 1e-6 relative to w for any vd/dist >= 1e-9)
           const double w = (double)ws * vd;
@@ -667,52 +831,52 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB)
             S.eta[lane] = __fadd_ru(S.eta[lane], __double2float_ru(0.5 * radius));
             S.tau[lane] = radius;   // triangle-level test of the window (the exact path rewrites tau)
           }
+          C.nsurv = 0;
+          C.keep_win = 32;
+          // pairs are kept only by windows of small radius: a wide window near a contact keeps so many pairs that
+          // walking its steps exactly is cheaper than listing and testing them
+          C.surv_limit = (double)ws * step_radius <= P.sweep_keep_rmax ? min(SURV_CAP, P.sweep_resolve / ws) : 0;
           const unsigned tried = __ballot_sync(FULL, mine_w);   // a prefix of the lanes
           __syncwarp();
           if (tried == 0) { exact_next = true; continue; }      // cannot happen for finite inputs; never spin
-          const unsigned blocked = traverse_tile<MODE_SWEPT>(P, S, C, tried, lane);
+          const unsigned blocked = traverse_tile<MODE_SWEPT_KEEP>(P, S, C, tried, lane);
           if (C.overflow) { done = true; break; }
           __syncwarp();
           const int ntried = __popc(tried);
-          const int cleared = blocked ? __ffs(blocked) - 1 : ntried;
-          if (cleared > 0) {
-            const int ns = cleared * ws;
-            double d = carry, last = carry;
-            const int valid = advance_chain(d, vd, dist, ns, last);   // the reference's running sum, rounding included
-            carry = d;
-            nposes += valid;
-            k0 += valid;
-            if (valid > 0) prev_tau = last * inv_dist;
-            if (valid < ns) {  // walked past dist: the whole segment is free
-              free_tau = prev_tau;
-              touch_tau = 0.0;
-              interpolate(a, b, prev_tau, lf);
-#pragma unroll
-              for (int k = 0; k < 7; k++) fh[k] = lf[k];
-              steps = k0;
-              free_flag = true;
-              done = true;
-              continue;
-            }
+          const int first_blocked = blocked ? min(ntried, __ffs(blocked) - 1) : ntried;
+          pend_keep = C.keep_win < first_blocked;      // that window kept at most surv_limit pairs, all of them listed
+          pend_clear = pend_keep ? C.keep_win : first_blocked;
+          pws = ws;
+#ifdef OSR_K2_TRACE
+          {
+            const unsigned tb = __reduce_add_sync(FULL, C.n_bv), tl = __reduce_add_sync(FULL, C.n_leaf);
+            if (lane == 0 && seg < 48)
+              printf("seg %d k0 %lld sweep ws %d nb %d tried %d blocked_at %d keep_win %d kept %d | bv %u leaf %u\n", (int)seg, k0, ws, nb,
+                     ntried, first_blocked, C.keep_win, C.nsurv, tb, tl);
           }
-          if (!blocked) {            // everything tried cleared: widen
+#endif
+          if (pend_keep) {           // near a contact: one window per traversal until windows clear again
+            fails = 0;
+            nb = 1;
+          } else if (first_blocked == ntried) {   // everything cleared: widen
             fails = 0;
             if (nb < 32) nb *= 2;
             else if (2 * ws <= ws_cap) ws *= 2;
           } else if (ws > 4) {       // split the blocked window
             ws >>= 1;
             nb = 2;
-          } else {                   // four steps that do not clear: walk the tile step by step
+          } else {                   // four steps with too many pairs to list: walk the tile step by step
             exact_next = true;
             nb = 2;
-            if (cleared == 0) fails++;
+            if (first_blocked == 0) fails++;
           }
           continue;
+        } else {
+          // a tile entered because four steps did not clear is short: the contact is expected within them, and every
+          // pose traversed beyond the first hit is wasted
+          exact_n = exact_next ? P.sweep_short_tile : 32;
+          exact_next = false;
         }
-        // a tile entered because four steps did not clear is short: the contact is expected within them, and every
-        // pose traversed beyond the first hit is wasted
-        const int exact_n = exact_next ? P.sweep_short_tile : 32;
-        exact_next = false;
         // step deltas of this tile: lane j takes the (j+1)-th value after `carry`.  The chain of fp64 adds is
         // inherently serial (the reference's running sum, rounding included), so all lanes run it; it is kept to
         // add / compare / select per step: with carry = 0 the first value is 0 + vd = vd exactly, and since the
@@ -735,9 +899,23 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB)
         }
         unsigned alive = __ballot_sync(FULL, mine_ok);
         __syncwarp();
-        unsigned hits = traverse_tile<MODE_SEGMENT>(P, S, C, alive, lane);
+        unsigned hits;
+        if (listed) {
+          hits = test_kept_pairs(P, S, C, ncur, 31 - __clz(exact_n), alive, lane);
+          res_left -= exact_n;
+        } else {
+          hits = traverse_tile<MODE_SEGMENT>(P, S, C, alive, lane);
+        }
         if (C.overflow) { done = true; break; }
         int nalive = __popc(alive);
+#ifdef OSR_K2_TRACE
+        {
+          const unsigned tb = __reduce_add_sync(FULL, C.n_bv), tl = __reduce_add_sync(FULL, C.n_leaf), t64 = __reduce_add_sync(FULL, C.n_fp64);
+          if (lane == 0 && seg < 48)
+            printf("seg %d k0 %lld %s n %d ncur %d alive %d hits %08x | bv %u leaf %u fp64 %u\n", (int)seg, k0, listed ? "listed" : "exact",
+                   exact_n, listed ? ncur : -1, nalive, hits, tb, tl, t64);
+        }
+#endif
         if (hits) {
           int j = __ffs(hits) - 1;
           nposes += j + 1;

@@ -18,7 +18,7 @@ uw.loadModelFromFile(os.path.join(A, envf)); uw.loadRobotFromFile(os.path.join(A
 uw.scaleToUnit(); uw.angleModel(0.0, 0.0)
 q0 = W.random_states(1 << 16, seed=0)
 ok = uw.is_valid_states(q0) & ~uw.is_disentangled_states(q0)
-fr, to = W.touch_rays(q0[ok][:1024], 65536, seed=1)
+fr, to = W.touch_rays(q0[ok][:1024], int(os.environ.get("TOUCH_N", "65536")), seed=1)
 uw.transit_states_to_with_contact(fr, to, 0.0125 / 8)
 uw.counters(reset=True)
 t = time.perf_counter()
