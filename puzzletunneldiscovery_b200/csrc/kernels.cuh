@@ -55,7 +55,10 @@ struct KParams {
   double sweep_keep_rmax;            // K2: ... and only windows whose swept radius stays below this keep pairs at all
 };
 
-constexpr int STACK_CAP = 512;   // shared-memory stack entries per warp
+#ifndef OSR_STACK_CAP
+#define OSR_STACK_CAP 512
+#endif
+constexpr int STACK_CAP = OSR_STACK_CAP;   // shared-memory stack entries per warp
 constexpr int SPILL_CHUNK = 256; // entries moved per spill / refill
 constexpr unsigned FULL = 0xffffffffu;
 // K2: most triangle pairs a swept traversal keeps for exact per-step tests of one window.  Kept small: shared memory
@@ -70,6 +73,8 @@ struct __align__(16) WarpShared {
   float Rf[12][32];   // same rounded to fp32
   float eta[32];      // per-pose absolute inflation of box extents
   double tau[32];     // segment walk: tau of each step in the tile
+  double seg[14];     // K2: end states of the segment the warp walks (from, to) -- warp-uniform, kept out of registers
+  double envtf[12];   // K2: environment transform (R row-major, t)
 };
 
 __device__ __forceinline__ unsigned long long make_entry(unsigned pose, unsigned n1, unsigned n2) {
@@ -364,20 +369,18 @@ __device__ __forceinline__ void load_pair_exact(const double* __restrict__ P, co
   }
 }
 
-// returns true iff the fp64 SAT-17 reports an intersection
-__device__ __forceinline__ bool tri_pair_intersect(const Tri6<double>& td, unsigned& n_recheck) {
+// bit 0: the fp64 SAT-17 reports an intersection; bit 1: the fp32 filter left the pair open and fp64 decided.
+// One copy per kernel (noinline): the predicate is ~700 instructions and has several callers.
+__device__ __noinline__ int tri_pair_intersect(const Tri6<double>& td) {
   Tri6<float> tf;
 #pragma unroll
   for (int k = 0; k < 3; k++) {
     tf.p2[k] = (float)td.p2[k]; tf.p3[k] = (float)td.p3[k];
     tf.q1[k] = (float)td.q1[k]; tf.q2[k] = (float)td.q2[k]; tf.q3[k] = (float)td.q3[k];
   }
-  int r = sat17_filter(tf);
-  if (r == 2) {
-    n_recheck++;
-    return sat17_exact(td);
-  }
-  return r == 1;
+  const int r = sat17_filter(tf);
+  if (r == 2) return 2 | (sat17_exact(td) ? 1 : 0);
+  return r;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -406,7 +409,9 @@ struct ContactRec {
 
 __device__ __forceinline__ unsigned contact_multiplicity_dev(const double* P, const double* Q, const double* Rd);
 
-enum { MODE_VALID = 0, MODE_SEGMENT = 1, MODE_CONTACTS = 2, MODE_SWEPT = 3, MODE_SWEPT_KEEP = 4 };
+// MODE_RT: MODE_SEGMENT or MODE_SWEPT_KEEP, chosen at run time (`rmode`), so that k_transit holds ONE copy of the
+// traversal loop (its instruction working set has to stay inside the instruction cache shared by the SM's warps).
+enum { MODE_VALID = 0, MODE_SEGMENT = 1, MODE_CONTACTS = 2, MODE_SWEPT = 3, MODE_SWEPT_KEEP = 4, MODE_RT = 5 };
 
 // alive: bit p set = pose p takes part.  Returns the mask of poses with at least one
 // intersecting triangle pair.  MODE_SEGMENT: once pose p hits, poses >= p are abandoned (only
@@ -425,7 +430,10 @@ template <int MODE>
 __device__ __forceinline__ unsigned traverse_tile(const KParams& P, WarpShared& S, WarpCtx& C, unsigned alive,
                                                   int lane, int state_base = 0, ContactRec* recs = nullptr,
                                                   unsigned long long* rec_count = nullptr,
-                                                  unsigned long long rec_cap = 0) {
+                                                  unsigned long long rec_cap = 0, int rmode = MODE_SEGMENT) {
+  const bool m_keep = MODE == MODE_RT ? rmode == MODE_SWEPT_KEEP : MODE == MODE_SWEPT_KEEP;
+  const bool m_swept = m_keep || MODE == MODE_SWEPT;
+  const bool m_segment = MODE == MODE_RT ? rmode == MODE_SEGMENT : MODE == MODE_SEGMENT;
   const unsigned ltmask = (1u << lane) - 1u;
   unsigned dead = ~alive;
   unsigned hits = 0;
@@ -457,7 +465,7 @@ __device__ __forceinline__ unsigned traverse_tile(const KParams& P, WarpShared& 
         const double* tq = P.rob.tris + (size_t)9 * entry_n2(e);
         Tri6<double> td;
         load_pair_exact(tp, tq, &S.Rd[0][pose], td);
-        if (MODE == MODE_SWEPT || MODE == MODE_SWEPT_KEEP) {
+        if (m_swept) {
           Tri6<float> tf;
 #pragma unroll
           for (int k = 0; k < 3; k++) {
@@ -466,9 +474,11 @@ __device__ __forceinline__ unsigned traverse_tile(const KParams& P, WarpShared& 
           }
           unsigned best;
           hit = !tri_gap_clear_f(tf, __double2float_ru(S.tau[pose]), best);
-          if (MODE == MODE_SWEPT_KEEP) e |= (unsigned long long)best << 28;   // triangle ids stay below 2^27
+          if (m_keep) e |= (unsigned long long)best << 28;   // triangle ids stay below 2^27
         } else {
-          hit = tri_pair_intersect(td, C.n_fp64);
+          const int r = tri_pair_intersect(td);
+          hit = (r & 1) != 0;
+          C.n_fp64 += (unsigned)r >> 1;
         }
         if (MODE == MODE_CONTACTS && hit) {
           unsigned long long slot = atomicAdd(rec_count, 1ull);
@@ -483,7 +493,7 @@ __device__ __forceinline__ unsigned traverse_tile(const KParams& P, WarpShared& 
         }
       }
       unsigned hm;
-      if (MODE == MODE_SWEPT_KEEP) {
+      if (m_keep) {
         hm = 0;
         if (__any_sync(FULL, hit)) {
           const int pmin = __reduce_min_sync(FULL, hit ? (int)pose : 32);
@@ -503,14 +513,14 @@ __device__ __forceinline__ unsigned traverse_tile(const KParams& P, WarpShared& 
       }
       hits |= hm;
       if (MODE == MODE_VALID) dead |= hm;
-      else if (MODE == MODE_SEGMENT || MODE == MODE_SWEPT || MODE == MODE_SWEPT_KEEP) { if (hm) dead |= FULL << (__ffs(hm) - 1); }
+      else if (m_segment || m_swept) { if (hm) dead |= FULL << (__ffs(hm) - 1); }
       __syncwarp();
-      if ((MODE == MODE_SWEPT || MODE == MODE_SWEPT_KEEP) && (dead & alive) == alive) { C.nspill = 0; break; }   // every window abandoned
+      if (m_swept && (dead & alive) == alive) { C.nspill = 0; break; }   // every window abandoned
       continue;
     }
     if (top > STACK_CAP - 32) {  // make room: move the oldest entries to global memory
       if (C.nspill + SPILL_CHUNK > C.spill_cap) {
-        if (MODE == MODE_SWEPT || MODE == MODE_SWEPT_KEEP) { hits = alive; C.nspill = 0; break; }   // no room: nothing proven, every window blocked
+        if (m_swept) { hits = alive; C.nspill = 0; break; }   // no room: nothing proven, every window blocked
         C.overflow = true;
         break;
       }
@@ -700,11 +710,56 @@ __device__ __forceinline__ unsigned test_kept_pairs(const KParams& P, WarpShared
         tf.p2[k] = (float)td.p2[k]; tf.p3[k] = (float)td.p3[k];
         tf.q1[k] = (float)td.q1[k]; tf.q2[k] = (float)td.q2[k]; tf.q3[k] = (float)td.q3[k];
       }
-      if (!(axis < 11u && sat17_axis_separates(tf, axis))) hit = tri_pair_intersect(td, C.n_fp64);
+      if (!(axis < 11u && sat17_axis_separates(tf, axis))) {
+        const int r = tri_pair_intersect(td);
+        hit = (r & 1) != 0;
+        C.n_fp64 += (unsigned)r >> 1;
+      }
     }
     hits |= __reduce_or_sync(FULL, hit ? (1u << pose) : 0u);
   }
   return hits;
+}
+
+// Pose slot `slot` := the walk's state at tau (osr::interpolate of the segment in S.seg) as the traversal wants it
+// (robot in the environment frame, fp64 + fp32 + box slack).  One copy per kernel: the slerp is ~400 instructions.
+__device__ __noinline__ void seg_pose_at(int slot, double tau) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  WarpShared& S = reinterpret_cast<WarpShared*>(smem_raw)[threadIdx.x >> 5];
+  double a[7], b[7], s[7];
+#pragma unroll
+  for (int k = 0; k < 7; k++) { a[k] = S.seg[k]; b[k] = S.seg[7 + k]; }
+  interpolate(a, b, tau, s);
+  Rigid env, rob, rel;
+#pragma unroll
+  for (int k = 0; k < 9; k++) env.R[k] = S.envtf[k];
+#pragma unroll
+  for (int k = 0; k < 3; k++) env.t[k] = S.envtf[9 + k];
+  state_to_rigid(s, rob);
+  relative_rigid(env, rob, rel);
+#pragma unroll
+  for (int k = 0; k < 9; k++) { S.Rd[k][slot] = rel.R[k]; S.Rf[k][slot] = (float)rel.R[k]; }
+#pragma unroll
+  for (int k = 0; k < 3; k++) { S.Rd[9 + k][slot] = rel.t[k]; S.Rf[9 + k][slot] = (float)rel.t[k]; }
+  S.eta[slot] = 2e-5f * (1.0f + fabsf((float)rel.t[0]) + fabsf((float)rel.t[1]) + fabsf((float)rel.t[2]));
+}
+
+// One output state of a segment, written by lanes 0..6: which = 0 the `from` state, 1 the `to` state, 2 the walk's
+// state at tau.
+__device__ __noinline__ void seg_write_state(double* __restrict__ dst, int which, double tau, int lane) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  WarpShared& S = reinterpret_cast<WarpShared*>(smem_raw)[threadIdx.x >> 5];
+  double a[7], b[7], s[7];
+#pragma unroll
+  for (int k = 0; k < 7; k++) { a[k] = S.seg[k]; b[k] = S.seg[7 + k]; }
+  if (which == 2) interpolate(a, b, tau, s);
+  double v = 0.0;
+#pragma unroll
+  for (int k = 0; k < 7; k++) {
+    const double x = which == 0 ? a[k] : (which == 1 ? b[k] : s[k]);
+    if (k == lane) v = x;
+  }
+  if (lane < 7) dst[lane] = v;
 }
 
 // transition_mode: vd := min(dist/2, vd) (isValidTransition)
@@ -718,33 +773,44 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB)
   const int lane = threadIdx.x & 31;
   WarpCtx C;
   ctx_init(P, C);
+  if (lane < 9) S.envtf[lane] = P.env_tf.R[lane];
+  else if (lane < 12) S.envtf[lane] = P.env_tf.t[lane - 9];
   unsigned long long nposes = 0;
+  enum { ST_FROM = 0, ST_TO = 1, ST_TAU = 2 };
+  enum { ACT_SWEEP = 0, ACT_EXACT = 1, ACT_LISTED = 2 };
   while (true) {
     unsigned long long seg = 0;
     if (lane == 0) seg = atomicAdd(P.work_counter, 1ull);
     seg = __shfl_sync(FULL, seg, 0);
     if ((long long)seg >= n) break;
-    double a[7], b[7];
-#pragma unroll
-    for (int k = 0; k < 7; k++) { a[k] = __ldg(from + 7 * seg + k); b[k] = __ldg(to + 7 * seg + k); }
+    __syncwarp();
+    if (lane < 7) { S.seg[lane] = __ldg(from + 7 * seg + lane); S.seg[7 + lane] = __ldg(to + 7 * seg + lane); }
+    __syncwarp();
     double vd = vd_arr ? __ldg(vd_arr + (vd_count > 1 ? seg : 0)) : vd_scalar;
-    const double dist = distance(a, b);
+    double dist, trans;
+    {
+      double a[7], b[7];
+#pragma unroll
+      for (int k = 0; k < 7; k++) { a[k] = S.seg[k]; b[k] = S.seg[7 + k]; }
+      dist = distance(a, b);
+      const double tdx = a[0] - b[0], tdy = a[1] - b[1], tdz = a[2] - b[2];
+      trans = sqrt(tdx * tdx + tdy * tdy + tdz * tdz);
+    }
     if (transition_mode) vd = fmin(dist / 2.0, vd);
-    // results (warp-uniform)
+    // results (warp-uniform).  The two output states are produced at the end from (which, tau): last_free is `from`
+    // until a step has been proven free, first_hit is `to` unless the walk says otherwise.
     bool free_flag = false;
     double free_tau = 0.0, touch_tau = 1.0;
     long long steps = 0;
-    double lf[7], fh[7];
-#pragma unroll
-    for (int k = 0; k < 7; k++) { lf[k] = a[k]; fh[k] = b[k]; }
+    int lf_which = ST_FROM, fh_which = ST_TO;
+    double lf_tau = 0.0, fh_tau = 0.0;
     // A NaN distance or verify_delta fails both `verify_delta >= dist` and `delta <= dist` of the reference
     // (unit_world.cc:443-447): its loop body never runs and it returns (from, from, false, 0, 0).  With
     // verify_delta <= 0 the reference's walk never ends; here that is an argument error (error flag 3, same tuple).
     const bool nan_walk = !(dist == dist) || !(vd == vd);
     const bool bad_vd = !nan_walk && !(vd >= dist) && !(vd > 0.0);
     if (nan_walk || bad_vd) {
-#pragma unroll
-      for (int k = 0; k < 7; k++) fh[k] = a[k];
+      fh_which = ST_FROM;
       touch_tau = 0.0;
       if (bad_vd && lane == 0) atomicExch(P.error_flag, 3);
     } else if (!(vd >= dist)) {
@@ -760,10 +826,8 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB)
       // overlaps at the window's mid pose with the boxes grown by the window's radius, no triangle pair can
       // intersect at any step of the window (triangles lie inside their leaf boxes), so the reference's per-step
       // checks (unit_world.cc:445-470) all say "free" and the walk advances over the window without traversing
-      // its steps.  A window that does not clear proves nothing: it is split, and single tiles are walked exactly.
+      // its steps.  A window that does not clear is split, decided from the pairs it kept, or walked exactly.
       // One traversal tests up to 32 consecutive windows (one per pose slot, lane-parallel over box pairs).
-      const double tdx = a[0] - b[0], tdy = a[1] - b[1], tdz = a[2] - b[2];
-      const double trans = sqrt(tdx * tdx + tdy * tdy + tdz * tdz);
       const double rate = (trans + (fmax(dist - trans, 0.0) + 1e-12) * P.rob_radius) * (1.0 + 1e-9);
       // steps per window (a power of two >= 4): never wider than the window whose radius reaches sweep_rmax (a
       // robot grown by more is not expected to clear anything), starts where the radius is sweep_rstart,
@@ -784,11 +848,10 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB)
       int pend_clear = 0, pws = 0, res_left = 0, ncur = 0;
       bool pend_keep = false;
       while (!done) {
-        int exact_n;
-        bool listed = false;
+        int act, exact_n = 0;
         if (res_left > 0) {
+          act = ACT_LISTED;
           exact_n = min(32, res_left);
-          listed = true;
         } else if (pend_clear > 0) {
           const int ns = pend_clear * pws;
           pend_clear = 0;
@@ -800,10 +863,9 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB)
           if (valid > 0) prev_tau = last * inv_dist;
           if (valid < ns) {  // walked past dist: the whole segment is free
             free_tau = prev_tau;
-            touch_tau = 0.0;
-            interpolate(a, b, prev_tau, lf);
-#pragma unroll
-            for (int k = 0; k < 7; k++) fh[k] = lf[k];
+            touch_tau = 0.0;  // the reference returns its shadowed outer `tau` (unit_world.cc:452-455,473)
+            lf_which = fh_which = ST_TAU;
+            lf_tau = fh_tau = prev_tau;
             steps = k0;
             free_flag = true;
             done = true;
@@ -815,46 +877,80 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB)
           res_left = pws;
           continue;
         } else if (ws > 0 && !exact_next && (fails < 1 || ((k0 >> 5) & 7) == 0)) {
+          act = ACT_SWEEP;
+        } else {
+          // a tile entered because four steps did not clear is short: the contact is expected within them, and every
+          // pose traversed beyond the first hit is wasted
+          act = ACT_EXACT;
+          exact_n = exact_next ? P.sweep_short_tile : 32;
+          exact_next = false;
+        }
+        // ---- the poses of this pass: mid poses of consecutive windows, or consecutive steps
+        bool have;
+        double my_tau, my_radius = 0.0;
+        if (act == ACT_SWEEP) {
           // window `lane` holds the steps whose delta lies in (carry + lane w, carry + (lane + 1) w], w = ws vd,
           // up to the rounding of the running sum (< 1e-6 relative to w for any vd/dist >= 1e-9)
           const double w = (double)ws * vd;
           const double lo = carry + (double)lane * w * (1.0 - 1e-6);
           const double hi = carry + (double)(lane + 1) * w * (1.0 + 1e-6);
-          const bool mine_w = lane < nb && lo <= dist;
-          if (mine_w) {
-            const double tau_lo = lo * inv_dist, tau_hi = fmin(1.0, hi * inv_dist * (1.0 + 1e-9));
-            const double radius = 0.5 * (tau_hi - tau_lo) * rate * (1.0 + 1e-9) + 1e-6;
-            double s[7];
-            interpolate(a, b, 0.5 * (tau_lo + tau_hi), s);
-            set_pose(P, S, lane, s);
-            // half of the radius on each box: every separating axis gains at least radius x |axis|
-            S.eta[lane] = __fadd_ru(S.eta[lane], __double2float_ru(0.5 * radius));
-            S.tau[lane] = radius;   // triangle-level test of the window (the exact path rewrites tau)
+          have = lane < nb && lo <= dist;
+          const double tau_lo = lo * inv_dist, tau_hi = fmin(1.0, hi * inv_dist * (1.0 + 1e-9));
+          my_radius = 0.5 * (tau_hi - tau_lo) * rate * (1.0 + 1e-9) + 1e-6;
+          my_tau = 0.5 * (tau_lo + tau_hi);
+        } else {
+          // step deltas of this tile: lane j takes the (j+1)-th value after `carry`.  The chain of fp64 adds is
+          // inherently serial (the reference's running sum, rounding included), so all lanes run it; it is kept to
+          // add / compare / select per step: with carry = 0 the first value is 0 + vd = vd exactly, and since the
+          // sequence increases strictly, "every delta up to mine is <= dist" is just mine <= dist.
+          double d = carry, mine = 0.0;
+#pragma unroll
+          for (int j = 0; j < 32; j++) {
+            const double t = d + vd;
+            d = (d < dist) ? fmin(dist, t) : t;
+            if (j == lane) mine = d;
           }
+          have = mine <= dist && lane < exact_n;
+          carry = __shfl_sync(FULL, mine, exact_n - 1);  // delta of the last slot (only used when all slots were valid)
+          my_tau = mine * inv_dist;
+        }
+        // Every lane fills its own slot, also the lanes without a step / window (their slot is not part of `alive`):
+        // a per-lane branch around the out-of-line call here costs the traversal below its convergence -- the two
+        // groups of lanes then run every round of it separately (1.75x the warp instructions, measured).
+        seg_pose_at(lane, have ? my_tau : 0.0);
+        if (act == ACT_SWEEP) {
+          // half of the radius on each box: every separating axis gains at least radius x |axis|
+          S.eta[lane] = __fadd_ru(S.eta[lane], __double2float_ru(0.5 * my_radius));
+          S.tau[lane] = my_radius;   // triangle-level test of the window
+        } else {
+          S.tau[lane] = my_tau;
+        }
+        const unsigned alive = __ballot_sync(FULL, have);   // a prefix of the lanes
+        __syncwarp();
+        if (act == ACT_SWEEP) {
+          if (alive == 0) { exact_next = true; continue; }   // cannot happen for finite inputs; never spin
           C.nsurv = 0;
           C.keep_win = 32;
           // pairs are kept only by windows of small radius: a wide window near a contact keeps so many pairs that
           // walking its steps exactly is cheaper than listing and testing them
           C.surv_limit = (double)ws * step_radius <= P.sweep_keep_rmax ? min(SURV_CAP, P.sweep_resolve / ws) : 0;
-          const unsigned tried = __ballot_sync(FULL, mine_w);   // a prefix of the lanes
-          __syncwarp();
-          if (tried == 0) { exact_next = true; continue; }      // cannot happen for finite inputs; never spin
-          const unsigned blocked = traverse_tile<MODE_SWEPT_KEEP>(P, S, C, tried, lane);
-          if (C.overflow) { done = true; break; }
-          __syncwarp();
-          const int ntried = __popc(tried);
-          const int first_blocked = blocked ? min(ntried, __ffs(blocked) - 1) : ntried;
+        }
+        unsigned hits;
+        if (act == ACT_LISTED) {
+          hits = test_kept_pairs(P, S, C, ncur, 31 - __clz(exact_n), alive, lane);
+          res_left -= exact_n;
+        } else {
+          hits = traverse_tile<MODE_RT>(P, S, C, alive, lane, 0, nullptr, nullptr, 0,
+                                        act == ACT_SWEEP ? MODE_SWEPT_KEEP : MODE_SEGMENT);
+        }
+        if (C.overflow) { done = true; break; }
+        __syncwarp();
+        if (act == ACT_SWEEP) {
+          const int ntried = __popc(alive);
+          const int first_blocked = hits ? min(ntried, __ffs(hits) - 1) : ntried;
           pend_keep = C.keep_win < first_blocked;      // that window kept at most surv_limit pairs, all of them listed
           pend_clear = pend_keep ? C.keep_win : first_blocked;
           pws = ws;
-#ifdef OSR_K2_TRACE
-          {
-            const unsigned tb = __reduce_add_sync(FULL, C.n_bv), tl = __reduce_add_sync(FULL, C.n_leaf);
-            if (lane == 0 && seg < 48)
-              printf("seg %d k0 %lld sweep ws %d nb %d tried %d blocked_at %d keep_win %d kept %d | bv %u leaf %u\n", (int)seg, k0, ws, nb,
-                     ntried, first_blocked, C.keep_win, C.nsurv, tb, tl);
-          }
-#endif
           if (pend_keep) {           // near a contact: one window per traversal until windows clear again
             fails = 0;
             nb = 1;
@@ -871,58 +967,15 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB)
             if (first_blocked == 0) fails++;
           }
           continue;
-        } else {
-          // a tile entered because four steps did not clear is short: the contact is expected within them, and every
-          // pose traversed beyond the first hit is wasted
-          exact_n = exact_next ? P.sweep_short_tile : 32;
-          exact_next = false;
         }
-        // step deltas of this tile: lane j takes the (j+1)-th value after `carry`.  The chain of fp64 adds is
-        // inherently serial (the reference's running sum, rounding included), so all lanes run it; it is kept to
-        // add / compare / select per step: with carry = 0 the first value is 0 + vd = vd exactly, and since the
-        // sequence increases strictly, "every delta up to mine is <= dist" is just mine <= dist.
-        double d = carry, mine = 0.0;
-#pragma unroll
-        for (int j = 0; j < 32; j++) {
-          const double t = d + vd;
-          d = (d < dist) ? fmin(dist, t) : t;
-          if (j == lane) mine = d;
-        }
-        const bool mine_ok = mine <= dist && lane < exact_n;
-        carry = __shfl_sync(FULL, mine, exact_n - 1);  // delta of the last slot (only used when all slots were valid)
-        double tau = mine * inv_dist;
-        if (mine_ok) {
-          double s[7];
-          interpolate(a, b, tau, s);
-          set_pose(P, S, lane, s);
-          S.tau[lane] = tau;
-        }
-        unsigned alive = __ballot_sync(FULL, mine_ok);
-        __syncwarp();
-        unsigned hits;
-        if (listed) {
-          hits = test_kept_pairs(P, S, C, ncur, 31 - __clz(exact_n), alive, lane);
-          res_left -= exact_n;
-        } else {
-          hits = traverse_tile<MODE_SEGMENT>(P, S, C, alive, lane);
-        }
-        if (C.overflow) { done = true; break; }
-        int nalive = __popc(alive);
-#ifdef OSR_K2_TRACE
-        {
-          const unsigned tb = __reduce_add_sync(FULL, C.n_bv), tl = __reduce_add_sync(FULL, C.n_leaf), t64 = __reduce_add_sync(FULL, C.n_fp64);
-          if (lane == 0 && seg < 48)
-            printf("seg %d k0 %lld %s n %d ncur %d alive %d hits %08x | bv %u leaf %u fp64 %u\n", (int)seg, k0, listed ? "listed" : "exact",
-                   exact_n, listed ? ncur : -1, nalive, hits, tb, tl, t64);
-        }
-#endif
+        const int nalive = __popc(alive);
         if (hits) {
-          int j = __ffs(hits) - 1;
+          const int j = __ffs(hits) - 1;
           nposes += j + 1;
           touch_tau = S.tau[j];
           free_tau = j > 0 ? S.tau[j - 1] : prev_tau;
-          interpolate(a, b, touch_tau, fh);
-          if (j > 0 || k0 > 0) interpolate(a, b, free_tau, lf);
+          fh_which = ST_TAU; fh_tau = touch_tau;
+          if (j > 0 || k0 > 0) { lf_which = ST_TAU; lf_tau = free_tau; }
           steps = k0 + j + 1;
           free_flag = false;
           done = true;
@@ -933,9 +986,8 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB)
           if (nalive < exact_n) {  // walked past dist: the whole segment is free
             free_tau = prev_tau;
             touch_tau = 0.0;  // the reference returns its shadowed outer `tau` (unit_world.cc:452-455,473)
-            interpolate(a, b, prev_tau, lf);
-#pragma unroll
-            for (int k = 0; k < 7; k++) fh[k] = lf[k];
+            lf_which = fh_which = ST_TAU;
+            lf_tau = fh_tau = prev_tau;
             steps = k0;
             free_flag = true;
             done = true;
@@ -950,10 +1002,8 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB)
       if (O.touch_tau) O.touch_tau[seg] = touch_tau;
       if (O.steps) O.steps[seg] = steps;
     }
-    if (lane < 7) {
-      if (O.last_free) O.last_free[7 * seg + lane] = lf[lane];
-      if (O.first_hit) O.first_hit[7 * seg + lane] = fh[lane];
-    }
+    if (O.last_free) seg_write_state(O.last_free + 7 * seg, lf_which, lf_tau, lane);
+    if (O.first_hit) seg_write_state(O.first_hit + 7 * seg, fh_which, fh_tau, lane);
     if (C.overflow) break;
   }
   ctx_flush(P, C, nposes, lane);

@@ -84,10 +84,12 @@ def main():
                 fr, to = cases["knn"]
                 oa, ob = sw.translate_unit_to_ompl(fr), sw.translate_unit_to_ompl(to)
                 oc, od = sw.translate_unit_to_ompl(cases["from_contact"][0]), sw.translate_unit_to_ompl(cases["from_contact"][1])
+                allp = np.concatenate([oa[:, :3], ob[:, :3], oc[:, :3], od[:, :3]])
+                bounds = (allp.min(axis=0) - 1.0, allp.max(axis=0) + 1.0)   # OmplDriver.set_bounds: every state inside
                 for res in (1e-4, 1e-3, 1e-2):
                     for (u, v2) in ((oa, ob), (oc[:1024], od[:1024])):
-                        x = sw.ompl_validate_motion_pairs(u, v2, 150.0, res, with_counts=True)
-                        y = pl.ompl_validate_motion_pairs(u, v2, 150.0, res, with_counts=True)
+                        x = sw.ompl_validate_motion_pairs(u, v2, bounds, res, with_counts=True)
+                        y = pl.ompl_validate_motion_pairs(u, v2, bounds, res, with_counts=True)
                         total += len(u)
                         if not (np.array_equal(x[0], y[0]) and np.array_equal(x[1], y[1])):
                             bad += 1
