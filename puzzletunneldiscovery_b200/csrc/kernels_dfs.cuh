@@ -169,6 +169,24 @@ __device__ __forceinline__ void dfs_expand_step(E& cur, int& sp, const int sb, S
   float s0, s1, va0, vb0, va1, vb1;
   const bool ov0 = obb_overlap_q2(A0, B0, bp, s0, va0, vb0);
   const bool ov1 = obb_overlap_q2(A1, B1, bp, s1, va1, vb1);
+#ifndef OSR_DFS_BRANCHY
+  // everything below is selects and predicated shared-memory accesses: the lanes of a warp take all combinations of
+  // (overlap, leaf pair, which child first), and branches here cost more in reconvergence than the few ALU
+  // instructions they skip
+  const bool pl0 = A0.link < 0 && B0.link < 0, pl1 = A1.link < 0 && B1.link < 0;
+  lf0 = ov0 && pl0; lf1 = ov1 && pl1;
+  ta0 = (unsigned)(-(A0.link + 1)); tb0 = (unsigned)(-(B0.link + 1));
+  ta1 = (unsigned)(-(A1.link + 1)); tb1 = (unsigned)(-(B1.link + 1));
+  const E x0 = expand_entry<E>(A0, B0, ia0, ib0, va0, vb0), x1 = expand_entry<E>(A1, B1, ia1, ib1, va1, vb1);
+  const E e0 = (ov0 && !pl0) ? x0 : (E)0, e1 = (ov1 && !pl1) ? x1 : (E)0;
+  const bool both = e0 != 0 && e1 != 0, second_first = s1 > s0;
+  if (both) stack[sp][lane] = second_first ? e0 : e1;
+  E nxt = both ? (second_first ? e1 : e0) : (e0 != 0 ? e0 : e1);
+  const bool pop = nxt == 0 && sp > sb;
+  sp += both ? 1 : (pop ? -1 : 0);
+  if (pop) nxt = stack[sp][lane];
+  cur = nxt;
+#else
   E e0 = 0, e1 = 0;
   if (ov0) {
     if (A0.link < 0 && B0.link < 0) { lf0 = true; ta0 = (unsigned)(-(A0.link + 1)); tb0 = (unsigned)(-(B0.link + 1)); }
@@ -188,6 +206,7 @@ __device__ __forceinline__ void dfs_expand_step(E& cur, int& sp, const int sb, S
     if (nxt == 0 && sp > sb) { sp--; nxt = stack[sp][lane]; }
     cur = nxt;
   }
+#endif
 }
 
 // The entry a pose starts from once its root boxes are known to overlap (0 when both roots are leaves: the only

@@ -224,6 +224,7 @@ OSR_HD bool obb_overlap_q2(const QNode& A, const QNode& B, const BoxPose& P, flo
   float s5 = (eb2 + fmaf(F02, ea0, fmaf(F12, ea1, F22 * ea2))) - fabsf(fmaf(B02, T0, fmaf(B12, T1, B22 * T2)));
   slack = fminf(fminf(fminf(s0, s1), fminf(s2, s3)), fminf(s4, s5));
   bool sep = slack < 0.f;
+  // (the nine edge x edge axes are not optional: without them K1 runs 30 % more box tests and 4.4x the triangle tests)
   sep |= fabsf(fmaf(T2, B10, -T1 * B20)) > fmaf(ea1, F20, fmaf(ea2, F10, fmaf(eb1, F02, eb2 * F01)));
   sep |= fabsf(fmaf(T2, B11, -T1 * B21)) > fmaf(ea1, F21, fmaf(ea2, F11, fmaf(eb0, F02, eb2 * F00)));
   sep |= fabsf(fmaf(T2, B12, -T1 * B22)) > fmaf(ea1, F22, fmaf(ea2, F12, fmaf(eb0, F01, eb1 * F00)));
