@@ -21,6 +21,7 @@
 #include <stdint.h>
 
 #include "se3.h"
+#include "sat17.h"
 
 namespace osr {
 
@@ -180,91 +181,6 @@ __device__ __forceinline__ void axis_gaps(const T* ax, const Tri6<T>& t, T& g1, 
   g2 = mnQ - mxP;
 }
 
-// Exact restatement (fp64, reference operation order) -> true iff no axis separates.
-__device__ __noinline__ bool sat17_exact(const Tri6<double>& t) {
-  double e1[3] = {t.p2[0], t.p2[1], t.p2[2]};                                  // p2 - p1
-  double e2[3] = {t.p3[0] - t.p2[0], t.p3[1] - t.p2[1], t.p3[2] - t.p2[2]};   // p3 - p2
-  double e3[3] = {0.0 - t.p3[0], 0.0 - t.p3[1], 0.0 - t.p3[2]};               // p1 - p3
-  double f1[3] = {t.q2[0] - t.q1[0], t.q2[1] - t.q1[1], t.q2[2] - t.q1[2]};
-  double f2[3] = {t.q3[0] - t.q2[0], t.q3[1] - t.q2[1], t.q3[2] - t.q2[2]};
-  double f3[3] = {t.q1[0] - t.q3[0], t.q1[1] - t.q3[1], t.q1[2] - t.q3[2]};
-  double n1[3], m1[3], ax[3], g1, g2;
-  crossT(e1, e2, n1);
-  axis_gaps(n1, t, g1, g2); if (g1 > 0 || g2 > 0) return false;
-  crossT(f1, f2, m1);
-  axis_gaps(m1, t, g1, g2); if (g1 > 0 || g2 > 0) return false;
-  const double* E[3] = {e1, e2, e3};
-  const double* F[3] = {f1, f2, f3};
-#pragma unroll
-  for (int i = 0; i < 3; i++)
-#pragma unroll
-    for (int j = 0; j < 3; j++) {
-      crossT(E[i], F[j], ax);
-      axis_gaps(ax, t, g1, g2); if (g1 > 0 || g2 > 0) return false;
-    }
-#pragma unroll
-  for (int i = 0; i < 3; i++) {
-    crossT(E[i], n1, ax);
-    axis_gaps(ax, t, g1, g2); if (g1 > 0 || g2 > 0) return false;
-  }
-#pragma unroll
-  for (int i = 0; i < 3; i++) {
-    crossT(F[i], m1, ax);
-    axis_gaps(ax, t, g1, g2); if (g1 > 0 || g2 > 0) return false;
-  }
-  return true;
-}
-
-// fp32 filter.  Inputs are the fp64 values rounded to nearest; with u = 2^-24 and
-// L = max |coordinate|, every gap of the 11 "quadratic" axes (n1, m1, e x f) is within
-// 600 u L^3 of its exact value and every gap of the 6 "cubic" axes (e x n1, f x m1) within
-// 3000 u L^4 (derivation in DESIGN.md).  Returns 0 = certainly separated, 1 = certainly
-// intersecting (no axis separates), 2 = undecided.
-__device__ __forceinline__ int sat17_filter(const Tri6<float>& t) {
-  float L = 0.f;
-#pragma unroll
-  for (int k = 0; k < 3; k++) {
-    L = fmaxf(L, fmaxf(fabsf(t.p2[k]), fabsf(t.p3[k])));
-    L = fmaxf(L, fmaxf(fabsf(t.q1[k]), fmaxf(fabsf(t.q2[k]), fabsf(t.q3[k]))));
-  }
-  const float u = 5.9604645e-08f;
-  float L3 = L * L * L;
-  float Eq = 640.f * u * L3 + 1e-37f;
-  float Ec = 3200.f * u * L3 * L + 1e-37f;
-  float e1[3] = {t.p2[0], t.p2[1], t.p2[2]};
-  float e2[3] = {t.p3[0] - t.p2[0], t.p3[1] - t.p2[1], t.p3[2] - t.p2[2]};
-  float e3[3] = {-t.p3[0], -t.p3[1], -t.p3[2]};
-  float f1[3] = {t.q2[0] - t.q1[0], t.q2[1] - t.q1[1], t.q2[2] - t.q1[2]};
-  float f2[3] = {t.q3[0] - t.q2[0], t.q3[1] - t.q2[1], t.q3[2] - t.q2[2]};
-  float f3[3] = {t.q1[0] - t.q3[0], t.q1[1] - t.q3[1], t.q1[2] - t.q3[2]};
-  float n1[3], m1[3], ax[3], g1, g2;
-  bool sep = false, unsure = false;
-  crossT(e1, e2, n1);
-  axis_gaps(n1, t, g1, g2); sep |= (g1 > Eq) | (g2 > Eq); unsure |= !((g1 < -Eq) & (g2 < -Eq));
-  crossT(f1, f2, m1);
-  axis_gaps(m1, t, g1, g2); sep |= (g1 > Eq) | (g2 > Eq); unsure |= !((g1 < -Eq) & (g2 < -Eq));
-  if (sep) return 0;
-  const float* E[3] = {e1, e2, e3};
-  const float* F[3] = {f1, f2, f3};
-#pragma unroll
-  for (int i = 0; i < 3; i++)
-#pragma unroll
-    for (int j = 0; j < 3; j++) {
-      crossT(E[i], F[j], ax);
-      axis_gaps(ax, t, g1, g2); sep |= (g1 > Eq) | (g2 > Eq); unsure |= !((g1 < -Eq) & (g2 < -Eq));
-    }
-  if (sep) return 0;
-#pragma unroll
-  for (int i = 0; i < 3; i++) {
-    crossT(E[i], n1, ax);
-    axis_gaps(ax, t, g1, g2); sep |= (g1 > Ec) | (g2 > Ec); unsure |= !((g1 < -Ec) & (g2 < -Ec));
-    crossT(F[i], m1, ax);
-    axis_gaps(ax, t, g1, g2); sep |= (g1 > Ec) | (g2 > Ec); unsure |= !((g1 < -Ec) & (g2 < -Ec));
-  }
-  if (sep) return 0;
-  return unsure ? 2 : 1;
-}
-
 // Edge vectors of both triangles and the a-th of the 11 "quadratic" axes (0: n1 = e1 x e2, 1: m1 = f1 x f2,
 // 2 + 3 i + j: e_i x f_j -- the order of intersect-inl.h:745-777), operands picked with selects.
 struct TriEdgesF {
@@ -327,7 +243,7 @@ __device__ __noinline__ bool tri_gap_clear_f(const Tri6<float>& t, float r, unsi
 }
 
 // One axis of the fp32 filter: true when quadratic axis a certainly separates (same arithmetic and bound as
-// sat17_filter for that axis, so the exact fp64 SAT-17 finds the same axis separating and reports "disjoint").
+// sat17_filter_c for that axis, so the exact fp64 SAT-17 finds the same axis separating and reports "disjoint").
 __device__ __forceinline__ bool sat17_axis_separates(const Tri6<float>& t, unsigned a) {
   float L = 0.f;
 #pragma unroll
@@ -335,9 +251,16 @@ __device__ __forceinline__ bool sat17_axis_separates(const Tri6<float>& t, unsig
     L = fmaxf(L, fmaxf(fabsf(t.p2[k]), fabsf(t.p3[k])));
     L = fmaxf(L, fmaxf(fabsf(t.q1[k]), fmaxf(fabsf(t.q2[k]), fabsf(t.q3[k]))));
   }
-  const float Eq = 640.f * 5.9604645e-08f * L * L * L + 1e-37f;
   TriEdgesF E;
   E.set(t);
+  // the two edge vectors the axis is the cross product of (0: e1 x e2, 1: f1 x f2, 2 + 3 i + j: e_i x f_j)
+  const unsigned b = a >= 2u ? a - 2u : 0u;
+  const unsigned i = b / 3u, j = b - 3u * i;
+  const float me0 = maxabs3(E.e[0]), me1 = maxabs3(E.e[1]), me2 = maxabs3(E.e[2]);
+  const float mf0 = maxabs3(E.f[0]), mf1 = maxabs3(E.f[1]), mf2 = maxabs3(E.f[2]);
+  const float mu = a == 0 ? me0 : (a == 1 ? mf0 : (i == 0 ? me0 : (i == 1 ? me1 : me2)));
+  const float mw = a == 0 ? me1 : (a == 1 ? mf1 : (j == 0 ? mf0 : (j == 1 ? mf1 : mf2)));
+  const float Eq = sat17_bound_q(1.1f * 5.9604645e-08f * L, L, mu, mw);
   float ax[3], g1, g2;
   E.axis(a, ax);
   axis_gaps(ax, t, g1, g2);
@@ -372,14 +295,16 @@ __device__ __forceinline__ void load_pair_exact(const double* __restrict__ P, co
 // bit 0: the fp64 SAT-17 reports an intersection; bit 1: the fp32 filter left the pair open and fp64 decided.
 // One copy per kernel (noinline): the predicate is ~700 instructions and has several callers.
 __device__ __noinline__ int tri_pair_intersect(const Tri6<double>& td) {
-  Tri6<float> tf;
+  // Tri6 and TriPair (sat17.h) have the same layout; the predicates are the host-tested ones of sat17.h
+  const TriPair<double>& pd = reinterpret_cast<const TriPair<double>&>(td);
+  TriPair<float> tf;
 #pragma unroll
   for (int k = 0; k < 3; k++) {
     tf.p2[k] = (float)td.p2[k]; tf.p3[k] = (float)td.p3[k];
     tf.q1[k] = (float)td.q1[k]; tf.q2[k] = (float)td.q2[k]; tf.q3[k] = (float)td.q3[k];
   }
-  const int r = sat17_filter(tf);
-  if (r == 2) return 2 | (sat17_exact(td) ? 1 : 0);
+  const int r = sat17_filter_c(tf);
+  if (r == 2) return 2 | (sat17_exact_c(pd) ? 1 : 0);
   return r;
 }
 

@@ -95,29 +95,52 @@ OSR_HD bool sat17_exact_c(const TriPair<double>& t) {
   return true;
 }
 
-// fp32 filter.  Inputs are the fp64 values rounded to nearest; with u = 2^-24 and L = max |coordinate|, every
-// gap of the 11 "quadratic" axes (n1, m1, e x f) is within 600 u L^3 of its exact value and every gap of the 6
-// "cubic" axes (e x n1, f x m1) within 3000 u L^4 (same bounds as sat17_filter in kernels.cuh).
+// fp32 filter.  Inputs are the fp64 values rounded to nearest.  With u = 2^-24, L = max |coordinate| and, for an edge
+// vector v, |v| = its largest |component| (as computed), the computed gap of an axis differs from the fp64 value by
+// at most
+//     u L (48 L (|a| + |b|) + 84 |a| |b|)                           axis a x b of two edges (n1, m1, e_i x f_j)
+//     u L (96 L (|a||b| + |v| (|a| + |b|)) + 216 |v| |a| |b|)        axis v x (a x b)  (e_i x n1, f_i x m1)
+// (edge components carry 4 u L of input rounding, a cross product of vectors with errors ea, eb gains
+// 2 (ea |b| + eb |a|) + 4 u |a| |b| per component, a projection on a point of magnitude <= L gains 3 L times that
+// plus 12 u L |axis|, a gap is the difference of two projections plus its own rounding); the factor 1.1 below
+// covers the second-order terms and the rounding of the fp64 evaluation itself.  The bounds scale with the edges
+// actually involved: with one L^3 / L^4 bound for all axes, the long thin triangles of the alpha puzzle left half
+// of all intersecting pairs undecided (their in-plane axes e x n have tiny projections next to L^4).
+// Returns 0 = certainly separated, 1 = certainly intersecting (no axis separates), 2 = undecided (the caller runs
+// sat17_exact_c).
+template <typename T>
+OSR_HD T maxabs3(const T* v) {
+  T a = v[0] < 0 ? -v[0] : v[0], b = v[1] < 0 ? -v[1] : v[1], c = v[2] < 0 ? -v[2] : v[2];
+  T m = a > b ? a : b;
+  return m > c ? m : c;
+}
+OSR_HD float sat17_bound_q(float uL, float L, float a, float b) {
+  return uL * (48.f * L * (a + b) + 84.f * a * b) + 1e-37f;
+}
+OSR_HD float sat17_bound_c(float uL, float L, float v, float a, float b) {
+  return uL * (96.f * L * (a * b + v * (a + b)) + 216.f * v * a * b) + 1e-37f;
+}
 OSR_HD int sat17_filter_c(const TriPair<float>& t) {
   float L = 0.f;
   for (int k = 0; k < 3; k++) {
     L = fmaxf(L, fmaxf(fabsf(t.p2[k]), fabsf(t.p3[k])));
     L = fmaxf(L, fmaxf(fabsf(t.q1[k]), fmaxf(fabsf(t.q2[k]), fabsf(t.q3[k]))));
   }
-  const float u_ = 5.9604645e-08f;
-  float L3 = L * L * L;
-  float Eq = 640.f * u_ * L3 + 1e-37f;
-  float Ec = 3200.f * u_ * L3 * L + 1e-37f;
+  const float uL = 1.1f * 5.9604645e-08f * L;
   Edges<float> E;
   E.set(t);
+  const float ue0 = maxabs3(E.e[0]), ue1 = maxabs3(E.e[1]), ue2 = maxabs3(E.e[2]);
+  const float uf0 = maxabs3(E.f[0]), uf1 = maxabs3(E.f[1]), uf2 = maxabs3(E.f[2]);
   float n1[3], m1[3], ax[3], u[3], w[3], g1, g2;
   bool sep = false, unsure = false;
   cross3(E.e[0], E.e[1], n1);
   gaps17(n1, t, g1, g2);
-  sep |= (g1 > Eq) | (g2 > Eq); unsure |= !((g1 < -Eq) & (g2 < -Eq));
+  float B = sat17_bound_q(uL, L, ue0, ue1);
+  sep |= (g1 > B) | (g2 > B); unsure |= !((g1 < -B) & (g2 < -B));
   cross3(E.f[0], E.f[1], m1);
   gaps17(m1, t, g1, g2);
-  sep |= (g1 > Eq) | (g2 > Eq); unsure |= !((g1 < -Eq) & (g2 < -Eq));
+  B = sat17_bound_q(uL, L, uf0, uf1);
+  sep |= (g1 > B) | (g2 > B); unsure |= !((g1 < -B) & (g2 < -B));
   if (sep) return 0;
 #pragma unroll 1
   for (int a = 0; a < 9; a++) {
@@ -126,7 +149,8 @@ OSR_HD int sat17_filter_c(const TriPair<float>& t) {
     E.pick_f(j, w);
     cross3(u, w, ax);
     gaps17(ax, t, g1, g2);
-    sep |= (g1 > Eq) | (g2 > Eq); unsure |= !((g1 < -Eq) & (g2 < -Eq));
+    B = sat17_bound_q(uL, L, i == 0 ? ue0 : (i == 1 ? ue1 : ue2), j == 0 ? uf0 : (j == 1 ? uf1 : uf2));
+    sep |= (g1 > B) | (g2 > B); unsure |= !((g1 < -B) & (g2 < -B));
   }
   if (sep) return 0;
 #pragma unroll 1
@@ -136,7 +160,9 @@ OSR_HD int sat17_filter_c(const TriPair<float>& t) {
     for (int k = 0; k < 3; k++) w[k] = a < 3 ? n1[k] : m1[k];
     cross3(u, w, ax);
     gaps17(ax, t, g1, g2);
-    sep |= (g1 > Ec) | (g2 > Ec); unsure |= !((g1 < -Ec) & (g2 < -Ec));
+    const float v = a < 3 ? (i == 0 ? ue0 : (i == 1 ? ue1 : ue2)) : (i == 0 ? uf0 : (i == 1 ? uf1 : uf2));
+    B = sat17_bound_c(uL, L, v, a < 3 ? ue0 : uf0, a < 3 ? ue1 : uf1);
+    sep |= (g1 > B) | (g2 > B); unsure |= !((g1 < -B) & (g2 < -B));
   }
   if (sep) return 0;
   return unsure ? 2 : 1;
