@@ -10,8 +10,8 @@
 //   * new poses are prepared 32 at a time by the whole warp (coalesced state loads, fp64 pose maths, the root
 //     box test) -- poses separated at the root never occupy a lane;
 //   * triangle pairs are not tested where they are found: they go to a per-warp queue that is drained 32 pairs
-//     at a time with the fp32-filtered SAT-17, undecided pairs go to a second queue for the fp64 SAT-17, so
-//     the expensive exact predicate also runs with full lanes;
+//     at a time with the fp32-filtered SAT-17; the few pairs it leaves open (about one in 500 states with the
+//     per-axis bounds of sat17.h) get the fp64 SAT-17 on the spot;
 //   * the trees are 32-byte QNodes (qnode.h); their first levels (for alpha-1.2: both whole trees, 129 KB)
 //     live in shared memory, where a 32-lane gather costs bank conflicts instead of one L1 wavefront per lane.
 #pragma once
@@ -65,7 +65,7 @@ constexpr int REFILL_MIN = 1;    // pull new poses once this many lanes are idle
 // 0: a lane keeps traversing while its triangle pairs wait in a queue; 1: it pauses while pairs wait for the fp32
 // filter (with depth-ordered expansion the first pair found is usually the hit); 2: also while pairs wait for fp64
 constexpr int PAUSE_ON_LEAF = OSR_PAUSE_ON_LEAF;
-constexpr unsigned PAUSE_MASK = PAUSE_ON_LEAF == 2 ? 12u : (PAUSE_ON_LEAF == 1 ? 4u : 0u);   // F_PL | F_PR bits
+constexpr unsigned PAUSE_MASK = PAUSE_ON_LEAF >= 1 ? 4u : 0u;   // F_PL (K1; the segment variant also pauses on F_PR)
 
 // work-stack entry = one OVERLAPPING (environment node, robot node) pair still to be expanded, stored as
 // (first child of the node that gets split, the other node, which tree is split); 0 means "none".
@@ -91,7 +91,6 @@ template <typename E, int DEPTH>
 struct __align__(16) DfsWarpMem {
   E stack[DEPTH][32];
   unsigned long long leafq[LEAFQ_CAP];
-  unsigned long long req[REQ_CAP];
   float pend[17][32];  // BoxPose of prepared poses: q[4] R[9] t[3] eta
   int pend_idx[32];
   int parts[32];       // work sharing at the end of the input: lanes still working on the pose of home lane i
@@ -286,8 +285,8 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
   int sp = 0, sb = 0;   // the lane's stack is stack[sb .. sp-1][lane]
   int home = lane;      // lane that pulled the pose this lane works on (differs after a steal)
   // warp state (uniform)
-  int pend_n = 0, nleaf = 0, nre = 0, since_flush = 0, re_age = 0;
-  bool exhausted = false, draining_leaf = false, draining_re = false, steal_mode = false;
+  int pend_n = 0, nleaf = 0, since_flush = 0;
+  bool exhausted = false, draining_leaf = false, steal_mode = false;
   unsigned n_bv = 0, n_leaf = 0, n_fp64 = 0;
   unsigned long long nposes = 0;
   if (FEED) M.ready_seen = (int)min(P.ready_floor, 0x7fffffffLL);  // same value from every lane
@@ -298,7 +297,7 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
   while (true) {
     // (1) completed poses.  Once lanes share poses (steal_mode) a pose is finished by the last of its parts.
     {
-      bool done = (fl & F_HAS) && ((fl & F_HIT) || (cur == 0 && !(fl & (F_PL | F_PR))));
+      bool done = (fl & F_HAS) && ((fl & F_HIT) || (cur == 0 && !(fl & F_PL)));
       if (!steal_mode) {
         if (done) src.result(tag, (fl & F_HIT) != 0);
       } else {
@@ -452,7 +451,7 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
     // of new triangle pairs on top)
     const bool runnable = cur != 0 && !(fl & PAUSE_MASK);
     const bool any_cur = __any_sync(FULL, runnable);
-    if (any_cur && !draining_leaf && !draining_re) {
+    if (any_cur && !draining_leaf) {
       bool lf0 = false, lf1 = false;
       unsigned ta0 = 0, tb0 = 0, ta1 = 0, tb1 = 0;
 #ifdef OSR_DFS_STATS
@@ -474,35 +473,23 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
         __syncwarp();
       }
       since_flush++;
-      re_age = nre > 0 ? re_age + 1 : 0;
     }
-    // (4) drain policy: which queue (if any) gets one chunk of up to 32 entries processed now
-    bool do_leaf = false, do_re = false;
+    // (4) drain policy: is one chunk of up to 32 queued triangle pairs processed now?
+    bool do_leaf = false;
     if (draining_leaf) do_leaf = true;
-    else if (draining_re) do_re = true;
     else if (!any_cur) {
       if (nleaf > 0) do_leaf = true;
-      else if (nre > 0) do_re = true;
       else if (!__any_sync(FULL, (fl & F_HAS) != 0) && exhausted && pend_n == 0) break;
-    } else {
-      if (nleaf > 0) {
-        unsigned waiting = __ballot_sync(FULL, (fl & (F_HAS | F_PL)) == (F_HAS | F_PL) && (cur == 0 || (fl & PAUSE_MASK)));
-        do_leaf = nleaf >= LEAF_FLUSH || __popc(waiting) >= WAIT_FLUSH || since_flush > 1024;
-      }
-      if (!do_leaf && nre > 0) {
-        unsigned waiting = __ballot_sync(FULL, (fl & (F_HAS | F_PL | F_PR)) == (F_HAS | F_PR) && (cur == 0 || (fl & PAUSE_MASK)));
-        do_re = nre >= RE_FLUSH || __popc(waiting) >= WAIT_FLUSH || re_age > 1024;
-      }
+    } else if (nleaf > 0) {
+      unsigned waiting = __ballot_sync(FULL, (fl & (F_HAS | F_PL)) == (F_HAS | F_PL) && (cur == 0 || (fl & PAUSE_MASK)));
+      do_leaf = nleaf >= LEAF_FLUSH || __popc(waiting) >= WAIT_FLUSH || since_flush > 1024;
     }
-    if (do_leaf && nre > REQ_CAP - 32) { do_leaf = false; do_re = true; draining_leaf = true; }  // make room first
-    if (do_leaf | do_re) {
-      // the fp32-filtered SAT-17 for queued pairs / the exact fp64 SAT-17 for the pairs the filter left open
-      unsigned long long* Q = do_leaf ? M.leafq : M.req;
-      int& cntq = do_leaf ? nleaf : nre;
-      int cnt = min(32, cntq);
+    if (do_leaf) {
+      // the fp32-filtered SAT-17 for queued pairs; a pair the filter leaves open gets the exact fp64 SAT-17 at once
+      int cnt = min(32, nleaf);
       bool act = lane < cnt;
-      unsigned long long e = act ? Q[cntq - 1 - lane] : 0ull;
-      cntq -= cnt;
+      unsigned long long e = act ? M.leafq[nleaf - 1 - lane] : 0ull;
+      nleaf -= cnt;
       unsigned owner = (unsigned)e & 31u, ep = (unsigned)(e >> 5) & 0x7ffu;
       unsigned oep = __shfl_sync(FULL, epoch, owner), ofl = __shfl_sync(FULL, fl, owner);
       int otag = __shfl_sync(FULL, tag, owner);
@@ -514,34 +501,23 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
         TriPair<double> td;
         load_pair_exact_r(P.env_tris + (size_t)9 * ((unsigned)(e >> 16) & 0xffffffu),
                           P.rob_tris + (size_t)9 * (unsigned)(e >> 40), rel, td);
-        if (do_leaf) {
-          TriPair<float> tf;
+        TriPair<float> tf;
 #pragma unroll
-          for (int k = 0; k < 3; k++) {
-            tf.p2[k] = (float)td.p2[k]; tf.p3[k] = (float)td.p3[k];
-            tf.q1[k] = (float)td.q1[k]; tf.q2[k] = (float)td.q2[k]; tf.q3[k] = (float)td.q3[k];
-          }
-          r = sat17_filter_c(tf);
-          n_leaf++;
-        } else {
+        for (int k = 0; k < 3; k++) {
+          tf.p2[k] = (float)td.p2[k]; tf.p3[k] = (float)td.p3[k];
+          tf.q1[k] = (float)td.q1[k]; tf.q2[k] = (float)td.q2[k]; tf.q3[k] = (float)td.q3[k];
+        }
+        r = sat17_filter_c(tf);
+        n_leaf++;
+        if (r == 2) {
           r = sat17_exact_c(td) ? 1 : 0;
           n_fp64++;
         }
       }
       unsigned hm = __reduce_or_sync(FULL, r == 1 ? (1u << owner) : 0u);
       if (hm >> lane & 1u) fl |= F_HIT;
-      if (do_leaf) {
-        unsigned um = __ballot_sync(FULL, r == 2);
-        unsigned uo = __reduce_or_sync(FULL, r == 2 ? (1u << owner) : 0u);
-        if (r == 2) M.req[nre + __popc(um & ltmask)] = e;
-        nre += __popc(um);
-        if (uo >> lane & 1u) fl |= F_PR;
-        draining_leaf = nleaf > 0;
-        if (nleaf == 0) { fl &= ~F_PL; since_flush = 0; }
-      } else {
-        draining_re = nre > 0;
-        if (nre == 0) fl &= ~F_PR;
-      }
+      draining_leaf = nleaf > 0;
+      if (nleaf == 0) { fl &= ~F_PL; since_flush = 0; }
       __syncwarp();
     }
   }

@@ -38,10 +38,28 @@ def _pairs(kind, n, rs):
     elif kind == "tiny":           # the scale of G-hi leaf triangles, far from the origin of the pair
         P = rs.randn(n, 3, 3) * 2e-4 + rs.randn(n, 1, 3) * 0.3
         Q = P.mean(1, keepdims=True) + rs.randn(n, 3, 3) * 2e-4
+    elif kind.startswith("thin"):  # long thin triangles (aspect 1 .. 1000) like the faces of the alpha puzzle: the
+        # per-axis error bounds of the filter scale with the edges involved, and these are the pairs that probe them
+        def thin(c):
+            a = 10 ** rs.uniform(-2, 0, size=(n, 1, 1)); r = 10 ** rs.uniform(-3, 0, size=(n, 1, 1))
+            d1 = rs.randn(n, 1, 3); d1 /= np.linalg.norm(d1, axis=2, keepdims=True)
+            d2 = rs.randn(n, 1, 3); d2 -= (d2 * d1).sum(2, keepdims=True) * d1
+            d2 /= np.linalg.norm(d2, axis=2, keepdims=True)
+            o = c - 0.5 * a * d1
+            return np.concatenate([o, o + a * d1, o + a * rs.rand(n, 1, 1) * d1 + a * r * d2], axis=1), a * r
+        P, w = thin(rs.randn(n, 1, 3) * 0.3)
+        off = rs.randn(n, 1, 3) * w * rs.choice([0, 1e-7, 1e-5, 1e-3, 1e-1, 1], size=(n, 1, 1))
+        Q, _ = thin(P.mean(1, keepdims=True) + off)
+        if kind == "thin_touching":    # a vertex of Q in P's plane
+            b = rs.rand(n, 3); b /= b.sum(1, keepdims=True)
+            Q[:, 0] = np.einsum("nj,njk->nk", b, P)
+        elif kind == "thin_shared":    # a shared vertex
+            Q[:, 0] = P[:, 1]
     return np.concatenate([P, Q], axis=1)
 
 
-@pytest.mark.parametrize("kind", ["random", "near", "parallel_edges", "shared_vertex", "touching", "needle", "grid", "tiny"])
+@pytest.mark.parametrize("kind", ["random", "near", "parallel_edges", "shared_vertex", "touching", "needle", "grid", "tiny",
+                                  "thin", "thin_touching", "thin_shared"])
 def test_filter_never_contradicts_the_exact_predicate(kind, oracle_mod):
     rs = np.random.RandomState(hash(kind) % 1000)
     T = _pairs(kind, 60000, rs)
@@ -53,6 +71,8 @@ def test_filter_never_contradicts_the_exact_predicate(kind, oracle_mod):
     assert np.array_equal(exact[sub], want)           # the exact predicate is the oracle's SAT-17, bit for bit
     if kind in ("random", "near"):
         assert (filt != 2).mean() > 0.99              # ... and generic pairs are decided in fp32
+    if kind == "thin":
+        assert (filt != 2).mean() > 0.9               # ... and so are long thin triangles (one L^4 bound left half open)
 
 
 def test_predicate_known_answers():
