@@ -701,6 +701,44 @@ def test_swept_windows_leave_every_output_unchanged(which, vd, n, monkeypatch):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("which,vd,resolve,rmax", [("wt2", 0.0125 / 8, "4096", "1"), ("wt2", 1.5164e-5, "64", "1"),
+                                                   ("wt2", 2e-4, "100000", "1"), ("org", 1.5164e-5, "2048", "1e-3"),
+                                                   ("org", 0.0125 / 8, "512", "1")])
+def test_windows_that_keep_pairs_leave_every_output_unchanged(which, vd, resolve, rmax, monkeypatch):
+    """A swept window may KEEP the triangle pairs it cannot clear and have its steps decided by the exact predicate
+    on exactly those pairs (windows that keep pairs).  With the gates forced wide open (every window
+    keeps pairs, also wide ones resolved in several 32-step chunks, also at the coarse verify_delta where a window
+    keeps a hundred pairs) the six outputs equal those of the walk that splits such windows (OSR_SWEEP_RESOLVE=0)
+    and of the walk that traverses every step, bit for bit."""
+    import os
+    from puzzletunneldiscovery_b200 import pyosr
+    centre = W.ROB_OMPL_CENTER if which == "wt2" else None
+    monkeypatch.setenv("OSR_SWEEP_TILES", "0")
+    plain = make_world(pyosr.UnitWorld, which, centre)
+    monkeypatch.delenv("OSR_SWEEP_TILES")
+    monkeypatch.setenv("OSR_SWEEP_RESOLVE", "0")
+    split = make_world(pyosr.UnitWorld, which, centre)
+    monkeypatch.setenv("OSR_SWEEP_RESOLVE", resolve)
+    monkeypatch.setenv("OSR_SWEEP_KEEP_RMAX", rmax)
+    keep = make_world(pyosr.UnitWorld, which, centre)
+    if which == "wt2":
+        tv = np.load(os.path.join(W.assets_dir(), "alpha-1.2.org.tunnel-more.npz"))["TUNNEL_V"]
+        fr, to = W.touch_rays(keep.translate_to_unit_states(tv), 1024 if vd < 1e-4 else 4096, seed=95)
+    else:
+        q = W.random_states(1 << 14, seed=96)
+        ok = q[keep.is_valid_states(q) & ~keep.is_disentangled_states(q)][:256]
+        fr, to = W.touch_rays(ok, 1024 if vd < 1e-4 else 4096, seed=97)
+    a = keep.transit_states_to_with_contact(fr, to, vd, with_steps=True)
+    kept_leaf = keep.counters(reset=True)["leaf_tests"]
+    b = split.transit_states_to_with_contact(fr, to, vd, with_steps=True)
+    split_leaf = split.counters(reset=True)["leaf_tests"]
+    c = plain.transit_states_to_with_contact(fr, to, vd, with_steps=True)
+    for x, y, z in zip(a, b, c):
+        assert np.array_equal(x, y) and np.array_equal(x, z)
+    assert (~a[2]).any() and kept_leaf != split_leaf     # walks end in contacts, and the listed path did run
+
+
+@pytest.mark.gpu
 def test_swept_windows_on_deep_trees(monkeypatch):
     """Same equality on a subdivided alpha puzzle (64 512 x 36 288 triangles: trees too large for shared memory,
     deeper work stacks): swept windows on = every step traversed, outputs bit-identical."""
