@@ -845,9 +845,22 @@ static int valid_states_host_impl(osr_world* w, const T* q, int64_t n, uint8_t* 
       CU(cudaStreamWaitEvent(s.stream3, s.evp, 0));
       CU(cudaMemsetAsync(s.ready, 0, sizeof(long long), s.stream3));
       StreamWriteValue64 wv = stream_write_value64();
+      // Chunk schedule.  The kernel is faster than the upload, so the call costs (upload) + (kernel work on the LAST
+      // chunk) + (a few us of event / flag traffic per chunk): uniform 64 Ki chunks paid 16 of those gaps and 30 us
+      // of tail.  Default: a first chunk of 64 Ki states (the kernel starts behind it; with float32 states the upload
+      // is no faster than the kernel and a late start would show), then every chunk is half of what is left, down
+      // to 8 Ki states -- 9 chunks for 2^20 states.  OSR_HOST_CHUNK set = uniform chunks of that size (A/B).
+      static const bool uniform_chunks = getenv("OSR_HOST_CHUNK") != nullptr;
+      const int64_t min_chunk = 8192;
+      int64_t first_len = 0;
       int c = 0;
-      for (int64_t c0 = 0; c0 < m; c0 += ck, c++) {
-        int64_t len = std::min(ck, m - c0);
+      for (int64_t c0 = 0, len = 0; c0 < m; c0 += len, c++) {
+        if (uniform_chunks || c == MAX_FEED_CHUNKS - 1) len = c == MAX_FEED_CHUNKS - 1 ? m - c0 : std::min(ck, m - c0);
+        else {
+          len = c == 0 ? std::min<int64_t>(65536, m) : std::max(min_chunk, ((m - c0) / 2 + 1023) / 1024 * 1024);
+          if (m - c0 - len < min_chunk / 2) len = m - c0;
+        }
+        if (c == 0) first_len = len;
         if (!s.feed_ev[c]) CU(cudaEventCreateWithFlags(&s.feed_ev[c], cudaEventDisableTiming));
         CU(cudaMemcpyAsync((T*)s.in0.p + 7 * c0, q + 7 * (lo + c0), (size_t)len * 7 * sizeof(T), cudaMemcpyHostToDevice, s.stream2));
         CU(cudaEventRecord(s.feed_ev[c], s.stream2));
@@ -860,7 +873,7 @@ static int valid_states_host_impl(osr_world* w, const T* q, int64_t n, uint8_t* 
       const bool wait_all = wait_all_env || safe;
       CU(cudaStreamWaitEvent(s.stream, s.feed_ev[wait_all ? c - 1 : 0], 0));
       rc = launch_valid_feed<T>(w, s, (const T*)s.in0.p, m, (uint8_t*)s.out[0].p, s.ready,
-                                (long long)(wait_all ? m : std::min(ck, m)));  // the launch waits for that event
+                                (long long)(wait_all ? m : first_len));  // the launch waits for that event
       if (rc) return rc;
       CU(cudaMemcpyAsync(out + lo, s.out[0].p, (size_t)m, cudaMemcpyDeviceToHost, s.stream));
       CU(cudaEventRecord(s.evq, s.stream3));
