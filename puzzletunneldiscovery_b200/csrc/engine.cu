@@ -570,7 +570,18 @@ static bool launches_may_block() {
     if (lb && atoi(lb) != 0) return true;
     const char* inj = getenv("CUDA_INJECTION64_PATH");
     if (inj && *inj) return true;
-    return getenv("OSR_FEED_SAFE") != nullptr;
+    if (getenv("OSR_FEED_SAFE") != nullptr) return true;
+    // Nsight Compute injects its interceptor without that variable; a kernel it replays sees the `ready` word of
+    // the first pass again and would wait out the feed timeout in every pass (observed: 40 passes x 20 s)
+    if (FILE* f = fopen("/proc/self/maps", "r")) {
+      char line[512];
+      bool hit = false;
+      while (!hit && fgets(line, sizeof line, f))
+        hit = strstr(line, "InjectionTarget") || strstr(line, "nsight-compute") || strstr(line, "cuda-injection");
+      fclose(f);
+      if (hit) return true;
+    }
+    return false;
   }();
   return v;
 }
