@@ -791,6 +791,23 @@ def test_pinned_host_arrays_give_the_same_labels(uw_org):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("n", [65536, 65537, 69631, 73729, 131071, 200003, 1048576 + 4097])
+def test_host_call_chunk_schedule_ragged_sizes(uw_org, n):
+    """The host validity call uploads in chunks (64 Ki states, then half of what is left, down to 8 Ki) under ONE
+    stream-fed kernel: whatever the batch size does to the schedule -- a single chunk, a one-state second chunk, a
+    remainder folded into the last chunk -- page-locked and pageable float64 samples and float32 samples give the
+    labels of one batch of small single-chunk calls."""
+    from puzzletunneldiscovery_b200 import pyosr
+    q = W.random_states(n, seed=98)
+    want = np.concatenate([uw_org.is_valid_states(q[i:i + 32768]) for i in range(0, n, 32768)])
+    assert np.array_equal(uw_org.is_valid_states(q), want)                        # pageable float64
+    qp = pyosr.pinned_empty((n, 7)); qp[:] = q
+    assert np.array_equal(uw_org.is_valid_states(qp), want)                       # page-locked float64
+    assert np.array_equal(uw_org.is_valid_states(q.astype(np.float32)), want)     # float32 (the states ARE float32 values)
+    del qp
+
+
+@pytest.mark.gpu
 def test_clearance_stats_edge_cases(uw_org, ow_org, oracle_mod):
     """One and two points per candidate (median = the value / the mean of both), targets closer than one step
     (the walk does not move: distance 0), an empty batch, and bad arguments raising like every other call."""
