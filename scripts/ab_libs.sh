@@ -1,4 +1,6 @@
-# usage: _ab.sh TAG...   ("base" = product library): segment legs + parity subset per library
+#!/bin/bash
+# A/B of development builds (build.py --variant TAG ...): parity tests + segment legs per library, same box, same run.
+# usage: scripts/ab_libs.sh TAG...   ("base" = the product library)
 for v in "$@"; do
   if [ "$v" != base ]; then export OSR_LIB=$PWD/puzzletunneldiscovery_b200/libosrgpu_$v.so; else unset OSR_LIB; fi
   echo "== variant '$v'"
