@@ -30,6 +30,49 @@ def test_validity_golden_fixtures(uw_org, uw_wt2):
     assert abs(uw_wt2.scene_scale - float(g2["scene_scale"])) == 0.0
 
 
+def test_reference_known_answers_through_the_engine(uw_wt2, ow_org_centred):
+    """SURVEY 8(c) C7, asked of the ENGINE through the drop-in module (tests/test_oracle_known_answers.py asks the
+    same of the oracle): the reference's own fixtures and the answers its scripts expect."""
+    import os
+    from conftest import ASSETS
+    from puzzletunneldiscovery_b200 import pyosr
+    # (2) src/RL/test_collide.py:40-43 on res/alpha/env-1.2.obj + robot.obj (no scaleToUnit there): "Expecting True"
+    w = pyosr.UnitWorld()
+    w.loadModelFromFile(os.path.join(ASSETS, "env-1.2.obj"))
+    w.loadRobotFromFile(os.path.join(ASSETS, "robot.obj"))
+    w.angleModel(0.0, 0.0)
+    q = np.array([[0.04, 0, 0, .5, .5, .5, .5], [0.7, 0, 0, .5, .5, .5, .5]])
+    assert w.is_valid_states(q).tolist() == [True, True]
+    assert w.is_valid_state(q[0]) and w.is_valid_state(q[1])
+    # (3) res/alpha/alpha-1.2.org.path (81 OMPL states, w last) and alpha-1.2.org.w-first.npz['VS']: every solution
+    # vertex is valid on G-org and on G-wt2 with the robot centre of the OMPL problem (preprocess_key.py:129-133);
+    # consecutive vertices connect at the pipeline's resolution exactly where the oracle says they do
+    uc = make_world(pyosr.UnitWorld, "org", W.ROB_OMPL_CENTER)
+    P = np.loadtxt(os.path.join(ASSETS, "alpha-1.2.org.path"))
+    for u in (uc, uw_wt2):
+        up = np.concatenate([P[:, :3] * u.scene_scale, P[:, 6:7], P[:, 3:6]], axis=1)
+        assert len(up) == 81 and u.is_valid_states(up).all()
+    up = np.concatenate([P[:, :3] * uc.scene_scale, P[:, 6:7], P[:, 3:6]], axis=1)
+    vd = uc.scene_scale * 0.001
+    ok = uc.is_valid_transitions(up[:-1], up[1:], vd)
+    assert np.array_equal(ok, ow_org_centred.is_valid_transitions(up[:-1], up[1:], vd).astype(bool)) and ok.mean() > 0.9
+    wf = np.load(os.path.join(ASSETS, "alpha-1.2.org.w-first.npz"))["VS"]
+    assert uc.is_valid_states(np.concatenate([wf[:, :3] * uc.scene_scale, wf[:, 3:]], axis=1)).all()
+    # (4) TUNNEL_V of alpha-1.2.org.tunnel.npz / tunnel-more.npz: valid narrow-tunnel states on G-wt2, the from-states
+    # of the reference's touch sampling (condor_touch_configuration.py:71-92), through translate_to_unit_state
+    for f in ("alpha-1.2.org.tunnel.npz", "alpha-1.2.org.tunnel-more.npz"):
+        tv = np.load(os.path.join(ASSETS, f))["TUNNEL_V"]
+        assert uw_wt2.is_valid_states(uw_wt2.translate_to_unit_states(tv)).all()
+    # (5) the run-time invariant of transitStateTo (unit_world.cc:325-326): the returned state is valid
+    tv = np.load(os.path.join(ASSETS, "alpha-1.2.org.tunnel.npz"))["TUNNEL_V"]
+    fr, to = W.touch_rays(uw_wt2.translate_to_unit_states(tv), 2048, seed=99)
+    lf, fh, isf, ft, tt = uw_wt2.transit_states_to_with_contact(fr, to, VD_TOUCH)
+    assert uw_wt2.is_valid_states(lf).all() and not uw_wt2.is_valid_states(fh[~isf & (tt > 0)]).any()
+    nq, free, tau = uw_wt2.transit_state_to(fr[0], to[0], VD_TOUCH)
+    # (the single-state call returns tau as a C float, like the reference's std::tuple<StateVector, bool, float>)
+    assert np.array_equal(nq, lf[0]) and bool(free) == bool(isf[0]) and tau == float(np.float32(ft[0]))
+
+
 @pytest.mark.parametrize("which,n,seed", [("org", 1 << 16, 11), ("wt2", 1 << 15, 12)])
 def test_validity_matches_oracle_bit_exact(which, n, seed, uw_org, uw_wt2, ow_org, ow_wt2):
     uw, ow = (uw_org, ow_org) if which == "org" else (uw_wt2, ow_wt2)
