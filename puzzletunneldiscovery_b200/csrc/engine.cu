@@ -84,6 +84,7 @@ struct Slot {  // one GPU
   unsigned long long* work = nullptr;   // [0] tile queue, [1] contact record count, [2..] queues of pipelined chunks
   unsigned long long* spill = nullptr;
   int* err = nullptr;
+  int* h_err = nullptr;                 // pinned landing word of the error flag (one small async copy per call)
   int grid_valid = 0, grid_transit = 0, grid_contacts = 0;
   int spill_cap = 0;
   DevBuf in0, in1, vd, out[6], recs, rowrec, seg, faces, cop, bary;
@@ -190,6 +191,7 @@ void free_slot(Slot& s) {
   cudaFree(s.ready);
   if (s.stage) cudaFreeHost(s.stage);
   if (s.h_ready) cudaFreeHost(s.h_ready);
+  if (s.h_err) cudaFreeHost(s.h_err);
   for (auto& e : s.feed_ev) if (e) cudaEventDestroy(e);
   if (s.stream3) cudaStreamDestroy(s.stream3);
   if (s.stream2) cudaStreamDestroy(s.stream2);
@@ -225,6 +227,7 @@ int init_slot(osr_world* w, Slot& s, int dev) {
   CU(cudaMalloc((void**)&s.work, WORK_SLOTS * sizeof(unsigned long long)));
   CU(cudaMalloc((void**)&s.err, sizeof(int)));
   CU(cudaMemset(s.err, 0, sizeof(int)));
+  CU(cudaHostAlloc((void**)&s.h_err, sizeof(int), cudaHostAllocDefault));
   // persistent grid: as many blocks as fit, on every SM
   CU(cudaFuncSetAttribute(osr::k_is_valid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_PER_BLOCK));
   CU(cudaFuncSetAttribute(osr::k_ompl_motion, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_PER_BLOCK));
@@ -335,9 +338,9 @@ int check_ready(osr_world* w) {
 
 thread_local bool g_feed_timed_out = false;   // set when a stream-fed K1 launch gave up waiting for its input
 int check_device_error(osr_world* w, Slot& s) {
-  int flag = 0;
-  CU(cudaMemcpyAsync(&flag, s.err, sizeof(int), cudaMemcpyDeviceToHost, s.stream));
+  CU(cudaMemcpyAsync(s.h_err, s.err, sizeof(int), cudaMemcpyDeviceToHost, s.stream));
   CU(cudaStreamSynchronize(s.stream));
+  const int flag = *s.h_err;
   if (flag) {
     cudaMemsetAsync(s.err, 0, sizeof(int), s.stream);
     if (flag == 2) {

@@ -1,0 +1,44 @@
+#!/usr/bin/env python
+"""Latency of small host calls through the C ABI (what a planner that asks one state at a time pays)."""
+import ctypes as C
+import os
+import sys
+import time
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import bench  # noqa: E402
+from puzzletunneldiscovery_b200 import pyosr, workloads as W  # noqa: E402
+from puzzletunneldiscovery_b200._lib import check  # noqa: E402
+
+uw = bench.make_world(pyosr.UnitWorld)
+L, h = uw._L, uw._h
+q = W.random_states(1 << 16, 0)
+out = np.empty(1 << 16, np.uint8)
+for n in (1, 32, 1024, 16384, 65536):
+    qq = np.ascontiguousarray(q[:n])
+    fn = lambda: check(L.osr_is_valid_states(h, qq.ctypes.data_as(C.POINTER(C.c_double)), n, out.ctypes.data_as(C.POINTER(C.c_uint8))))
+    for _ in range(20):
+        fn()
+    reps = 300
+    t = time.perf_counter()
+    for _ in range(reps):
+        fn()
+    dt = (time.perf_counter() - t) / reps
+    print("osr_is_valid_states n=%6d: %8.1f us per call  (%.3e configs/s)" % (n, dt * 1e6, n / dt))
+v = uw.is_valid_states(q[:4096])
+fr, to = W.touch_rays(q[:4096][v][:64], 64, seed=1)
+for n in (1, 64):
+    a, b = np.ascontiguousarray(fr[:n]), np.ascontiguousarray(to[:n])
+    fn = lambda: uw.transit_states_to_with_contact(a, b, 0.0125 / 8)
+    for _ in range(10):
+        fn()
+    t = time.perf_counter()
+    for _ in range(100):
+        fn()
+    print("transit_states_to_with_contact n=%3d: %8.1f us per call" % (n, (time.perf_counter() - t) / 100 * 1e6))
+t = time.perf_counter()
+for i in range(300):
+    uw.is_valid_state(q[i])
+print("pyosr.is_valid_state (one state, Python): %.1f us per call" % ((time.perf_counter() - t) / 300 * 1e6))
