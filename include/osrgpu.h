@@ -227,6 +227,17 @@ int osr_transit_states_device(osr_world* w, const double* d_from, const double* 
                               double* d_free_tau, double* d_touch_tau, int64_t* d_steps);
 int osr_is_valid_transitions_device(osr_world* w, const double* d_from, const double* d_to, int64_t n,
                                     double initial_verify_delta, uint8_t* d_out);
+/* Allocation-free variant of osr_is_valid_transitions_device.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same kernel and labels; the kernel's scratch (work-queue word, per-warp spill
+ * areas of the traversal stack: 1 024 entries per warp instead of 8 192) lives in a static device array of
+ * 16 MiB + 256 B that every GPU loading the library holds until exit.  The call allocates nothing (no cudaMalloc /
+ * cudaFree, no allocating library routine); at most OSR_NOALLOC_MAX_SEGMENTS segments per call, more is OSR_EINVAL.
+ * All calls on one GPU share the array: calls that overlap on the GPU (two handles, two processes' worth of streams)
+ * race -- serialise them.  Launch only, like the other *_device calls: osr_sync() surfaces a spill overflow. */
+#define OSR_NOALLOC_MAX_SEGMENTS (1 << 22)
+int osr_is_valid_transitions_device_noalloc(osr_world* w, const double* d_from, const double* d_to, int64_t n,
+                                            double initial_verify_delta, uint8_t* d_out);
 void* osr_stream(osr_world* w);   /* cudaStream_t of device slot 0 */
 int osr_sync(osr_world* w);
 /* elapsed GPU milliseconds of the most recent *_device launch on slot 0 (CUDA events recorded

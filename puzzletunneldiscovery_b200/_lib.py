@@ -83,6 +83,8 @@ SIGNATURES = {
                                   [C.c_void_p] * 6),
     "osr_is_valid_transitions_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_double,
                                                   C.c_void_p]),
+    "osr_is_valid_transitions_device_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_double,
+                                                          C.c_void_p]),
     "osr_stream": (C.c_void_p, [C.c_void_p]),
     "osr_sync": (C.c_int, [C.c_void_p]),
     "osr_last_kernel_ms": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),

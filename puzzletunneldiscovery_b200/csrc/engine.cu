@@ -26,6 +26,17 @@
 #include "kernels_clearance.cuh"
 #include "kernels_keyconf.cuh"
 
+// Scratch of the allocation-free entry point osr_is_valid_transitions_device_noalloc (end of this file): the work-queue
+// word of K2 and its per-warp traversal-stack spill areas.  File scope, in every GPU's memory that loads the library
+// until the process exits: 256 B + 2048 warps x 1024 entries x 8 B = 16 MiB + 256 B.  In HOST code this name is a
+// host-side stand-in, not a device address: init_slot asks cudaGetSymbolAddress for the address on each device.
+#define OSR_NOALLOC_HEADER_BYTES 256
+#define OSR_NOALLOC_MAX_WARPS 2048
+#define OSR_NOALLOC_SPILL_CAP 1024
+#define OSR_NOALLOC_SCRATCH_BYTES \
+  ((size_t)OSR_NOALLOC_HEADER_BYTES + (size_t)OSR_NOALLOC_MAX_WARPS * OSR_NOALLOC_SPILL_CAP * sizeof(unsigned long long))
+static __device__ __align__(256) unsigned char g_noalloc_scratch[OSR_NOALLOC_SCRATCH_BYTES];
+
 namespace {
 
 thread_local std::string g_err;
@@ -85,6 +96,7 @@ struct Slot {  // one GPU
   unsigned long long* spill = nullptr;
   int* err = nullptr;
   int* h_err = nullptr;                 // pinned landing word of the error flag (one small async copy per call)
+  unsigned char* noalloc = nullptr;     // device address of g_noalloc_scratch on this GPU (cudaGetSymbolAddress)
   int grid_valid = 0, grid_transit = 0, grid_contacts = 0;
   int spill_cap = 0;
   DevBuf in0, in1, vd, out[6], recs, rowrec, seg, faces, cop, bary;
@@ -228,6 +240,7 @@ int init_slot(osr_world* w, Slot& s, int dev) {
   CU(cudaMalloc((void**)&s.err, sizeof(int)));
   CU(cudaMemset(s.err, 0, sizeof(int)));
   CU(cudaHostAlloc((void**)&s.h_err, sizeof(int), cudaHostAllocDefault));
+  CU(cudaGetSymbolAddress((void**)&s.noalloc, g_noalloc_scratch));   // this device's copy of the static scratch
   // persistent grid: as many blocks as fit, on every SM
   CU(cudaFuncSetAttribute(osr::k_is_valid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_PER_BLOCK));
   CU(cudaFuncSetAttribute(osr::k_ompl_motion, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_PER_BLOCK));
@@ -1061,6 +1074,52 @@ int osr_is_valid_transitions_device(osr_world* w, const double* d_from, const do
   CU(cudaSetDevice(s.dev));
   osr::SegOut O = {nullptr, nullptr, d_out, nullptr, nullptr, nullptr};
   return launch_transit(w, s, d_from, d_to, n, nullptr, 1, initial_verify_delta, 1, O);
+}
+
+// Allocation-free variant of osr_is_valid_transitions_device (no counterpart in the reference; added
+// for callers that cannot allocate: CUDA graph capture, tight serving loops).  Same kernel, same
+// labels; K2's scratch -- the work-queue word and the per-warp spill areas of the traversal stack -- lives in the
+// static array g_noalloc_scratch instead of the handle's cudaMalloc'ed buffers.  Calls no cudaMalloc / cudaFree and
+// no allocating library routine: a memset of the 256-byte header, two event records, one launch.  Every call (of every
+// handle in the process) on one GPU shares the array: calls that overlap on that GPU race.
+int osr_is_valid_transitions_device_noalloc(osr_world* w, const double* d_from, const double* d_to, int64_t n,
+                                            double initial_verify_delta, uint8_t* d_out) {
+  int rc = check_ready(w);
+  if (rc) return rc;
+  if (initial_verify_delta < 0.0) return fail(OSR_EINVAL, "verify_delta must not be negative");
+  if (n < 0 || (n > 0 && (!d_from || !d_to || !d_out))) return fail(OSR_EINVAL, "bad arguments");
+  if (n > (int64_t)OSR_NOALLOC_MAX_SEGMENTS)
+    return fail(OSR_EINVAL, "osr_is_valid_transitions_device_noalloc: more than OSR_NOALLOC_MAX_SEGMENTS (" +
+                                std::to_string((long long)OSR_NOALLOC_MAX_SEGMENTS) + ") segments in one call");
+  if (n == 0) return OSR_OK;
+  std::lock_guard<std::mutex> lk(w->mu);
+  Slot& s = w->slots[0];
+  CU(cudaSetDevice(s.dev));
+  if (!s.noalloc) return fail(OSR_ECUDA, "static scratch not resolved on this device");
+  if ((size_t)s.grid_transit * osr::WARPS_PER_BLOCK > (size_t)OSR_NOALLOC_MAX_WARPS)
+    return fail(OSR_EOVERFLOW, "osr_is_valid_transitions_device_noalloc: the launch grid has more warps than the static "
+                               "scratch holds spill areas for");
+  osr::KParams P = w->params(s);   // error flag and counters stay the handle's (osr_sync, osr_get_counters)
+  P.work_counter = reinterpret_cast<unsigned long long*>(s.noalloc);
+  P.spill = reinterpret_cast<unsigned long long*>(s.noalloc + OSR_NOALLOC_HEADER_BYTES);
+  P.spill_cap = OSR_NOALLOC_SPILL_CAP;
+  // the array keeps the last call's contents: the queue word must start at zero, the spill areas need no clearing
+  CU(cudaMemsetAsync(s.noalloc, 0, OSR_NOALLOC_HEADER_BYTES, s.stream));
+  osr::SegOut O = {nullptr, nullptr, d_out, nullptr, nullptr, nullptr};
+  CU(cudaEventRecord(s.ev0, s.stream));
+  if (s.transit_minb == 4)
+    osr::k_transit<4><<<s.grid_transit, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK, s.stream>>>(
+        P, d_from, d_to, (long long)n, nullptr, 1LL, initial_verify_delta, 1, O);
+  else if (s.transit_minb == 3)
+    osr::k_transit<3><<<s.grid_transit, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK, s.stream>>>(
+        P, d_from, d_to, (long long)n, nullptr, 1LL, initial_verify_delta, 1, O);
+  else
+    osr::k_transit<2><<<s.grid_transit, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK, s.stream>>>(
+        P, d_from, d_to, (long long)n, nullptr, 1LL, initial_verify_delta, 1, O);
+  CU(cudaGetLastError());
+  CU(cudaEventRecord(s.ev1, s.stream));
+  w->host_counters.kernel_launches++;
+  return OSR_OK;
 }
 
 // Page-locked host memory for sample / result arrays: a host call whose buffers are pageable is bounded by the
