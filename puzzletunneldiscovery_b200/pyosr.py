@@ -717,6 +717,65 @@ class UnitWorld:
         return q[0][valid[0]]
 
     # ---- state-frame maps (module.cc:157-169) ----------------------------------------------------
+    def enum_2drot_free_configuration(self, rob_surface_point, rob_surface_normal, rob_prim_id, env_surface_point,
+                                      env_surface_normal, env_prim_id, margin, azimuth_divider, altitude_divider,
+                                      return_all=False, enable_mt=True):
+        """UnitWorld::enum2DRotationFreeConfiguration (unit_world.cc:1391-1523), restated with its quirks because
+        src/GP/pipeline/keyconf.py:244 consumes exactly this output: the azimuth step is 2 pi / ALTITUDE_divider
+        (:1435), validity is stubbed to 1 in the reference (:1471-1476: no collision query is issued, so there is
+        nothing for the GPU to do), and the connected-component pass indexes `valids` and `qs` by the altitude ROW
+        (:1493, :1517).  Host only (numpy, Eigen 3.3 semantics).  enable_mt only gated the stubbed loop."""
+        rp = np.asarray(rob_surface_point, np.float64); rn = np.asarray(rob_surface_normal, np.float64)
+        ep = np.asarray(env_surface_point, np.float64); en = np.asarray(env_surface_normal, np.float64)
+        Vr, Fr = self._geometry(self.GEO_ROB)
+        Ve, Fe = self._geometry(self.GEO_ENV)
+        rob_v = Vr[Fr[int(rob_prim_id)]]
+        env_v = Ve[Fe[int(env_prim_id)]]
+        tan_env = env_v[1] - env_v[0]
+        nt = np.linalg.norm(tan_env)
+        if nt > 0:
+            tan_env = tan_env / nt
+        az, al = int(azimuth_divider), int(altitude_divider)
+        env_o = ep + en * margin
+        rot_1 = _quat_from_two_vectors(rn, -en)
+
+        def aa_quat(angle, axis):     # Eigen Quaternion(AngleAxis): the axis is used as given
+            return np.concatenate([[np.cos(0.5 * angle)], np.sin(0.5 * angle) * axis])
+        qs = np.zeros((az * al, 7))
+        d_alt = 0.5 * np.pi / float(al)
+        d_azi = 2.0 * np.pi / float(al)
+        for i in range(al):
+            rot_2 = aa_quat(i * d_alt, tan_env)
+            acc = _quat_mul(rot_2, rot_1)
+            align = env_o - _quat_rotate(acc, rp)
+            pen = min(float(en @ (_quat_rotate(acc, rob_v[k]) + align - ep)) for k in range(3))
+            alt_margin = margin if pen > 0 else -pen + margin
+            alt_env_o = ep + en * alt_margin
+            for j in range(az):
+                acc3 = _quat_mul(_quat_mul(aa_quat(j * d_azi, en), rot_2), rot_1)
+                qs[i * az + j] = np.concatenate([alt_env_o - _quat_rotate(acc3, rp), _quat_normalized(acc3)])
+        valids = np.ones(az * al, np.int32)
+        if return_all:
+            return qs[valids != 0]
+        out = []
+        for i in range(al):
+            for j in range(az):
+                if not valids[i]:
+                    continue
+                queue = [i * az + j]
+                while queue:
+                    cur = queue.pop(0)
+                    ci, cj = cur // az, cur % az
+                    for dx in (-1, 1):
+                        for dy in (-1, 1):
+                            pi_, pj = (ci + dx + al) % al, (cj + dy + az) % az
+                            k = pi_ * az + pj
+                            if valids[k]:
+                                queue.append(k)
+                                valids[k] = 0
+                out.append(qs[i].copy())
+        return np.array(out).reshape(-1, 7)
+
     def _map(self, fn, qs):
         q = _states(qs)
         out = np.empty_like(q)

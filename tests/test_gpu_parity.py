@@ -850,6 +850,42 @@ def test_host_call_chunk_schedule_ragged_sizes(uw_org, n):
     del qp
 
 
+def test_enum_2drot_free_configuration_closed_form_properties(uw_org):
+    """enum2DRotationFreeConfiguration (unit_world.cc:1391-1523; validity is stubbed to 1 there, so the output is pure
+    geometry): every state puts the robot surface point on the pushed-out environment point, the first altitude row
+    aligns the normals, no vertex of the robot triangle ends up below the environment triangle's plane (:1443-1459), the
+    azimuth step is 2 pi / altitude_divider (the reference's own arithmetic), and the row-indexed component pass of
+    return_all=False returns altitude rows of the same table."""
+    from puzzletunneldiscovery_b200.pyosr import _quat_rotate, _angular_distance
+    Vr, Fr = uw_org._geometry(uw_org.GEO_ROB)
+    Ve, Fe = uw_org._geometry(uw_org.GEO_ENV)
+    rs = np.random.RandomState(5)
+    for trial in range(4):
+        rprim, eprim = int(rs.randint(len(Fr))), int(rs.randint(len(Fe)))
+        rt, et = Vr[Fr[rprim]], Ve[Fe[eprim]]
+        rp, ep = rt.mean(0), et.mean(0)
+        rn = np.cross(rt[1] - rt[0], rt[2] - rt[0]); rn /= np.linalg.norm(rn)
+        en = np.cross(et[1] - et[0], et[2] - et[0]); en /= np.linalg.norm(en)
+        margin, az, al = 1e-3, 5, 6
+        qs = uw_org.enum_2drot_free_configuration(rp, rn, rprim, ep, en, eprim, margin, az, al, return_all=True)
+        assert qs.shape == (az * al, 7) and np.abs(np.linalg.norm(qs[:, 3:], axis=1) - 1).max() < 1e-12
+        for i in range(al):
+            for j in range(az):
+                q = qs[i * az + j]
+                p = _quat_rotate(q[3:], rp) + q[:3]
+                depth = float(en @ (p - ep))
+                assert depth >= margin - 1e-12 and np.abs((p - ep) - en * depth).max() < 1e-12   # on the normal ray
+                tri = np.array([_quat_rotate(q[3:], v) + q[:3] for v in rt])
+                assert ((tri - ep) @ en).min() >= -1e-12       # the robot triangle stays on the outer side of the plane
+                if i == 0:
+                    assert np.abs(_quat_rotate(q[3:], rn) + en).max() < 1e-9                       # normals opposed
+                if j > 0:   # consecutive azimuth samples differ by a turn of 2 pi / altitude_divider about en
+                    turn = _angular_distance(q[3:], qs[i * az + j - 1][3:])
+                    assert abs(turn - 2 * np.pi / al) < 1e-9
+        some = uw_org.enum_2drot_free_configuration(rp, rn, rprim, ep, en, eprim, margin, az, al, return_all=False)
+        assert len(some) >= 1 and all(any(np.array_equal(r, qs[k]) for k in range(al)) for r in some)
+
+
 @pytest.mark.gpu
 def test_clearance_stats_edge_cases(uw_org, ow_org, oracle_mod):
     """One and two points per candidate (median = the value / the mean of both), targets closer than one step
