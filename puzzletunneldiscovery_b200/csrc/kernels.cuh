@@ -75,6 +75,7 @@ struct __align__(16) WarpShared {
   float eta[32];      // per-pose absolute inflation of box extents
   double tau[32];     // segment walk: tau of each step in the tile
   double seg[14];     // K2: end states of the segment the warp walks (from, to) -- warp-uniform, kept out of registers
+  SlerpPlan plan;     // K2: what osr::interpolate needs of them (normalised quaternions, arc angle, its sine)
   double envtf[12];   // K2: environment transform (R row-major, t)
 };
 
@@ -646,15 +647,13 @@ __device__ __forceinline__ unsigned test_kept_pairs(const KParams& P, WarpShared
   return hits;
 }
 
-// Pose slot `slot` := the walk's state at tau (osr::interpolate of the segment in S.seg) as the traversal wants it
-// (robot in the environment frame, fp64 + fp32 + box slack).  One copy per kernel: the slerp is ~400 instructions.
+// Pose slot `slot` := the walk's state at tau (osr::interpolate of the segment, prepared in S.plan) as the traversal
+// wants it (robot in the environment frame, fp64 + fp32 + box slack).  One copy per kernel.
 __device__ __noinline__ void seg_pose_at(int slot, double tau) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   WarpShared& S = reinterpret_cast<WarpShared*>(smem_raw)[threadIdx.x >> 5];
-  double a[7], b[7], s[7];
-#pragma unroll
-  for (int k = 0; k < 7; k++) { a[k] = S.seg[k]; b[k] = S.seg[7 + k]; }
-  interpolate(a, b, tau, s);
+  double s[7];
+  slerp_at(S.plan, tau, s);
   Rigid env, rob, rel;
 #pragma unroll
   for (int k = 0; k < 9; k++) env.R[k] = S.envtf[k];
@@ -674,14 +673,14 @@ __device__ __noinline__ void seg_pose_at(int slot, double tau) {
 __device__ __noinline__ void seg_write_state(double* __restrict__ dst, int which, double tau, int lane) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   WarpShared& S = reinterpret_cast<WarpShared*>(smem_raw)[threadIdx.x >> 5];
-  double a[7], b[7], s[7];
+  double s[7];
 #pragma unroll
-  for (int k = 0; k < 7; k++) { a[k] = S.seg[k]; b[k] = S.seg[7 + k]; }
-  if (which == 2) interpolate(a, b, tau, s);
+  for (int k = 0; k < 7; k++) s[k] = 0.0;
+  if (which == 2) slerp_at(S.plan, tau, s);
   double v = 0.0;
 #pragma unroll
   for (int k = 0; k < 7; k++) {
-    const double x = which == 0 ? a[k] : (which == 1 ? b[k] : s[k]);
+    const double x = which == 0 ? S.seg[k] : (which == 1 ? S.seg[7 + k] : s[k]);
     if (k == lane) v = x;
   }
   if (lane < 7) dst[lane] = v;
@@ -717,6 +716,13 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB)
       double a[7], b[7];
 #pragma unroll
       for (int k = 0; k < 7; k++) { a[k] = S.seg[k]; b[k] = S.seg[7 + k]; }
+      {   // once per segment; every pose of the walk reads it.  Computed by every lane (no per-lane branch around
+          // the libm calls), stored by one.
+        SlerpPlan pl;
+        slerp_prepare(a, b, pl);
+        if (lane == 0) S.plan = pl;
+        __syncwarp();
+      }
       dist = distance(a, b);
       const double tdx = a[0] - b[0], tdy = a[1] - b[1], tdz = a[2] - b[2];
       trans = sqrt(tdx * tdx + tdy * tdy + tdz * tdz);

@@ -67,28 +67,57 @@ OSR_HD void relative_rigid(const Rigid& env, const Rigid& rob, Rigid& o) {
   for (int i = 0; i < 3; i++) o.t[i] = env.R[i] * d0 + env.R[3 + i] * d1 + env.R[6 + i] * d2;
 }
 
-OSR_HD void interpolate(const double* a, const double* b, double tau, double* o) {
+// osr::interpolate (lib/osr/osr_state.cc:28-44: lerp of the translation, both quaternions normalised, Eigen 3.3 slerp)
+// in two parts: what depends on the two end states only (SlerpPlan) and what depends on tau.  interpolate() is their
+// composition, operation for operation, so a walk that prepares the plan once per segment gets the same bits as one
+// that calls interpolate() per step -- without two normalisations (2 sqrt, 8 divisions), acos and one sin per step.
+struct SlerpPlan {
+  double ta[3], tb[3];   // translations
+  double qa[4], qb[4];   // normalised quaternions (w, x, y, z)
+  double d;              // qa . qb
+  double th, st;         // acos|d| and its sine (unused when linear)
+  int linear;            // |d| >= 1 - eps: Eigen's slerp lerps the coefficients
+};
+
+OSR_HD void slerp_prepare(const double* a, const double* b, SlerpPlan& p) {
   double aw = a[3], ax = a[4], ay = a[5], az = a[6];
   double bw = b[3], bx = b[4], by = b[5], bz = b[6];
   quat_normalize(aw, ax, ay, az);
   quat_normalize(bw, bx, by, bz);
   const double one = 1.0 - 2.220446049250313e-16;
-  double d = ax * bx + ay * by + az * bz + aw * bw;
-  double ad = fabs(d);
+  p.d = ax * bx + ay * by + az * bz + aw * bw;
+  const double ad = fabs(p.d);
+  p.linear = ad >= one ? 1 : 0;
+  p.th = 0.0; p.st = 1.0;
+  if (!p.linear) {
+    p.th = acos(ad);
+    p.st = sin(p.th);
+  }
+  for (int k = 0; k < 3; k++) { p.ta[k] = a[k]; p.tb[k] = b[k]; }
+  p.qa[0] = aw; p.qa[1] = ax; p.qa[2] = ay; p.qa[3] = az;
+  p.qb[0] = bw; p.qb[1] = bx; p.qb[2] = by; p.qb[3] = bz;
+}
+
+OSR_HD void slerp_at(const SlerpPlan& p, double tau, double* o) {
   double s0, s1;
-  if (ad >= one) {
+  if (p.linear) {
     s0 = 1.0 - tau; s1 = tau;
   } else {
-    double th = acos(ad);
-    double st = sin(th);
-    s0 = sin((1.0 - tau) * th) / st;
-    s1 = sin(tau * th) / st;
+    s0 = sin((1.0 - tau) * p.th) / p.st;
+    s1 = sin(tau * p.th) / p.st;
   }
-  if (d < 0) s1 = -s1;
-  o[0] = a[0] * (1 - tau) + b[0] * tau;
-  o[1] = a[1] * (1 - tau) + b[1] * tau;
-  o[2] = a[2] * (1 - tau) + b[2] * tau;
-  o[3] = s0 * aw + s1 * bw; o[4] = s0 * ax + s1 * bx; o[5] = s0 * ay + s1 * by; o[6] = s0 * az + s1 * bz;
+  if (p.d < 0) s1 = -s1;
+  o[0] = p.ta[0] * (1 - tau) + p.tb[0] * tau;
+  o[1] = p.ta[1] * (1 - tau) + p.tb[1] * tau;
+  o[2] = p.ta[2] * (1 - tau) + p.tb[2] * tau;
+  o[3] = s0 * p.qa[0] + s1 * p.qb[0]; o[4] = s0 * p.qa[1] + s1 * p.qb[1];
+  o[5] = s0 * p.qa[2] + s1 * p.qb[2]; o[6] = s0 * p.qa[3] + s1 * p.qb[3];
+}
+
+OSR_HD void interpolate(const double* a, const double* b, double tau, double* o) {
+  SlerpPlan p;
+  slerp_prepare(a, b, p);
+  slerp_at(p, tau, o);
 }
 
 OSR_HD double distance(const double* a, const double* b) {
@@ -181,6 +210,14 @@ OSR_HD double bits_to_double(long long b) {
 #endif
 }
 OSR_HD long long imin64(long long a, long long b) { return a < b ? a : b; }
+// floor(a / b) for 0 <= a < 2^53, 0 < b < 2^53: both are exact doubles, the rounded quotient is off by at most one,
+// and two multiplications put it right -- the GPU has no 64-bit integer divide (a ~70-instruction subroutine).
+OSR_HD long long div53(long long a, long long b) {
+  long long q = (long long)((double)a / (double)b);
+  if (q * b > a) q--;
+  else if ((q + 1) * b <= a) q++;
+  return q;
+}
 
 // The reference's running sum over `ns` steps, d <- (d < dist) ? min(dist, d + vd) : d + vd, stopping at the first
 // value beyond dist -- with the result of every fp64 add reproduced exactly but not one add per step.  While d stays
@@ -201,16 +238,18 @@ OSR_HD int advance_chain(double& d, const double vd, const double dist, const in
       const double t = d + vd;
       const long long tb = dbits(t);
       if (e > 0 && e < 2046 && (int)(tb >> 52) == e && t <= dist) {   // normal, same binade, not past dist
-        const double x = scalbn(vd, 53 - (e - 1023));             // 2 vd / u
+        // 2 vd / u = vd 2^(53 - (e - 1023)), an exact scaling (x < 2^54 because t stays in d's binade); the power
+        // of two is built from its exponent bits (e >= 53 always holds for distances a walk can have)
+        const double x = e >= 53 ? vd * bits_to_double((long long)(2099 - e) << 52) : scalbn(vd, 53 - (e - 1023));
         const long long xi = (long long)x;
         const bool tie = x < 4.0e18 && (double)xi == x && (xi & 1);
         if (!tie) {
           D = (bits & 0xfffffffffffffLL) | (1LL << 52);
           Ci = ((tb & 0xfffffffffffffLL) | (1LL << 52)) - D;      // c / u  (> 0: t > d)
           if (Ci > 0) {                                           // (vd below half an ulp of d: the sum stalls)
-            long long kk = ((1LL << 53) - 1 - D) / Ci;            // stay inside the binade
+            long long kk = div53((1LL << 53) - 1 - D, Ci);        // stay inside the binade
             const long long db = dbits(dist);
-            if ((int)(db >> 52) == e) kk = imin64(kk, (((db & 0xfffffffffffffLL) | (1LL << 52)) - D) / Ci);   // <= dist
+            if ((int)(db >> 52) == e) kk = imin64(kk, div53(((db & 0xfffffffffffffLL) | (1LL << 52)) - D, Ci));   // <= dist
             k = (int)imin64(kk, (long long)left);
           }
         }
