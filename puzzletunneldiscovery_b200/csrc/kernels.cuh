@@ -835,7 +835,7 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB)
           // add / compare / select per step: with carry = 0 the first value is 0 + vd = vd exactly, and since the
           // sequence increases strictly, "every delta up to mine is <= dist" is just mine <= dist.
           double d = carry, mine = 0.0;
-#pragma unroll
+#pragma unroll 1   // (rolled: the chain is latency bound either way, and unrolled it was 525 instructions of cold code)
           for (int j = 0; j < 32; j++) {
             const double t = d + vd;
             d = (d < dist) ? fmin(dist, t) : t;

@@ -34,6 +34,20 @@ OSR_HD void quat_normalize(double& w, double& x, double& y, double& z) {
   }
 }
 
+// The same, out of line and by value, for per-segment code of the segment kernels: four fp64 divisions are ~100
+// instructions inline, a segment normalises four quaternions, and code size matters there.
+struct Quat4 { double w, x, y, z; };
+#if defined(__CUDACC__)
+static __host__ __device__ __noinline__
+#else
+inline
+#endif
+Quat4 quat_normalized(double w, double x, double y, double z) {
+  quat_normalize(w, x, y, z);
+  Quat4 q = {w, x, y, z};
+  return q;
+}
+
 OSR_HD void quat_mul(const double* a, const double* b, double* o) {  // (w,x,y,z)
   double w = a[0] * b[0] - a[1] * b[1] - a[2] * b[2] - a[3] * b[3];
   double x = a[0] * b[1] + a[1] * b[0] + a[2] * b[3] - a[3] * b[2];
@@ -80,10 +94,8 @@ struct SlerpPlan {
 };
 
 OSR_HD void slerp_prepare(const double* a, const double* b, SlerpPlan& p) {
-  double aw = a[3], ax = a[4], ay = a[5], az = a[6];
-  double bw = b[3], bx = b[4], by = b[5], bz = b[6];
-  quat_normalize(aw, ax, ay, az);
-  quat_normalize(bw, bx, by, bz);
+  const Quat4 qa = quat_normalized(a[3], a[4], a[5], a[6]), qb = quat_normalized(b[3], b[4], b[5], b[6]);
+  const double aw = qa.w, ax = qa.x, ay = qa.y, az = qa.z, bw = qb.w, bx = qb.x, by = qb.y, bz = qb.z;
   const double one = 1.0 - 2.220446049250313e-16;
   p.d = ax * bx + ay * by + az * bz + aw * bw;
   const double ad = fabs(p.d);
@@ -121,9 +133,8 @@ OSR_HD void interpolate(const double* a, const double* b, double tau, double* o)
 }
 
 OSR_HD double distance(const double* a, const double* b) {
-  double qa[4] = {a[3], a[4], a[5], a[6]}, qb[4] = {b[3], b[4], b[5], b[6]};
-  quat_normalize(qa[0], qa[1], qa[2], qa[3]);
-  quat_normalize(qb[0], qb[1], qb[2], qb[3]);
+  const Quat4 na = quat_normalized(a[3], a[4], a[5], a[6]), nb = quat_normalized(b[3], b[4], b[5], b[6]);
+  double qa[4] = {na.w, na.x, na.y, na.z}, qb[4] = {nb.w, nb.x, nb.y, nb.z};
   double dx = a[0] - b[0], dy = a[1] - b[1], dz = a[2] - b[2];
   double tr = sqrt(dx * dx + dy * dy + dz * dz);
   double cb[4] = {qb[0], -qb[1], -qb[2], -qb[3]}, d[4];
