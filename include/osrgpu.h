@@ -196,6 +196,14 @@ int osr_clearance_stats(osr_world* w, const double* q0, int64_t m, const double*
 int osr_knn_windowed(osr_world* w, const double* q, int64_t n, int k, int64_t window, int32_t* out_idx,
                      double* out_dist);
 
+/* osr_knn_windowed + osr_is_valid_transitions on the edges it finds, without building them: out_valid[n][k] = 1 iff
+ * is_valid_transition(q[i], q[out_idx[i][s]], initial_verify_delta) (unit_world.cc:477-486), 0 where out_idx is -1.
+ * The planners' pattern -- nearest neighbours, then checkMotion on every edge (lib/pyse3ompl/ompldriver.cc:176-260,
+ * RDT-forest edge validation of BASELINE config 3).  Only the milestones are uploaded.  out_idx optional.  Labels equal
+ * those of the two separate calls.  Runs on the handle's first device; n k < 2^31. */
+int osr_knn_validate_edges(osr_world* w, const double* q, int64_t n, int k, int64_t window, double initial_verify_delta,
+                           int32_t* out_idx, uint8_t* out_valid);
+
 /* Renderer::renderBarycentric (lib/osr/osr_render.cc:590-759, shaders lib/osr/shader/bary.{vert,geom,frag}) as a
  * headless rasteriser: primitive p has three vertices with uv[3p+v][2] (UV corners of its surface face),
  * bary[3p+v][3] and weight[3p+v]; vertex v is drawn at sum_k uv[3p+k]*bary[3p+v][k] in a res_x x res_y chart,

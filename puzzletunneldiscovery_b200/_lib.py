@@ -63,6 +63,7 @@ SIGNATURES = {
     "osr_ompl_validate_states": (C.c_int, [C.c_void_p, c_dp, C.c_int64, c_dp, c_u8p]),
     "osr_ompl_check_motions": (C.c_int, [C.c_void_p, c_dp, c_dp, C.c_int64, c_dp, C.c_double, c_u8p, c_i64p]),
     "osr_knn_windowed": (C.c_int, [C.c_void_p, c_dp, C.c_int64, C.c_int, C.c_int64, c_i32p, c_dp]),
+    "osr_knn_validate_edges": (C.c_int, [C.c_void_p, c_dp, C.c_int64, C.c_int, C.c_int64, C.c_double, c_i32p, c_u8p]),
     "osr_clearance_stats": (C.c_int, [C.c_void_p, c_dp, C.c_int64, c_dp, C.c_int, C.c_double, c_dp, c_dp]),
     "osr_enum_free_configurations": (C.c_int, [C.c_void_p, c_dp, C.c_int64, C.c_double, C.c_int, C.c_int, c_dp, c_u8p,
                                                c_i32p]),

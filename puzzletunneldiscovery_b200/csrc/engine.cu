@@ -667,7 +667,7 @@ static int launch_transit(osr_world* w, Slot& s, const double* d_from, const dou
   // K2 default = the tile kernel: on every measured segment workload (profiles/r01/README.md) the warp-shared
   // frontier keeps all 32 lanes busy on the mostly FREE steps of a walk, where depth-first early exit buys nothing.
   // OSR_SEG_KERNEL=dfs selects the lane-owned depth-first variant (kernels_seg.cuh) for A/B runs.
-  if (s.seg_warps > 0 && w->seg_dfs) {
+  if (s.seg_warps > 0 && w->seg_dfs && !O.to_idx) {   // (indexed segments exist in the tile kernel only)
     osr::DfsParams D = dfs_params(w, s);
     D.env_smem_nodes = s.seg_env_smem; D.rob_smem_nodes = s.seg_rob_smem;
     osr::SegArgs A = {d_from, d_to, (long long)n, d_vd, (long long)vd_count, vd_scalar, transition_mode, O};
@@ -1571,6 +1571,40 @@ int osr_knn_windowed(osr_world* w, const double* q, int64_t n, int k, int64_t wi
   if (out_dist) CU(cudaMemcpyAsync(out_dist, s.seg.p, (size_t)n * k * 8, cudaMemcpyDeviceToHost, s.stream));
   CU(cudaStreamSynchronize(s.stream));
   return OSR_OK;
+}
+
+// ---- k-NN edges validated where they are --------------------------------------
+// The planners' pattern (GNAT k-NN, then checkMotion on every edge found: lib/pyse3ompl/ompldriver.cc:176-260) and
+// config 3 of BASELINE.json in one call: K6 leaves the neighbour indices on the device and K2 walks edge
+// (i, idx[i][s]) straight from the milestone array.  56 bytes per milestone go up, k (4 + 1) bytes come back; the
+// (from, to) arrays of the edges -- 112 bytes per edge, 3.7 GB for 4M milestones x 8 -- are never built or moved.
+int osr_knn_validate_edges(osr_world* w, const double* q, int64_t n, int k, int64_t window, double initial_verify_delta,
+                           int32_t* out_idx, uint8_t* out_valid) {
+  int rc = check_ready(w);
+  if (rc) return rc;
+  if (n < 0 || (n > 0 && (!q || !out_valid)) || k <= 0 || k > osr::KNN_KMAX || window <= 0 ||
+      window % osr::KNN_TILE != 0 || n > 0x7fffffffLL / osr::KNN_KMAX)
+    return fail(OSR_EINVAL, "bad arguments (1 <= k <= 16, window a positive multiple of 256, n k < 2^31)");
+  if (initial_verify_delta < 0.0) return fail(OSR_EINVAL, "verify_delta must not be negative");
+  if (n == 0) return OSR_OK;
+  std::lock_guard<std::mutex> lk(w->mu);
+  Slot& s = w->slots[0];
+  CU(cudaSetDevice(s.dev));
+  const int64_t m = n * k;
+  CU(s.in0.need((size_t)n * 56));
+  CU(s.faces.need((size_t)m * 4));
+  CU(s.out[2].need((size_t)m));
+  CU(cudaMemcpyAsync(s.in0.p, q, (size_t)n * 56, cudaMemcpyHostToDevice, s.stream));
+  osr::k_knn_window<<<(unsigned)((n + osr::KNN_TILE - 1) / osr::KNN_TILE), osr::KNN_TILE, 0, s.stream>>>(
+      (const double*)s.in0.p, (long long)n, k, (long long)window, (int*)s.faces.p, nullptr);
+  CU(cudaGetLastError());
+  w->host_counters.kernel_launches++;
+  if (out_idx) CU(cudaMemcpyAsync(out_idx, s.faces.p, (size_t)m * 4, cudaMemcpyDeviceToHost, s.stream));
+  osr::SegOut O = {nullptr, nullptr, (uint8_t*)s.out[2].p, nullptr, nullptr, nullptr, (const int*)s.faces.p, k};
+  rc = launch_transit(w, s, (const double*)s.in0.p, (const double*)s.in0.p, m, nullptr, 1, initial_verify_delta, 1, O);
+  if (rc) return rc;
+  CU(cudaMemcpyAsync(out_valid, s.out[2].p, (size_t)m, cudaMemcpyDeviceToHost, s.stream));
+  return check_device_error(w, s);
 }
 
 // ---- clearance statistics of key-configuration candidates ----------------------

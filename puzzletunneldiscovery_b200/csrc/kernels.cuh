@@ -603,6 +603,10 @@ struct SegOut {
   double* free_tau;    // [n] or null
   double* touch_tau;   // [n] or null
   long long* steps;    // [n] or null
+  // indexed segments (k-NN edges validated where they are, osr_knn_validate_edges): segment e runs from state
+  // e / idx_k to state to_idx[e] of ONE state array (`from` == `to`); to_idx[e] < 0 = no such edge, label 0
+  const int* to_idx;   // [n] or null
+  int idx_k;
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -708,7 +712,21 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB)
     seg = __shfl_sync(FULL, seg, 0);
     if ((long long)seg >= n) break;
     __syncwarp();
-    if (lane < 7) { S.seg[lane] = __ldg(from + 7 * seg + lane); S.seg[7 + lane] = __ldg(to + 7 * seg + lane); }
+    long long fi = (long long)seg, ti = (long long)seg;
+    if (O.to_idx) {
+      fi = div53((long long)seg, (long long)O.idx_k);
+      ti = __ldg(O.to_idx + seg);
+      if (ti < 0) {
+        if (lane == 0) {
+          if (O.is_free) O.is_free[seg] = 0;
+          if (O.free_tau) O.free_tau[seg] = 0.0;
+          if (O.touch_tau) O.touch_tau[seg] = 0.0;
+          if (O.steps) O.steps[seg] = 0;
+        }
+        continue;
+      }
+    }
+    if (lane < 7) { S.seg[lane] = __ldg(from + 7 * fi + lane); S.seg[7 + lane] = __ldg(to + 7 * ti + lane); }
     __syncwarp();
     double vd = vd_arr ? __ldg(vd_arr + (vd_count > 1 ? seg : 0)) : vd_scalar;
     double dist, trans;

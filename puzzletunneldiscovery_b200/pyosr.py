@@ -637,6 +637,17 @@ class UnitWorld:
                                        _p(dist, c_dp)))
         return (idx, dist) if with_distance else idx
 
+    def knn_validate_edges(self, qs, k=8, window=4096, verify_delta=None):
+        """Windowed k-NN and is_valid_transition of every edge found, in one call that uploads only the milestones
+        (osr_knn_validate_edges): (idx int32[N, k], valid bool[N, k]); valid is False where idx is -1."""
+        q = _states(qs)
+        n = len(q)
+        vd = self.recommended_cres if verify_delta is None else float(verify_delta)
+        idx = np.empty((n, k), np.int32); ok = np.empty((n, k), np.uint8)
+        check(self._L.osr_knn_validate_edges(self._h, _p(q, c_dp), n, int(k), int(window), vd, _p(idx, c_i32p),
+                                             _p(ok, c_u8p)))
+        return idx, ok.astype(bool)
+
     def knn_edges(self, qs, k=8, window=4096):
         """(from, to) state arrays of the k-NN edges, milestone-major like workloads.knn_edges."""
         q = _states(qs)

@@ -116,6 +116,10 @@ def leg_edges(O, scale):
     ores, ocnt = ow.is_valid_transitions(fr[:m], to[:m], vd, counters=True)
     dtc = time.perf_counter() - tc
     c = uw.counters(reset=True)
+    # the same workload without building the edges: k-NN and validation in one call, only the milestones uploaded
+    (fidx, fok), dt_fused = timed(lambda: uw.knn_validate_edges(q, k=8, window=4096, verify_delta=vd))
+    fdst = fidx.reshape(-1)
+    fused_same = bool(np.array_equal(fok.reshape(-1)[fdst >= 0], res) and np.array_equal(q[fdst[fdst >= 0]], to))
     # full-size properties: a random subset re-evaluated on its own gives the same labels; an edge reversed end for
     # end is walked at different taus but between the same two valid milestones, so the two directions may only
     # disagree when a contact lies inside one verify_delta of the path (reported, not asserted)
@@ -130,6 +134,10 @@ def leg_edges(O, scale):
             "properties_full_size": props,
             "edges_per_s": len(fr) / dt, "seconds": dt, "valid_edge_fraction": float(res.mean()),
             "gpu_knn_seconds": t_knn, "knn_edges_per_s": len(fr) / t_knn,
+            "fused_knn_and_validation": {"seconds": dt_fused, "edges_per_s": len(fr) / dt_fused,
+                                         "same_edges_and_labels": fused_same,
+                                         "separate_calls_seconds (k-NN + edge arrays + validation)": t_knn + dt,
+                                         "h2d_bytes": int(q.nbytes), "h2d_bytes_separate_calls": int(q.nbytes + fr.nbytes + to.nbytes)},
             "knn_first_window_equals_host_restatement": bool(same_edges), "oracle_prefix": m,
             "labels_equal_oracle_on_prefix": bool(np.array_equal(res[:m], ores.astype(bool))),
             "steps_reference_semantics": int(c["poses"]) // 2, "box_tests_per_step": c["bv_tests"] / max(1, c["poses"]),

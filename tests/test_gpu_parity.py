@@ -886,6 +886,31 @@ def test_enum_2drot_free_configuration_closed_form_properties(uw_org):
         assert len(some) >= 1 and all(any(np.array_equal(r, qs[k]) for k in range(al)) for r in some)
 
 
+def test_knn_validate_edges_equals_the_two_separate_calls(uw_org):
+    """osr_knn_validate_edges (k-NN edges validated where they are, only the milestones uploaded) = osr_knn_windowed
+    followed by osr_is_valid_transitions on the materialised (from, to) arrays: same indices, same labels; windows
+    with fewer than k other states give index -1 and label 0."""
+    q = W.random_states(6000, seed=203)
+    ms = q[uw_org.is_valid_states(q)][:4096 + 256 + 3]      # a full window, a short one, and one of three states
+    for (k, window, vd) in ((8, 4096, None), (4, 256, 2e-3)):
+        if k == 8:
+            sel = np.concatenate([ms[:4096], ms[4096:4096 + 3]])   # second window holds 3 states: 2 neighbours each
+        else:
+            sel = ms
+        idx, ok = uw_org.knn_validate_edges(sel, k=k, window=window, verify_delta=vd)
+        want_idx = uw_org.knn_windowed(sel, k, window)
+        assert np.array_equal(idx, want_idx)
+        src = np.repeat(np.arange(len(sel)), k); dst = idx.reshape(-1)
+        have = dst >= 0
+        lab = uw_org.is_valid_transitions(sel[src[have]], sel[dst[have]], uw_org.recommended_cres if vd is None else vd)
+        assert np.array_equal(ok.reshape(-1)[have], lab) and not ok.reshape(-1)[~have].any()
+        assert 0 < lab.sum() < len(lab)
+        if k == 8:
+            assert (~have).sum() == 3 * (8 - 2)
+    i0, ok0 = uw_org.knn_validate_edges(np.zeros((0, 7)), k=4, window=256)
+    assert i0.shape == (0, 4) and ok0.shape == (0, 4)
+
+
 @pytest.mark.gpu
 def test_clearance_stats_edge_cases(uw_org, ow_org, oracle_mod):
     """One and two points per candidate (median = the value / the mean of both), targets closer than one step
