@@ -127,6 +127,7 @@ struct osr_world {
   double sweep_rmax = 0.02;        // K2: largest swept radius worth a traversal (OSR_SWEEP_RMAX, unit-scene lengths)
   double sweep_rstart = 0.005;     // K2: swept radius of the first windows of a walk (OSR_SWEEP_RSTART)
   int sweep_short_tile = 8;        // K2: steps of the exact tile after a blocked 4-step window (OSR_SWEEP_SHORT_TILE)
+  int sweep_nb0 = 4;               // K2: windows in the first swept traversal of a walk (OSR_SWEEP_NB0)
   double sweep_keep_rmax = 3e-4;   // K2: windows of a larger swept radius keep no pairs (OSR_SWEEP_KEEP_RMAX, unit-scene lengths)
   int sweep_resolve = 512;         // K2: exact (pair, step) tests one window may cost before it counts as blocked (OSR_SWEEP_RESOLVE, 0 = off)
 
@@ -142,6 +143,7 @@ struct osr_world {
     P.sweep_rmax = sweep_rmax;
     P.sweep_rstart = sweep_rstart;
     P.sweep_short_tile = sweep_short_tile;
+    P.sweep_nb0 = sweep_nb0;
     P.sweep_resolve = sweep_resolve;
     P.sweep_keep_rmax = sweep_keep_rmax;
     P.counters = s.counters;
@@ -404,6 +406,7 @@ int osr_create(osr_world** out) {
   if (const char* k3 = getenv("OSR_SWEEP_TILES")) (*out)->sweep_tiles = std::max(0, std::min(1 << 16, atoi(k3)));
   if (const char* k4 = getenv("OSR_SWEEP_RMAX")) (*out)->sweep_rmax = std::max(0.0, atof(k4));
   if (const char* k5 = getenv("OSR_SWEEP_RSTART")) (*out)->sweep_rstart = std::max(0.0, atof(k5));
+  if (const char* k9 = getenv("OSR_SWEEP_NB0")) (*out)->sweep_nb0 = std::max(1, std::min(32, atoi(k9)));
   if (const char* k6 = getenv("OSR_SWEEP_SHORT_TILE")) (*out)->sweep_short_tile = std::max(1, std::min(32, atoi(k6)));
   if (const char* k8 = getenv("OSR_SWEEP_KEEP_RMAX")) (*out)->sweep_keep_rmax = std::max(0.0, atof(k8));
   if (const char* k7 = getenv("OSR_SWEEP_RESOLVE")) (*out)->sweep_resolve = std::max(0, std::min(1 << 20, atoi(k7)));

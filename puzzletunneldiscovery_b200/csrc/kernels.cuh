@@ -51,6 +51,7 @@ struct KParams {
   double sweep_rmax;                 // K2: windows whose swept radius exceeds this are not attempted
   double sweep_rstart;               // K2: swept radius of the first windows of a walk
   int sweep_short_tile;              // K2: steps of the exact tile that follows a blocked 4-step window (1..32)
+  int sweep_nb0;                     // K2: windows in the first swept traversal of a walk (1..32)
   int sweep_resolve;                 // K2: most exact (triangle pair, step) tests spent on one window whose swept
                                      //     traversal left pairs that are not provably clear (0 = such windows are blocked)
   double sweep_keep_rmax;            // K2: ... and only windows whose swept radius stays below this keep pairs at all
@@ -788,7 +789,7 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB)
         ws = 4;
         while (2 * ws <= ws_cap && (double)(2 * ws) * step_radius <= P.sweep_rstart) ws *= 2;
       }
-      int nb = 4;                  // windows per traversal
+      int nb = P.sweep_nb0;        // windows per traversal
       int fails = 0;
       bool exact_next = false;     // the next tile is known not to clear
       // What the last swept traversal left to consume, in walk order: pend_clear windows of pws steps that kept no
