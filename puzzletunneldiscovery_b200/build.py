@@ -8,7 +8,7 @@ CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libosrgpu.so")
 SOURCES = ["engine.cu", "geometry.cc"]
 DEPS = SOURCES + ["kernels.cuh", "kernels_dfs.cuh", "kernels_seg.cuh", "kernels_surface.cuh", "kernels_knn.cuh",
-                  "kernels_raster.cuh", "kernels_clearance.cuh", "kernels_keyconf.cuh", "qnode.h", "sat17.h", "se3.h", "geometry.h",
+                  "kernels_raster.cuh", "kernels_clearance.cuh", "kernels_keyconf.cuh", "kernels_contacts.cuh", "qnode.h", "sat17.h", "se3.h", "geometry.h",
                   os.path.join("..", "..", "include", "osrgpu.h")]
 
 NVCC_FLAGS = [

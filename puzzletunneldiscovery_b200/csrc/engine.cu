@@ -25,6 +25,7 @@
 #include "kernels_raster.cuh"
 #include "kernels_clearance.cuh"
 #include "kernels_keyconf.cuh"
+#include "kernels_contacts.cuh"
 
 // Scratch of the allocation-free entry point osr_is_valid_transitions_device_noalloc (end of this file): the work-queue
 // word of K2 and its per-warp traversal-stack spill areas.  File scope, in every GPU's memory that loads the library
@@ -102,6 +103,7 @@ struct Slot {  // one GPU
   DevBuf in0, in1, vd, out[6], recs, rowrec, seg, faces, cop, bary;
   DevBuf surf_v, surf_f, surf_flags, surf_cnt, surf_off, surf_face, surf_l;  // K5 (kernels_surface.cuh)
   DevBuf clr_q0, clr_stats, clr_dist;                                         // K8 (kernels_clearance.cuh)
+  DevBuf c_cnt, c_msum, c_cur, c_recoff, c_rowoff, c_recs2;                   // K3c (kernels_contacts.cuh)
 };
 
 }  // namespace
@@ -1371,10 +1373,11 @@ int osr_intersecting_segments(osr_world* w, const double* q, int64_t n, int64_t 
   if (overflow) memset(overflow, 0, (size_t)n);
   if (total) *total = 0;
   if (n == 0) return OSR_OK;
-  // Pass 1 (every device, index-range shards): all intersecting (state, env tri, rob tri) records.
+  // Pass 1 (every device, index-range shards): all intersecting (state, env tri, rob tri) records, then their
+  // number and their FCL row count per state (K3c; the records stay on the device).
   int parts = (int)w->slots.size();
-  std::vector<std::vector<osr::ContactRec>> host_recs(parts);
-  std::vector<int64_t> los(parts);
+  std::vector<int64_t> los(parts), nrec(parts, 0);
+  std::vector<std::vector<int>> h_cnt(parts), h_msum(parts);
   for (int i = 0; i < parts; i++) {
     Slot& s = w->slots[i];
     int64_t lo, hi;
@@ -1401,69 +1404,76 @@ int osr_intersecting_segments(osr_world* w, const double* q, int64_t n, int64_t 
       rc = check_device_error(w, s);
       if (rc) return rc;
       if (found <= rec_cap) {
-        host_recs[i].resize((size_t)found);
-        if (found) CU(cudaMemcpy(host_recs[i].data(), s.recs.p, (size_t)found * sizeof(osr::ContactRec), cudaMemcpyDeviceToHost));
+        nrec[i] = (int64_t)found;
         break;
       }
       if (attempt == 1) return fail(OSR_EOVERFLOW, "contact record buffer overflow");
       rec_cap = found + 1024;  // exact size known now: run again
     }
+    h_cnt[i].assign((size_t)m, 0);
+    h_msum[i].assign((size_t)m, 0);
+    if (nrec[i] == 0) continue;
+    CU(s.c_cnt.need((size_t)m * 4));
+    CU(s.c_msum.need((size_t)m * 4));
+    CU(cudaMemsetAsync(s.c_cnt.p, 0, (size_t)m * 4, s.stream));
+    CU(cudaMemsetAsync(s.c_msum.p, 0, (size_t)m * 4, s.stream));
+    osr::k_rec_count<<<(unsigned)((nrec[i] + 255) / 256), 256, 0, s.stream>>>(
+        (const osr::ContactRec*)s.recs.p, (long long)nrec[i], (int*)s.c_cnt.p, (int*)s.c_msum.p);
+    CU(cudaGetLastError());
+    w->host_counters.kernel_launches++;
+    CU(cudaMemcpyAsync(h_cnt[i].data(), s.c_cnt.p, (size_t)m * 4, cudaMemcpyDeviceToHost, s.stream));
+    CU(cudaMemcpyAsync(h_msum[i].data(), s.c_msum.p, (size_t)m * 4, cudaMemcpyDeviceToHost, s.stream));
   }
-  // Host: canonical order (state, env tri, rob tri), FCL row multiplicity, CSR offsets, truncation.
+  for (auto& s : w->slots) {
+    CU(cudaSetDevice(s.dev));
+    CU(cudaStreamSynchronize(s.stream));
+  }
+  // Host: CSR offsets of the rows with the output capacity applied (n integers; the records are not touched).
   int64_t rows_found = 0, rows_written = 0;
-  std::vector<int64_t> per_state((size_t)n, 0);
-  for (int i = 0; i < parts; i++) {
-    auto& v = host_recs[i];
-    for (auto& r : v) r.state += (int)los[i];
-    std::sort(v.begin(), v.end(), [](const osr::ContactRec& a, const osr::ContactRec& b) {
-      if (a.state != b.state) return a.state < b.state;
-      if (a.env_tri != b.env_tri) return a.env_tri < b.env_tri;
-      return a.rob_tri < b.rob_tri;
-    });
-    for (auto& r : v) per_state[r.state] += r.mult;
-  }
-  for (int64_t i = 0; i < n; i++) {
-    rows_found += per_state[i];
-    int64_t room = cap - rows_written;
-    int64_t take = std::min(per_state[i], std::max<int64_t>(room, 0));
-    if (take < per_state[i] && overflow) overflow[i] = 1;
-    rows_written += take;
-    offsets[i + 1] = rows_written;
-  }
+  for (int i = 0; i < parts; i++)
+    for (size_t j = 0; j < h_msum[i].size(); j++) {
+      const int64_t st = los[i] + (int64_t)j, have = h_msum[i][j];
+      rows_found += have;
+      const int64_t take = std::min(have, std::max<int64_t>(cap - rows_written, 0));
+      if (take < have && overflow) overflow[st] = 1;
+      rows_written += take;
+      offsets[st + 1] = rows_written;
+    }
   if (total) *total = rows_found;
-  // Pass 2: one thread per output row (Moeller segment + optional barycentrics), per device.
+  // Pass 2 (per device): records into per-state buckets, ordered inside each bucket, row list laid out (K3c); then
+  // one thread per output row (Moeller segment + optional barycentrics).
   for (int i = 0; i < parts; i++) {
     Slot& s = w->slots[i];
-    auto& v = host_recs[i];
-    if (v.empty()) continue;
-    std::vector<int> row_rec;
-    int64_t first_row = -1;
-    for (size_t r = 0; r < v.size(); r++) {
-      int st = v[r].state;
-      // rows of state st start at offsets[st]; records of a state are consecutive in v
-      if (r == 0 || v[r - 1].state != st) {
-        if (first_row < 0) first_row = offsets[st];
-      }
-      v[r].state -= (int)los[i];  // back to shard-local index for the device lookup
-    }
-    // rebuild row list honouring truncation
-    {
-      size_t r = 0;
-      while (r < v.size()) {
-        int st = v[r].state + (int)los[i];
-        int64_t budget = offsets[st + 1] - offsets[st];
-        while (r < v.size() && v[r].state + (int)los[i] == st) {
-          for (int k = 0; k < v[r].mult && budget > 0; k++, budget--) row_rec.push_back((int)r);
-          r++;
-        }
-      }
-    }
-    int64_t nrows = (int64_t)row_rec.size();
+    const int64_t m = (int64_t)h_cnt[i].size();
+    if (m == 0 || nrec[i] == 0) continue;
+    const int64_t first_row = offsets[los[i]], nrows = offsets[los[i] + m] - first_row;
     if (nrows == 0) continue;
+    std::vector<long long> rec_off((size_t)m + 1), row_off((size_t)m + 1);
+    rec_off[0] = 0;
+    for (int64_t j = 0; j < m; j++) {
+      rec_off[(size_t)j + 1] = rec_off[(size_t)j] + h_cnt[i][(size_t)j];
+      row_off[(size_t)j] = offsets[los[i] + j] - first_row;
+    }
+    row_off[(size_t)m] = nrows;
     CU(cudaSetDevice(s.dev));
-    CU(cudaMemcpyAsync(s.recs.p, v.data(), v.size() * sizeof(osr::ContactRec), cudaMemcpyHostToDevice, s.stream));
+    CU(s.c_recoff.need((size_t)(m + 1) * 8));
+    CU(s.c_rowoff.need((size_t)(m + 1) * 8));
+    CU(s.c_cur.need((size_t)m * 4));
+    CU(s.c_recs2.need((size_t)nrec[i] * sizeof(osr::ContactRec)));
     CU(s.rowrec.need((size_t)nrows * 4));
-    CU(cudaMemcpyAsync(s.rowrec.p, row_rec.data(), (size_t)nrows * 4, cudaMemcpyHostToDevice, s.stream));
+    CU(cudaMemcpyAsync(s.c_recoff.p, rec_off.data(), (size_t)(m + 1) * 8, cudaMemcpyHostToDevice, s.stream));
+    CU(cudaMemcpyAsync(s.c_rowoff.p, row_off.data(), (size_t)(m + 1) * 8, cudaMemcpyHostToDevice, s.stream));
+    CU(cudaMemsetAsync(s.c_cur.p, 0, (size_t)m * 4, s.stream));
+    osr::k_rec_scatter<<<(unsigned)((nrec[i] + 255) / 256), 256, 0, s.stream>>>(
+        (const osr::ContactRec*)s.recs.p, (long long)nrec[i], (const long long*)s.c_recoff.p, (int*)s.c_cur.p,
+        (osr::ContactRec*)s.c_recs2.p);
+    CU(cudaGetLastError());
+    const unsigned order_blocks = (unsigned)std::min<int64_t>((m + 3) / 4, (int64_t)s.num_sms * 16);
+    osr::k_rec_order<<<order_blocks, 128, 0, s.stream>>>(
+        (const osr::ContactRec*)s.c_recs2.p, (osr::ContactRec*)s.recs.p, (const long long*)s.c_recoff.p, (long long)m,
+        (const long long*)s.c_rowoff.p, (int*)s.rowrec.p);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(s.stream));   // rec_off / row_off (host vectors of this iteration) have been consumed
     CU(s.seg.need((size_t)nrows * 48));
     CU(s.faces.need((size_t)nrows * 8));
     CU(s.cop.need((size_t)nrows));
@@ -1473,7 +1483,7 @@ int osr_intersecting_segments(osr_world* w, const double* q, int64_t n, int64_t 
         P, (const double*)s.in0.p, (const osr::ContactRec*)s.recs.p, (const int*)s.rowrec.p, (long long)nrows,
         (double*)s.seg.p, (int*)s.faces.p, (uint8_t*)s.cop.p, bary ? (double*)s.bary.p : nullptr);
     CU(cudaGetLastError());
-    w->host_counters.kernel_launches++;
+    w->host_counters.kernel_launches += 3;
     CU(cudaMemcpyAsync(seg + 6 * first_row, s.seg.p, (size_t)nrows * 48, cudaMemcpyDeviceToHost, s.stream));
     CU(cudaMemcpyAsync(faces + 2 * first_row, s.faces.p, (size_t)nrows * 8, cudaMemcpyDeviceToHost, s.stream));
     CU(cudaMemcpyAsync(coplanar + first_row, s.cop.p, (size_t)nrows, cudaMemcpyDeviceToHost, s.stream));
