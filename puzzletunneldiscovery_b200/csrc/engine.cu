@@ -130,6 +130,7 @@ struct osr_world {
   double sweep_rstart = 0.005;     // K2: swept radius of the first windows of a walk (OSR_SWEEP_RSTART)
   int sweep_short_tile = 8;        // K2: steps of the exact tile after a blocked 4-step window (OSR_SWEEP_SHORT_TILE)
   int sweep_nb0 = 4;               // K2: windows in the first swept traversal of a walk (OSR_SWEEP_NB0)
+  int rec_warp_max = osr::REC_ORDER_WARP_MAX;   // K3c: largest bucket ranked by one warp (OSR_REC_WARP_MAX; tests)
   double sweep_keep_rmax = 3e-4;   // K2: windows of a larger swept radius keep no pairs (OSR_SWEEP_KEEP_RMAX, unit-scene lengths)
   int sweep_resolve = 512;         // K2: exact (pair, step) tests one window may cost before it counts as blocked (OSR_SWEEP_RESOLVE, 0 = off)
 
@@ -408,6 +409,7 @@ int osr_create(osr_world** out) {
   if (const char* k3 = getenv("OSR_SWEEP_TILES")) (*out)->sweep_tiles = std::max(0, std::min(1 << 16, atoi(k3)));
   if (const char* k4 = getenv("OSR_SWEEP_RMAX")) (*out)->sweep_rmax = std::max(0.0, atof(k4));
   if (const char* k5 = getenv("OSR_SWEEP_RSTART")) (*out)->sweep_rstart = std::max(0.0, atof(k5));
+  if (const char* k10 = getenv("OSR_REC_WARP_MAX")) (*out)->rec_warp_max = std::max(1, atoi(k10));
   if (const char* k9 = getenv("OSR_SWEEP_NB0")) (*out)->sweep_nb0 = std::max(1, std::min(32, atoi(k9)));
   if (const char* k6 = getenv("OSR_SWEEP_SHORT_TILE")) (*out)->sweep_short_tile = std::max(1, std::min(32, atoi(k6)));
   if (const char* k8 = getenv("OSR_SWEEP_KEEP_RMAX")) (*out)->sweep_keep_rmax = std::max(0.0, atof(k8));
@@ -1471,9 +1473,21 @@ int osr_intersecting_segments(osr_world* w, const double* q, int64_t n, int64_t 
     const unsigned order_blocks = (unsigned)std::min<int64_t>((m + 3) / 4, (int64_t)s.num_sms * 16);
     osr::k_rec_order<<<order_blocks, 128, 0, s.stream>>>(
         (const osr::ContactRec*)s.c_recs2.p, (osr::ContactRec*)s.recs.p, (const long long*)s.c_recoff.p, (long long)m,
-        (const long long*)s.c_rowoff.p, (int*)s.rowrec.p);
+        (const long long*)s.c_rowoff.p, (int*)s.rowrec.p, w->rec_warp_max);
     CU(cudaGetLastError());
-    CU(cudaStreamSynchronize(s.stream));   // rec_off / row_off (host vectors of this iteration) have been consumed
+    std::vector<int> big;
+    for (int64_t j = 0; j < m; j++)
+      if (h_cnt[i][(size_t)j] > w->rec_warp_max) big.push_back((int)j);
+    if (!big.empty()) {
+      CU(s.c_cnt.need(big.size() * 4));   // (the per-state counts on the device are no longer needed)
+      CU(cudaMemcpyAsync(s.c_cnt.p, big.data(), big.size() * 4, cudaMemcpyHostToDevice, s.stream));
+      osr::k_rec_order_big<<<(unsigned)big.size(), 1024, 0, s.stream>>>(
+          (const osr::ContactRec*)s.c_recs2.p, (osr::ContactRec*)s.recs.p, (const long long*)s.c_recoff.p,
+          (const int*)s.c_cnt.p, (const long long*)s.c_rowoff.p, (int*)s.rowrec.p);
+      CU(cudaGetLastError());
+      w->host_counters.kernel_launches++;
+    }
+    CU(cudaStreamSynchronize(s.stream));   // rec_off / row_off / big (host vectors of this iteration) have been consumed
     CU(s.seg.need((size_t)nrows * 48));
     CU(s.faces.need((size_t)nrows * 8));
     CU(s.cop.need((size_t)nrows));

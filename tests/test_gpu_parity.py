@@ -318,6 +318,49 @@ def test_contacts_capacity_overflow_flag(uw_org):
     assert e["total"] == 0 and (e["offsets"] == 0).all()
 
 
+def test_contacts_of_deep_penetrations_large_buckets(oracle_mod, monkeypatch):
+    """States with many touching triangle pairs: buckets beyond a threshold (2 048 records; lowered to 64 here so
+    that states of the subdivided puzzle cross it, with buckets spanning several 1 024-key tiles) are ranked by a
+    whole block instead of a warp (kernels_contacts.cuh).  Rows, flags and segments equal the oracle's, and the
+    rows of a state are the same alone and inside a batch, ordered by (env triangle, robot triangle)."""
+    import os
+    from puzzletunneldiscovery_b200 import pyosr
+    A = W.assets_dir()
+    eV, eF = W.load_obj_vf(os.path.join(A, "alpha_env-1.2.org.obj"))
+    rV, rF = W.load_obj_vf(os.path.join(A, "alpha-1.2.org.obj"))
+    EV, EF = W.subdivide(eV, eF, 8)
+    RV, RF = W.subdivide(rV, rF, 8)
+
+    def mk(cls):
+        w = cls()
+        w.set_meshes(EV, EF, RV, RF)
+        w.scaleToUnit()
+        w.angleModel(0.0, 0.0)
+        return w
+    monkeypatch.setenv("OSR_REC_WARP_MAX", "64")
+    uw = mk(pyosr.UnitWorld)
+    monkeypatch.delenv("OSR_REC_WARP_MAX")
+    uw_warp = mk(pyosr.UnitWorld)
+    q = W.random_states(1024, seed=301)
+    r = uw.intersecting_segments_batch(q, cap=1 << 22)
+    rw = uw_warp.intersecting_segments_batch(q, cap=1 << 22)
+    for k in ("offsets", "faces", "seg", "coplanar"):
+        assert np.array_equal(r[k], rw[k])           # block-ranked = warp-ranked, row for row
+    rows = np.diff(r["offsets"])
+    top = np.argsort(-rows)[:3]
+    assert rows[top].min() > 2 * 1024 + 8            # > 1 024 records each: more than one key tile
+    ow = mk(oracle_mod.OracleWorld)
+    ooff, osegs, ofaces, ocop, ototal = ow.intersecting_segments_batch(q[top], cap=1 << 20)
+    r2 = uw.intersecting_segments_batch(q[top], cap=1 << 20)
+    assert r2["total"] == ototal and np.array_equal(r2["offsets"], ooff)
+    assert np.array_equal(_canon(r2["offsets"], r2["faces"], r2["seg"], r2["coplanar"]), _canon(ooff, ofaces, osegs, ocop))
+    for k, i in enumerate(top):                      # same rows, same order, alone and inside the batch
+        sl = slice(r["offsets"][i], r["offsets"][i + 1]); s2 = slice(r2["offsets"][k], r2["offsets"][k + 1])
+        assert np.array_equal(r["faces"][sl], r2["faces"][s2]) and np.array_equal(r["seg"][sl], r2["seg"][s2])
+        f = r["faces"][sl].astype(np.int64)
+        assert (np.diff(f[:, 0] * (1 << 32) + f[:, 1]) >= 0).all()
+
+
 # ---- other hot-path entry points -------------------------------------------------------------------------
 def test_enum_free_configurations_labels_are_validity(uw_org):
     V0, F0 = uw_org._geometry(0)
