@@ -200,7 +200,7 @@ int osr_knn_windowed(osr_world* w, const double* q, int64_t n, int k, int64_t wi
  * is_valid_transition(q[i], q[out_idx[i][s]], initial_verify_delta) (unit_world.cc:477-486), 0 where out_idx is -1.
  * The planners' pattern -- nearest neighbours, then checkMotion on every edge (lib/pyse3ompl/ompldriver.cc:176-260,
  * RDT-forest edge validation of BASELINE config 3).  Only the milestones are uploaded.  out_idx optional.  Labels equal
- * those of the two separate calls.  Runs on the handle's first device; n k < 2^31. */
+ * those of the two separate calls.  Whole windows are sharded over the devices of the handle; n k < 2^31. */
 int osr_knn_validate_edges(osr_world* w, const double* q, int64_t n, int k, int64_t window, double initial_verify_delta,
                            int32_t* out_idx, uint8_t* out_valid);
 

@@ -1615,23 +1615,50 @@ int osr_knn_validate_edges(osr_world* w, const double* q, int64_t n, int k, int6
   if (initial_verify_delta < 0.0) return fail(OSR_EINVAL, "verify_delta must not be negative");
   if (n == 0) return OSR_OK;
   std::lock_guard<std::mutex> lk(w->mu);
-  Slot& s = w->slots[0];
-  CU(cudaSetDevice(s.dev));
-  const int64_t m = n * k;
-  CU(s.in0.need((size_t)n * 56));
-  CU(s.faces.need((size_t)m * 4));
-  CU(s.out[2].need((size_t)m));
-  CU(cudaMemcpyAsync(s.in0.p, q, (size_t)n * 56, cudaMemcpyHostToDevice, s.stream));
-  osr::k_knn_window<<<(unsigned)((n + osr::KNN_TILE - 1) / osr::KNN_TILE), osr::KNN_TILE, 0, s.stream>>>(
-      (const double*)s.in0.p, (long long)n, k, (long long)window, (int*)s.faces.p, nullptr);
-  CU(cudaGetLastError());
-  w->host_counters.kernel_launches++;
-  if (out_idx) CU(cudaMemcpyAsync(out_idx, s.faces.p, (size_t)m * 4, cudaMemcpyDeviceToHost, s.stream));
-  osr::SegOut O = {nullptr, nullptr, (uint8_t*)s.out[2].p, nullptr, nullptr, nullptr, (const int*)s.faces.p, k};
-  rc = launch_transit(w, s, (const double*)s.in0.p, (const double*)s.in0.p, m, nullptr, 1, initial_verify_delta, 1, O);
-  if (rc) return rc;
-  CU(cudaMemcpyAsync(out_valid, s.out[2].p, (size_t)m, cudaMemcpyDeviceToHost, s.stream));
-  return check_device_error(w, s);
+  // k-NN is local to a window, so whole windows are sharded over the devices of the handle: each device gets the
+  // milestones of its windows only and works on local indices; the window's first index is added on the way out.
+  const int parts = (int)w->slots.size();
+  const int64_t nwin = (n + window - 1) / window;
+  std::vector<int64_t> los(parts, 0), his(parts, 0);
+  for (int i = 0; i < parts; i++) {
+    int64_t wlo, whi;
+    shard(nwin, parts, i, wlo, whi);
+    los[i] = std::min(n, wlo * window);
+    his[i] = std::min(n, whi * window);
+    const int64_t nl = his[i] - los[i];
+    if (nl == 0) continue;
+    Slot& s = w->slots[i];
+    CU(cudaSetDevice(s.dev));
+    const int64_t m = nl * k;
+    CU(s.in0.need((size_t)nl * 56));
+    CU(s.faces.need((size_t)m * 4));
+    CU(s.out[2].need((size_t)m));
+    CU(cudaMemcpyAsync(s.in0.p, q + 7 * los[i], (size_t)nl * 56, cudaMemcpyHostToDevice, s.stream));
+    osr::k_knn_window<<<(unsigned)((nl + osr::KNN_TILE - 1) / osr::KNN_TILE), osr::KNN_TILE, 0, s.stream>>>(
+        (const double*)s.in0.p, (long long)nl, k, (long long)window, (int*)s.faces.p, nullptr);
+    CU(cudaGetLastError());
+    w->host_counters.kernel_launches++;
+    if (out_idx) CU(cudaMemcpyAsync(out_idx + los[i] * k, s.faces.p, (size_t)m * 4, cudaMemcpyDeviceToHost, s.stream));
+    osr::SegOut O = {nullptr, nullptr, (uint8_t*)s.out[2].p, nullptr, nullptr, nullptr, (const int*)s.faces.p, k};
+    rc = launch_transit(w, s, (const double*)s.in0.p, (const double*)s.in0.p, m, nullptr, 1, initial_verify_delta, 1, O);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(out_valid + los[i] * k, s.out[2].p, (size_t)m, cudaMemcpyDeviceToHost, s.stream));
+  }
+  for (int i = 0; i < parts; i++) {
+    if (his[i] == los[i]) continue;
+    Slot& s = w->slots[i];
+    CU(cudaSetDevice(s.dev));
+    rc = check_device_error(w, s);
+    if (rc) return rc;
+    if (out_idx && los[i] > 0) {
+      const int32_t base = (int32_t)los[i];
+      int32_t* p = out_idx + los[i] * k;
+      const int64_t cnt = (his[i] - los[i]) * k;
+      for (int64_t j = 0; j < cnt; j++)
+        if (p[j] >= 0) p[j] += base;
+    }
+  }
+  return OSR_OK;
 }
 
 // ---- clearance statistics of key-configuration candidates ----------------------

@@ -554,6 +554,11 @@ def test_two_devices_one_handle_equal_one_device(uw_org):
     sa, da = uw_org.clearance_stats(cq, cto, VD_TOUCH, with_distances=True)
     sb, db = uw2.clearance_stats(cq, cto, VD_TOUCH, with_distances=True)
     assert np.array_equal(sa, sb) and np.array_equal(da, db)
+    # window-sharded: k-NN edges validated where they are (three windows over two devices, the last one short)
+    ms = q[v1][:2 * 256 + 100]
+    ia, oa = uw_org.knn_validate_edges(ms, k=4, window=256, verify_delta=2e-3)
+    ib, ob = uw2.knn_validate_edges(ms, k=4, window=256, verify_delta=2e-3)
+    assert np.array_equal(ia, ib) and np.array_equal(oa, ob) and ib[256:].min() >= 256
     pts = np.random.RandomState(44).randn(9, 4, 3)
     ka = uw_org.enum_free_configurations(pts, 1e-4, 19, only_median=True)
     kb = uw2.enum_free_configurations(pts, 1e-4, 19, only_median=True)
