@@ -7,6 +7,9 @@
 #include <atomic>
 #include <thread>
 #include <cmath>
+#include <condition_variable>
+#include <deque>
+#include <functional>
 #include <cstdio>
 #include <cstring>
 #include <memory>
@@ -14,6 +17,9 @@
 #include <string>
 #include <type_traits>
 #include <vector>
+#if defined(__x86_64__)
+#include <emmintrin.h>
+#endif
 
 #include "../../include/osrgpu.h"
 #include "geometry.h"
@@ -747,10 +753,80 @@ static int launch_valid_feed(osr_world* w, Slot& s, const T* d_q, int64_t n, uin
 static int staging_threads() {
   static int v = [] {
     const char* e = getenv("OSR_STAGING_THREADS");
-    int x = e ? atoi(e) : 4;
+    // default: half of the host's hardware threads, between 2 and 8 (the staging is bound by the memory system)
+    int x = e ? atoi(e) : std::max(2, std::min(8, (int)std::thread::hardware_concurrency() / 2));
     return std::max(0, std::min(16, x));
   }();
   return v;
+}
+
+// Copy into a pinned staging buffer with non-temporal stores: the buffer is read next by the DMA engine, not by a
+// core, and ordinary stores would first read every destination line into the cache (the host's memory system, not
+// its cores, bounds the staging of a pageable upload).
+static void stage_copy(void* dst, const void* src, size_t bytes) {
+#if defined(__x86_64__)
+  if ((((uintptr_t)dst | (uintptr_t)src) & 15) == 0) {
+    const __m128i* s = (const __m128i*)src;
+    __m128i* d = (__m128i*)dst;
+    size_t n = bytes / 64;
+    for (size_t i = 0; i < n; i++) {
+      __m128i a = _mm_load_si128(s + 4 * i), b = _mm_load_si128(s + 4 * i + 1), c = _mm_load_si128(s + 4 * i + 2),
+              e = _mm_load_si128(s + 4 * i + 3);
+      _mm_stream_si128(d + 4 * i, a); _mm_stream_si128(d + 4 * i + 1, b);
+      _mm_stream_si128(d + 4 * i + 2, c); _mm_stream_si128(d + 4 * i + 3, e);
+    }
+    _mm_sfence();
+    const size_t done = n * 64;
+    if (done < bytes) memcpy((char*)dst + done, (const char*)src + done, bytes - done);
+    return;
+  }
+#endif
+  memcpy(dst, src, bytes);
+}
+
+// Persistent staging workers (a host call on pageable arrays used to create and join its threads: ~0.3 ms of a 3 ms
+// call).  Detached: they sleep on the queue and end with the process.
+class StagePool {
+ public:
+  // runs job(0) .. job(n - 1) on the workers; returns false when a worker could not be created (caller runs them)
+  bool run(int n, const std::function<void(int)>& job, std::atomic<int>& remaining) {
+    std::unique_lock<std::mutex> lk(m_);
+    while ((int)workers_ < n) {
+      try {
+        std::thread([this] { loop(); }).detach();
+        workers_++;
+      } catch (...) {
+        return false;
+      }
+    }
+    remaining.store(n);
+    for (int t = 0; t < n; t++) q_.push_back([&job, &remaining, t] { job(t); remaining.fetch_sub(1, std::memory_order_release); });
+    lk.unlock();
+    cv_.notify_all();
+    return true;
+  }
+
+ private:
+  void loop() {
+    for (;;) {
+      std::function<void()> f;
+      {
+        std::unique_lock<std::mutex> lk(m_);
+        cv_.wait(lk, [this] { return !q_.empty(); });
+        f = std::move(q_.front());
+        q_.pop_front();
+      }
+      f();
+    }
+  }
+  std::mutex m_;
+  std::condition_variable cv_;
+  std::deque<std::function<void()>> q_;
+  size_t workers_ = 0;
+};
+static StagePool& stage_pool() {
+  static StagePool* p = new StagePool();   // never destroyed: its workers may outlive static destructors
+  return *p;
 }
 
 static bool is_pageable(const void* p) {
@@ -797,20 +873,18 @@ static int feed_pageable(osr_world* w, Slot& s, const T* q, int64_t m, int64_t c
       }
       char* st = s.stage + (size_t)(c % R) * cbytes;
       const int64_t c0 = (int64_t)c * ck, len = std::min(ck, m - c0);
-      memcpy(st, q + 7 * c0, (size_t)len * 7 * sizeof(T));
+      stage_copy(st, q + 7 * c0, (size_t)len * 7 * sizeof(T));
       if (cudaMemcpyAsync((T*)s.in0.p + 7 * c0, st, (size_t)len * 7 * sizeof(T), cudaMemcpyHostToDevice, s.stream2) != cudaSuccess ||
           cudaEventRecord(s.feed_ev[c], s.stream2) != cudaSuccess)
         err.store(1);
       enq[c].store(1, std::memory_order_release);
     }
   };
-  std::vector<std::thread> pool;
-  for (int t = 0; t < nthreads; t++) {
-    try {
-      pool.emplace_back(work, t);
-    } catch (...) {   // no thread to be had: this thread stages that share itself (the DMA does not depend on `ready`)
-      work(t);
-    }
+  std::atomic<int> remaining(0);
+  const std::function<void(int)> job = work;
+  if (!stage_pool().run(nthreads, job, remaining)) {
+    // no thread to be had: this thread stages everything itself (the DMA does not depend on `ready`)
+    for (int t = 0; t < nthreads; t++) work(t);
   }
   StreamWriteValue64 wv = stream_write_value64();
   cudaError_t ce = cudaSuccess;
@@ -822,7 +896,7 @@ static int feed_pageable(osr_world* w, Slot& s, const T* q, int64_t m, int64_t c
     if (ce == cudaSuccess && (!wv || wv(s.stream3, (unsigned long long)(uintptr_t)s.ready, (unsigned long long)upto, 0) != 0))
       ce = cudaMemcpyAsync(s.ready, s.h_ready + c, sizeof(long long), cudaMemcpyHostToDevice, s.stream3);
   }
-  for (auto& th : pool) th.join();
+  while (remaining.load(std::memory_order_acquire) > 0) std::this_thread::yield();   // `work` reads this frame
   if (ce != cudaSuccess || err.load()) {
     // the kernel may still be waiting for input that will not come: release it before reporting
     long long all = m;

@@ -5,7 +5,7 @@ Every leg goes through the C ABI (`libosrgpu.so`) with HOST buffers, is timed by
 (copies included), and a prefix of its output is compared with the CPU oracle (test infrastructure, used here
 only as the checker and as the timed CPU baseline).  One JSON line per leg; keep the output under profiles/.
 
-    python scripts/bench_configs.py [--legs touch,touch_fine,edges,hipoly,contacts,clearance,keyconf,ompl_motions] [--scale 1.0]
+    python scripts/bench_configs.py [--legs validity_wt2,touch,touch_fine,edges,hipoly,contacts,clearance,keyconf,ompl_motions] [--scale 1.0]
 """
 import argparse
 import json
@@ -92,6 +92,44 @@ def leg_touch(O, scale, fine=False):
             "oracle_prefix": m, "same_first_contact_step_as_oracle_on_prefix": same,
             "cpu_port": {"segments_per_s": m / dtc, "validity_checks_per_s": float(ocnt[:, 0].sum()) / dtc,
                          "threads": O.lib().orc_max_threads()}}
+
+
+def leg_validity_wt2(O, scale):
+    """Config 1 repeated on G-wt2 (the mesh set of the reference's alpha-1.2 touch scripts, 5 690 x 5 948
+    triangles -- the trees no longer fit into shared memory): 2^20 seeded uniform states, host call with page-locked
+    and pageable arrays, the kernel alone on device-resident states, oracle-checked prefix."""
+    import ctypes as C
+    import torch
+    from puzzletunneldiscovery_b200._lib import check
+    uw = world(pyosr.UnitWorld, "wt2", W.ROB_OMPL_CENTER)
+    ow = world(O.OracleWorld, "wt2", W.ROB_OMPL_CENTER)
+    n = int((1 << 20) * scale)
+    q = W.random_states(n, seed=0)
+    qp = pyosr.pinned_empty((n, 7)); qp[:] = q
+    op = pyosr.pinned_empty(n, np.uint8)
+    v, dt = timed(lambda: uw.is_valid_states(qp, out=op), reps=3)
+    v = np.array(v, copy=True)
+    _, dt_pageable = timed(lambda: uw.is_valid_states(q), reps=2)
+    dq = torch.from_numpy(q).cuda(); do = torch.empty(n, dtype=torch.uint8, device="cuda")
+    ms = []
+    uw.counters(reset=True)
+    for _ in range(4):
+        check(uw._L.osr_is_valid_states_device(uw._h, C.c_void_p(dq.data_ptr()), n, C.c_void_p(do.data_ptr())))
+        check(uw._L.osr_sync(uw._h))
+        f = C.c_float(0); check(uw._L.osr_last_kernel_ms(uw._h, C.byref(f))); ms.append(f.value)
+    c = uw.counters(reset=True)
+    m = min(n, 65536 * PREFIX_SCALE)
+    tc = time.perf_counter()
+    ov = ow.is_valid_states(q[:m], threads=0)
+    dtc = time.perf_counter() - tc
+    return {"leg": "validity_wt2", "geometry": "G-wt2", "states": n, "configs_per_s": n / dt, "seconds": dt,
+            "configs_per_s_pageable_host_arrays": n / dt_pageable,
+            "configs_per_s_device_resident": n / (min(ms[1:]) * 1e-3), "kernel_ms": min(ms[1:]),
+            "valid_fraction": float(v.mean()), "box_tests_per_state": c["bv_tests"] / (4.0 * n),
+            "triangle_tests_per_state": c["leaf_tests"] / (4.0 * n), "fp64_rechecks_per_state": c["fp64_rechecks"] / (4.0 * n),
+            "device_labels_equal_host_call": bool(np.array_equal(do.cpu().numpy().astype(bool), v)),
+            "oracle_prefix": m, "labels_equal_oracle_on_prefix": bool(np.array_equal(v[:m], ov.astype(bool))),
+            "cpu_port": {"configs_per_s": m / dtc, "threads": O.lib().orc_max_threads()}}
 
 
 def leg_edges(O, scale):
@@ -342,7 +380,7 @@ def leg_ompl(O, scale):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--legs", default="touch,touch_fine,edges,hipoly,contacts,clearance,keyconf,ompl_motions")
+    ap.add_argument("--legs", default="validity_wt2,touch,touch_fine,edges,hipoly,contacts,clearance,keyconf,ompl_motions")
     ap.add_argument("--scale", type=float, default=1.0)
     ap.add_argument("--prefix-scale", type=int, default=1)
     ap.add_argument("--full", action="store_true",
@@ -356,7 +394,7 @@ def main():
     mult = {"touch": 4, "touch_fine": 16, "edges": 64, "hipoly": 4, "contacts": 2} if args.full else {}
     sc = lambda leg: args.scale * mult.get(leg, 1)
     devs = tuple(int(x) for x in args.devices.split(","))
-    legs = {"touch": lambda: leg_touch(O, sc("touch")), "touch_fine": lambda: leg_touch(O, sc("touch_fine"), fine=True),
+    legs = {"validity_wt2": lambda: leg_validity_wt2(O, args.scale), "touch": lambda: leg_touch(O, sc("touch")), "touch_fine": lambda: leg_touch(O, sc("touch_fine"), fine=True),
             "edges": lambda: leg_edges(O, sc("edges")), "hipoly": lambda: leg_hipoly(O, sc("hipoly"), devs),
             "contacts": lambda: leg_contacts(O, sc("contacts")), "clearance": lambda: leg_clearance(O, args.scale),
             "keyconf": lambda: leg_keyconf(O, args.scale), "ompl_motions": lambda: leg_ompl(O, args.scale)}
