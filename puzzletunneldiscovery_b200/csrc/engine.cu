@@ -1055,48 +1055,121 @@ int osr_is_valid_states_device(osr_world* w, const double* d_q, int64_t n, uint8
 }
 
 // ---- segments ---------------------------------------------------------------------------------
+// Host buffers in, host buffers out.  Every device gets a contiguous index range; inside a range the segments move
+// in chunks: the upload of chunk c runs on a copy stream while the kernel of chunk c - 1 works, and the download of
+// chunk c - 1 is issued after the kernel of chunk c has been queued -- so that a device always has its next kernel
+// waiting, also when the caller's arrays are pageable and every copy blocks this thread until it is done (then the
+// copies used to be 15 % of a 2^20-segment touch call, and the devices of one handle took turns).
 static int transit_host(osr_world* w, const double* from, const double* to, int64_t n, const double* vd,
                         int64_t vd_count, double vd_scalar, int transition_mode, double* last_free,
                         double* first_hit, uint8_t* is_free, double* free_tau, double* touch_tau, int64_t* steps) {
-  int parts = (int)w->slots.size();
+  const int parts = (int)w->slots.size();
   int rc;
+  std::vector<int64_t> los(parts, 0), ms(parts, 0), cks(parts, 0);
+  std::vector<int> ncs(parts, 0);
+  int rounds = 0;
+  const bool per_seg_vd = vd && vd_count > 1;
   for (int i = 0; i < parts; i++) {
     Slot& s = w->slots[i];
     int64_t lo, hi;
     shard(n, parts, i, lo, hi);
-    int64_t m = hi - lo;
+    const int64_t m = hi - lo;
+    los[i] = lo; ms[i] = m;
     if (m == 0) continue;
+    // Few chunks: a chunk's kernel ends with its slowest segment (walks that graze an obstacle take 100x the
+    // average; measured 2-3 ms per extra chunk), so a range is split only where the copies it hides are worth it:
+    // estimated copy time (pageable arrays move at ~9 GB/s) / 10 ms chunks, at most 16.  Two or three become
+    // 1/8, 3/4, 1/8 of the range, which exposes only a small first upload and last download.  OSR_SEG_CHUNKS=1
+    // forces the single launch (A/B).
+    static const int max_chunks = [] { const char* e = getenv("OSR_SEG_CHUNKS"); return e ? std::max(1, std::min(16, atoi(e))) : 16; }();
+    const double bytes_per_seg = 112.0 + (per_seg_vd ? 8 : 0) + (last_free ? 56 : 0) + (first_hit ? 56 : 0) + (is_free ? 1 : 0) +
+                                 (free_tau ? 8 : 0) + (touch_tau ? 8 : 0) + (steps ? 8 : 0);
+    const int want = (int)std::min<double>(16.0, (double)m * bytes_per_seg / 9.0e6 / 10.0);
+    ncs[i] = std::min(max_chunks, want <= 1 ? 1 : (want <= 3 ? 3 : want));
+    cks[i] = (m + ncs[i] - 1) / ncs[i];     // (uniform; the three-chunk split is in chunk_range)
+    rounds = std::max(rounds, ncs[i]);
     CU(cudaSetDevice(s.dev));
     CU(s.in0.need((size_t)m * 56));
     CU(s.in1.need((size_t)m * 56));
-    CU(cudaMemcpyAsync(s.in0.p, from + 7 * lo, (size_t)m * 56, cudaMemcpyHostToDevice, s.stream));
-    CU(cudaMemcpyAsync(s.in1.p, to + 7 * lo, (size_t)m * 56, cudaMemcpyHostToDevice, s.stream));
-    const double* d_vd = nullptr;
-    if (vd && vd_count > 1) {
-      CU(s.vd.need((size_t)m * 8));
-      CU(cudaMemcpyAsync(s.vd.p, vd + lo, (size_t)m * 8, cudaMemcpyHostToDevice, s.stream));
-      d_vd = (const double*)s.vd.p;
+    if (per_seg_vd) CU(s.vd.need((size_t)m * 8));
+    if (last_free) CU(s.out[0].need((size_t)m * 56));
+    if (first_hit) CU(s.out[1].need((size_t)m * 56));
+    if (is_free) CU(s.out[2].need((size_t)m));
+    if (free_tau) CU(s.out[3].need((size_t)m * 8));
+    if (touch_tau) CU(s.out[4].need((size_t)m * 8));
+    if (steps) CU(s.out[5].need((size_t)m * 8));
+    for (int c = 0; c < 2 * ncs[i]; c++)
+      if (!s.feed_ev[c]) CU(cudaEventCreateWithFlags(&s.feed_ev[c], cudaEventDisableTiming));
+    CU(cudaEventRecord(s.evp, s.stream));              // the copy streams join behind what the main stream holds
+    CU(cudaStreamWaitEvent(s.stream2, s.evp, 0));
+    CU(cudaStreamWaitEvent(s.stream3, s.evp, 0));
+  }
+  auto chunk_range = [&](int i, int c, int64_t& c0, int64_t& len) {
+    if (ncs[i] == 3) {
+      const int64_t e = (ms[i] / 8 + 1023) / 1024 * 1024;
+      c0 = c == 0 ? 0 : (c == 1 ? e : ms[i] - e);
+      len = c == 1 ? ms[i] - 2 * e : e;
+    } else {
+      c0 = (int64_t)c * cks[i];
+      len = std::min(cks[i], ms[i] - c0);
     }
-    osr::SegOut O = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-    if (last_free) { CU(s.out[0].need((size_t)m * 56)); O.last_free = (double*)s.out[0].p; }
-    if (first_hit) { CU(s.out[1].need((size_t)m * 56)); O.first_hit = (double*)s.out[1].p; }
-    if (is_free) { CU(s.out[2].need((size_t)m)); O.is_free = (uint8_t*)s.out[2].p; }
-    if (free_tau) { CU(s.out[3].need((size_t)m * 8)); O.free_tau = (double*)s.out[3].p; }
-    if (touch_tau) { CU(s.out[4].need((size_t)m * 8)); O.touch_tau = (double*)s.out[4].p; }
-    if (steps) { CU(s.out[5].need((size_t)m * 8)); O.steps = (long long*)s.out[5].p; }
-    rc = launch_transit(w, s, (const double*)s.in0.p, (const double*)s.in1.p, m, d_vd, d_vd ? m : 1,
-                        (vd && vd_count == 1) ? vd[0] : vd_scalar, transition_mode, O);
-    if (rc) return rc;
-    if (last_free) CU(cudaMemcpyAsync(last_free + 7 * lo, O.last_free, (size_t)m * 56, cudaMemcpyDeviceToHost, s.stream));
-    if (first_hit) CU(cudaMemcpyAsync(first_hit + 7 * lo, O.first_hit, (size_t)m * 56, cudaMemcpyDeviceToHost, s.stream));
-    if (is_free) CU(cudaMemcpyAsync(is_free + lo, O.is_free, (size_t)m, cudaMemcpyDeviceToHost, s.stream));
-    if (free_tau) CU(cudaMemcpyAsync(free_tau + lo, O.free_tau, (size_t)m * 8, cudaMemcpyDeviceToHost, s.stream));
-    if (touch_tau) CU(cudaMemcpyAsync(touch_tau + lo, O.touch_tau, (size_t)m * 8, cudaMemcpyDeviceToHost, s.stream));
-    if (steps) CU(cudaMemcpyAsync(steps + lo, O.steps, (size_t)m * 8, cudaMemcpyDeviceToHost, s.stream));
+  };
+  auto download = [&](int i, int c) -> int {
+    Slot& s = w->slots[i];
+    int64_t c0, len;
+    chunk_range(i, c, c0, len);
+    const int64_t g0 = los[i] + c0;
+    CU(cudaSetDevice(s.dev));
+    CU(cudaStreamWaitEvent(s.stream3, s.feed_ev[2 * c + 1], 0));
+    if (last_free) CU(cudaMemcpyAsync(last_free + 7 * g0, (double*)s.out[0].p + 7 * c0, (size_t)len * 56, cudaMemcpyDeviceToHost, s.stream3));
+    if (first_hit) CU(cudaMemcpyAsync(first_hit + 7 * g0, (double*)s.out[1].p + 7 * c0, (size_t)len * 56, cudaMemcpyDeviceToHost, s.stream3));
+    if (is_free) CU(cudaMemcpyAsync(is_free + g0, (uint8_t*)s.out[2].p + c0, (size_t)len, cudaMemcpyDeviceToHost, s.stream3));
+    if (free_tau) CU(cudaMemcpyAsync(free_tau + g0, (double*)s.out[3].p + c0, (size_t)len * 8, cudaMemcpyDeviceToHost, s.stream3));
+    if (touch_tau) CU(cudaMemcpyAsync(touch_tau + g0, (double*)s.out[4].p + c0, (size_t)len * 8, cudaMemcpyDeviceToHost, s.stream3));
+    if (steps) CU(cudaMemcpyAsync(steps + g0, (long long*)s.out[5].p + c0, (size_t)len * 8, cudaMemcpyDeviceToHost, s.stream3));
+    return OSR_OK;
+  };
+  for (int c = 0; c <= rounds; c++) {
+    for (int i = 0; i < parts && c < rounds; i++) {      // upload + kernel of chunk c on every device
+      if (c >= ncs[i]) continue;
+      Slot& s = w->slots[i];
+      int64_t c0, len;
+      chunk_range(i, c, c0, len);
+      const int64_t g0 = los[i] + c0;
+      CU(cudaSetDevice(s.dev));
+      CU(cudaMemcpyAsync((double*)s.in0.p + 7 * c0, from + 7 * g0, (size_t)len * 56, cudaMemcpyHostToDevice, s.stream2));
+      CU(cudaMemcpyAsync((double*)s.in1.p + 7 * c0, to + 7 * g0, (size_t)len * 56, cudaMemcpyHostToDevice, s.stream2));
+      const double* d_vd = nullptr;
+      if (per_seg_vd) {
+        CU(cudaMemcpyAsync((double*)s.vd.p + c0, vd + g0, (size_t)len * 8, cudaMemcpyHostToDevice, s.stream2));
+        d_vd = (const double*)s.vd.p + c0;
+      }
+      CU(cudaEventRecord(s.feed_ev[2 * c], s.stream2));
+      CU(cudaStreamWaitEvent(s.stream, s.feed_ev[2 * c], 0));
+      osr::SegOut O = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+      if (last_free) O.last_free = (double*)s.out[0].p + 7 * c0;
+      if (first_hit) O.first_hit = (double*)s.out[1].p + 7 * c0;
+      if (is_free) O.is_free = (uint8_t*)s.out[2].p + c0;
+      if (free_tau) O.free_tau = (double*)s.out[3].p + c0;
+      if (touch_tau) O.touch_tau = (double*)s.out[4].p + c0;
+      if (steps) O.steps = (long long*)s.out[5].p + c0;
+      rc = launch_transit(w, s, (const double*)s.in0.p + 7 * c0, (const double*)s.in1.p + 7 * c0, len, d_vd, d_vd ? len : 1,
+                          (vd && vd_count == 1) ? vd[0] : vd_scalar, transition_mode, O);
+      if (rc) return rc;
+      CU(cudaEventRecord(s.feed_ev[2 * c + 1], s.stream));
+    }
+    for (int i = 0; i < parts && c > 0; i++) {           // download of chunk c - 1
+      if (c - 1 >= ncs[i]) continue;
+      rc = download(i, c - 1);
+      if (rc) return rc;
+    }
   }
   for (int i = 0; i < parts; i++) {
+    if (ms[i] == 0) continue;
     Slot& s = w->slots[i];
     CU(cudaSetDevice(s.dev));
+    CU(cudaEventRecord(s.evq, s.stream3));
+    CU(cudaStreamWaitEvent(s.stream, s.evq, 0));
     rc = check_device_error(w, s);
     if (rc) return rc;
   }
