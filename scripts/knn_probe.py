@@ -1,6 +1,8 @@
+#!/usr/bin/env python
+"""K6 timing and checksums (uniform, scaled and clustered states): the neighbour lists must not change when the kernel does."""
 import os, sys, time
 import numpy as np
-sys.path.insert(0, '/root/repo')
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import bench
 from puzzletunneldiscovery_b200 import pyosr, workloads as W
 uw = bench.make_world(pyosr.UnitWorld)
