@@ -104,6 +104,8 @@ struct Slot {  // one GPU
   int* err = nullptr;
   int* h_err = nullptr;                 // pinned landing word of the error flag (one small async copy per call)
   unsigned char* noalloc = nullptr;     // device address of g_noalloc_scratch on this GPU (cudaGetSymbolAddress)
+  double* small_in = nullptr;           // mapped page-locked buffers of the small-call path (SMALL_STATES states / labels)
+  uint8_t* small_out = nullptr;
   int grid_valid = 0, grid_transit = 0, grid_contacts = 0;
   int spill_cap = 0;
   DevBuf in0, in1, vd, out[6], recs, rowrec, seg, faces, cop, bary;
@@ -167,6 +169,7 @@ struct osr_world {
 namespace {
 
 constexpr int MAX_FEED_CHUNKS = 64;
+constexpr int64_t SMALL_STATES = 1024;   // host validity calls up to this size take the small-call path
 
 // cuStreamWriteValue64 (driver API stream memory operation) through the runtime's entry-point lookup, so the
 // library does not link libcuda: a stream-ordered 8-byte write costs ~1 us where a tiny cudaMemcpyAsync costs
@@ -215,6 +218,8 @@ void free_slot(Slot& s) {
   if (s.stage) cudaFreeHost(s.stage);
   if (s.h_ready) cudaFreeHost(s.h_ready);
   if (s.h_err) cudaFreeHost(s.h_err);
+  if (s.small_in) cudaFreeHost(s.small_in);
+  if (s.small_out) cudaFreeHost(s.small_out);
   for (auto& e : s.feed_ev) if (e) cudaEventDestroy(e);
   if (s.stream3) cudaStreamDestroy(s.stream3);
   if (s.stream2) cudaStreamDestroy(s.stream2);
@@ -252,6 +257,8 @@ int init_slot(osr_world* w, Slot& s, int dev) {
   CU(cudaMemset(s.err, 0, sizeof(int)));
   CU(cudaHostAlloc((void**)&s.h_err, sizeof(int), cudaHostAllocDefault));
   CU(cudaGetSymbolAddress((void**)&s.noalloc, g_noalloc_scratch));   // this device's copy of the static scratch
+  CU(cudaHostAlloc((void**)&s.small_in, SMALL_STATES * 56, cudaHostAllocMapped));
+  CU(cudaHostAlloc((void**)&s.small_out, SMALL_STATES, cudaHostAllocMapped));
   // persistent grid: as many blocks as fit, on every SM
   CU(cudaFuncSetAttribute(osr::k_is_valid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_PER_BLOCK));
   CU(cudaFuncSetAttribute(osr::k_ompl_motion, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_PER_BLOCK));
@@ -385,15 +392,16 @@ namespace {
 // the four tree-size variants of K1 x {resident input, stream-fed input}
 template <bool FEED, typename T>
 void launch_dfs_variant(const Slot& s, const osr::DfsParams& D, const T* d_q, long long n, uint8_t* d_out,
-                        cudaStream_t st) {
+                        cudaStream_t st, int grid = 0) {
+  const int g = grid > 0 ? grid : s.num_sms;   // persistent: one block per SM (fewer for the small-call path)
   if (s.dfs_variant == 0 && s.dfs_all_smem)
-    osr::k_valid_dfs<uint32_t, 32, true, FEED, T><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, st>>>(D, d_q, n, d_out);
+    osr::k_valid_dfs<uint32_t, 32, true, FEED, T><<<g, osr::DFS_THREADS, s.dfs_smem_bytes, st>>>(D, d_q, n, d_out);
   else if (s.dfs_variant == 0)
-    osr::k_valid_dfs<uint32_t, 32, false, FEED, T><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, st>>>(D, d_q, n, d_out);
+    osr::k_valid_dfs<uint32_t, 32, false, FEED, T><<<g, osr::DFS_THREADS, s.dfs_smem_bytes, st>>>(D, d_q, n, d_out);
   else if (s.dfs_variant == 1)
-    osr::k_valid_dfs<uint32_t, 64, false, FEED, T><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, st>>>(D, d_q, n, d_out);
+    osr::k_valid_dfs<uint32_t, 64, false, FEED, T><<<g, osr::DFS_THREADS, s.dfs_smem_bytes, st>>>(D, d_q, n, d_out);
   else
-    osr::k_valid_dfs<unsigned long long, 48, false, FEED, T><<<s.num_sms, osr::DFS_THREADS, s.dfs_smem_bytes, st>>>(D, d_q, n, d_out);
+    osr::k_valid_dfs<unsigned long long, 48, false, FEED, T><<<g, osr::DFS_THREADS, s.dfs_smem_bytes, st>>>(D, d_q, n, d_out);
 }
 
 }  // namespace
@@ -1017,12 +1025,38 @@ static int valid_states_host_impl(osr_world* w, const T* q, int64_t n, uint8_t* 
   return OSR_OK;
 }
 
+// Small host calls (a planner or a Python loop asking for a handful of states): what counts is the round trip, not
+// throughput.  The states are copied into a mapped page-locked buffer, ONE launch reads them over PCIe and writes the
+// labels into a second mapped buffer, one synchronisation: a memset, a launch and a wait instead of two copies, a
+// memset, two events, a launch, a flag copy and a wait (72 -> ~35 us for one state).  As many blocks as the states
+// need (a block preloads both trees: 129 KB), one state per lane.
+static int valid_small(osr_world* w, const double* q, int64_t n, uint8_t* out) {
+  std::lock_guard<std::mutex> lk(w->mu);
+  Slot& s = w->slots[0];
+  CU(cudaSetDevice(s.dev));
+  memcpy(s.small_in, q, (size_t)n * 56);
+  CU(cudaMemsetAsync(s.work, 0, 2 * sizeof(unsigned long long), s.stream));
+  osr::DfsParams D = dfs_params(w, s);
+  D.work_counter = s.work;
+  const int grid = (int)std::min<int64_t>(s.num_sms, (n + osr::DFS_THREADS - 1) / osr::DFS_THREADS);
+  launch_dfs_variant<false, double>(s, D, s.small_in, (long long)n, s.small_out, s.stream, grid);
+  CU(cudaGetLastError());
+  w->host_counters.kernel_launches++;
+  CU(cudaStreamSynchronize(s.stream));   // (the resident kernel raises no device error flag: nothing else to read)
+  memcpy(out, s.small_out, (size_t)n);
+  return OSR_OK;
+}
+
 template <typename T>
 static int valid_states_host(osr_world* w, const T* q, int64_t n, uint8_t* out) {
   int rc = check_ready(w);
   if (rc) return rc;
   if (n < 0 || (n > 0 && (!q || !out))) return fail(OSR_EINVAL, "bad arguments");
   if (n == 0) return OSR_OK;
+  if (std::is_same<T, double>::value && n <= SMALL_STATES && w->slots[0].dfs_variant >= 0 && !w->force_tile_kernel) {
+    static const bool no_small = getenv("OSR_NO_SMALL_PATH") != nullptr;   // A/B
+    if (!no_small) return valid_small(w, (const double*)q, n, out);
+  }
   g_feed_timed_out = false;
   rc = valid_states_host_impl<T>(w, q, n, out, launches_may_block());
   if (rc == OSR_ECUDA && g_feed_timed_out) {   // the fed kernel starved: same call, nothing to wait for
