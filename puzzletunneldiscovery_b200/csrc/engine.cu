@@ -169,7 +169,7 @@ struct osr_world {
 namespace {
 
 constexpr int MAX_FEED_CHUNKS = 64;
-constexpr int64_t SMALL_STATES = 1024;   // host validity calls up to this size take the small-call path
+constexpr int64_t SMALL_STATES = 16384;  // host validity calls up to this size take the small-call path
 
 // cuStreamWriteValue64 (driver API stream memory operation) through the runtime's entry-point lookup, so the
 // library does not link libcuda: a stream-ordered 8-byte write costs ~1 us where a tiny cudaMemcpyAsync costs
@@ -675,7 +675,7 @@ static int launch_valid(osr_world* w, Slot& s, const double* d_q, int64_t n, uin
   osr::KParams P = w->params(s);
   P.work_counter = work;
   if (lane == 0) CU(cudaEventRecord(s.ev0, s.stream));
-  osr::k_is_valid<<<s.grid_valid, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK, st>>>(P, d_q, (long long)n, d_out);
+  osr::k_is_valid<<<s.grid_valid, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK, st>>>(P, d_q, (long long)n, d_out, 32);
   CU(cudaGetLastError());
   if (lane == 0) CU(cudaEventRecord(s.ev1, s.stream));
   w->host_counters.kernel_launches++;
@@ -1036,13 +1036,32 @@ static int valid_small(osr_world* w, const double* q, int64_t n, uint8_t* out) {
   CU(cudaSetDevice(s.dev));
   memcpy(s.small_in, q, (size_t)n * 56);
   CU(cudaMemsetAsync(s.work, 0, 2 * sizeof(unsigned long long), s.stream));
-  osr::DfsParams D = dfs_params(w, s);
-  D.work_counter = s.work;
-  const int grid = (int)std::min<int64_t>(s.num_sms, (n + osr::DFS_THREADS - 1) / osr::DFS_THREADS);
-  launch_dfs_variant<false, double>(s, D, s.small_in, (long long)n, s.small_out, s.stream, grid);
+  static const int64_t tile_n = [] { const char* e = getenv("OSR_SMALL_TILE_N"); return e ? (int64_t)atoll(e) : SMALL_STATES; }();
+  bool tile_kernel = n <= tile_n;
+  if (tile_kernel) {
+    // a handful of states: one WARP per state on the warp-shared frontier of the tile kernel (32 lanes on one pose's
+    // node pairs) -- the lane-owned traversal would walk each pose's tree with a single lane (40 us for one state)
+    osr::KParams P = w->params(s);
+    P.work_counter = s.work;
+    int ppt = 1;                                        // poses per warp: one while the warps fit the GPU at once
+    while (ppt < 32 && (n + ppt - 1) / ppt > (int64_t)s.grid_valid * osr::WARPS_PER_BLOCK) ppt *= 2;
+    const int64_t tiles = (n + ppt - 1) / ppt;
+    const int grid = (int)std::min<int64_t>(s.grid_valid, (tiles + osr::WARPS_PER_BLOCK - 1) / osr::WARPS_PER_BLOCK);
+    osr::k_is_valid<<<grid, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK, s.stream>>>(P, s.small_in, (long long)n, s.small_out, ppt);
+  } else {
+    osr::DfsParams D = dfs_params(w, s);
+    D.work_counter = s.work;
+    const int grid = (int)std::min<int64_t>(s.num_sms, (n + osr::DFS_THREADS - 1) / osr::DFS_THREADS);
+    launch_dfs_variant<false, double>(s, D, s.small_in, (long long)n, s.small_out, s.stream, grid);
+  }
   CU(cudaGetLastError());
   w->host_counters.kernel_launches++;
-  CU(cudaStreamSynchronize(s.stream));   // (the resident kernel raises no device error flag: nothing else to read)
+  if (tile_kernel) {                     // the tile kernel can exhaust its spill area: read the flag with the labels
+    int rc = check_device_error(w, s);
+    if (rc) return rc;
+  } else {
+    CU(cudaStreamSynchronize(s.stream));   // (the resident lane-owned kernel raises no device error flag)
+  }
   memcpy(out, s.small_out, (size_t)n);
   return OSR_OK;
 }

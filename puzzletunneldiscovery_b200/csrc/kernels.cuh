@@ -524,6 +524,28 @@ __device__ __forceinline__ void set_pose(const KParams& P, WarpShared& S, int la
 #pragma unroll
   for (int k = 0; k < 3; k++) { S.Rd[9 + k][lane] = rel.t[k]; S.Rf[9 + k][lane] = (float)rel.t[k]; }
   S.eta[lane] = 2e-5f * (1.0f + fabsf((float)rel.t[0]) + fabsf((float)rel.t[1]) + fabsf((float)rel.t[2]));
+  // The reference does not renormalise the quaternion (lib/osr/osr_state.cc:16-25): for a non-unit one the map M
+  // above is 1 + |q|^2 (Rot - 1), not a rotation, and the 15-axis box test assumes one.  Boxes are then placed with
+  // the rotation of the NORMALISED quaternion and grown by |M - Rot|_F x (largest robot vertex radius), which bounds
+  // how far any robot point lands from where the boxes put it; the triangle tests keep M (S.Rd).  Same rule as
+  // make_box_pose of the lane-owned kernel (qnode.h).
+  const double n2 = q[3] * q[3] + q[4] * q[4] + q[5] * q[5] + q[6] * q[6];
+  if (fabs(n2 - 1.0) > 1e-9) {
+    double w = q[3], x = q[4], y = q[5], z = q[6];
+    quat_normalize(w, x, y, z);
+    Rigid rn, reln;
+    quat_to_rot(w, x, y, z, rn.R);
+    rn.t[0] = q[0]; rn.t[1] = q[1]; rn.t[2] = q[2];
+    relative_rigid(P.env_tf, rn, reln);
+    double dev = 0.0;
+#pragma unroll
+    for (int k = 0; k < 9; k++) {
+      const double d = rel.R[k] - reln.R[k];
+      dev += d * d;
+      S.Rf[k][lane] = (float)reln.R[k];
+    }
+    S.eta[lane] = __fadd_ru(S.eta[lane], __double2float_ru(1.0001 * sqrt(dev) * P.rob_radius));
+  }
 }
 
 __device__ __forceinline__ void ctx_init(const KParams& P, WarpCtx& C) {
@@ -556,22 +578,24 @@ constexpr int WARPS_PER_BLOCK = 4;
 // K1: batched validity.  out[i] = 1 iff state i is collision free (UnitWorld::isValid,
 // /root/reference/lib/osr/unit_world.cc:215-247).
 // ---------------------------------------------------------------------------------------------
+// ppt = poses per tile (32; 1 for small host calls: every warp then puts its 32 lanes on ONE pose's node pairs,
+// which is what the round trip of a handful of states is made of)
 __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_is_valid(KParams P, const double* __restrict__ q,
-                                                                    long long n, uint8_t* __restrict__ out) {
+                                                                    long long n, uint8_t* __restrict__ out, int ppt) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   WarpShared& S = reinterpret_cast<WarpShared*>(smem_raw)[threadIdx.x >> 5];
   const int lane = threadIdx.x & 31;
   WarpCtx C;
   ctx_init(P, C);
-  const long long ntiles = (n + 31) >> 5;
+  const long long ntiles = (n + ppt - 1) / ppt;
   unsigned long long nposes = 0;
   while (true) {
     unsigned long long tile = 0;
     if (lane == 0) tile = atomicAdd(P.work_counter, 1ull);
     tile = __shfl_sync(FULL, tile, 0);
     if ((long long)tile >= ntiles) break;
-    long long i = (long long)tile * 32 + lane;
-    bool have = i < n;
+    long long i = (long long)tile * ppt + lane;
+    bool have = lane < ppt && i < n;
     if (have) {
       double s[7];
 #pragma unroll

@@ -16,7 +16,7 @@ uw = bench.make_world(pyosr.UnitWorld)
 L, h = uw._L, uw._h
 q = W.random_states(1 << 16, 0)
 out = np.empty(1 << 16, np.uint8)
-for n in (1, 32, 1024, 16384, 65536):
+for n in (1, 32, 1024, 2048, 4096, 8192, 16384, 65536):
     qq = np.ascontiguousarray(q[:n])
     fn = lambda: check(L.osr_is_valid_states(h, qq.ctypes.data_as(C.POINTER(C.c_double)), n, out.ctypes.data_as(C.POINTER(C.c_uint8))))
     for _ in range(20):

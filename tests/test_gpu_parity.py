@@ -960,14 +960,15 @@ def test_knn_validate_edges_equals_the_two_separate_calls(uw_org):
 
 
 def test_small_host_calls_equal_the_batch(uw_org, uw_wt2, ow_org):
-    """Host calls of up to 1 024 states take the small-call path (mapped buffers, a grid sized to the states); their
+    """Host calls of up to 16 384 states take the small-call path (mapped buffers, one warp per state or per few
+    states on the warp-shared frontier, a grid sized to the states); their
     labels are those of the same states inside one large batch and of the oracle; a single state through
     is_valid_state too.  Repeated calls reuse the mapped buffers: a later, shorter call must not see an earlier one."""
     q = W.random_states(40000, seed=204)
     for uw in (uw_org, uw_wt2):
         big = uw.is_valid_states(q)
-        for n in (1024, 1, 31, 33, 384, 385, 1023, 1025, 7):
-            o = (n * 37) % 30000
+        for n in (1024, 1, 31, 33, 384, 385, 1023, 1025, 7, 1777, 5000, 16384, 16385, 3):
+            o = (n * 37) % 20000
             assert np.array_equal(uw.is_valid_states(q[o:o + n]), big[o:o + n])
         assert [bool(uw.is_valid_state(q[i])) for i in range(20)] == big[:20].tolist()
     assert np.array_equal(uw_org.is_valid_states(q[:1024]), ow_org.is_valid_states(q[:1024]).astype(bool))
