@@ -23,6 +23,23 @@ def task_chunk(n, total_chunks, index):
     return min(lo, n), max(min(hi, n), min(lo, n))
 
 
+def get_task_chunk(shape, total_chunks, index):
+    """partt.get_task_chunk (/root/reference/src/GP/pipeline/partt.py:10-35), literally: the index tuples of
+    numpy.ndindex(shape) cut by chunk_it -- boundaries from the RUNNING float sum `last += avg` (not k * avg), the
+    last chunk taking what is left."""
+    grand = [e for e in np.ndindex(tuple(int(x) for x in shape))]
+    avg = len(grand) / float(total_chunks)
+    out = []
+    last = 0.0
+    while last < len(grand) and len(out) < total_chunks:
+        out.append(grand[int(last):int(last + avg)])
+        last += avg
+    out[-1] += grand[int(last):]
+    if len(out) != total_chunks:
+        raise ValueError("len(out) (%d) != %d" % (len(out), total_chunks))
+    return out[index]
+
+
 def engine_shard(n, parts, i):
     """The range device slot i gets inside one handle (csrc/engine.cu: shard)."""
     return n * i // parts, n * (i + 1) // parts

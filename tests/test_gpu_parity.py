@@ -974,6 +974,38 @@ def test_small_host_calls_equal_the_batch(uw_org, uw_wt2, ow_org):
     assert np.array_equal(uw_org.is_valid_states(q[:1024]), ow_org.is_valid_states(q[:1024]).astype(bool))
 
 
+def test_batched_touch_stages_equal_the_reference_loop(uw_wt2, tmp_path):
+    """stages.calc_touch / stages.sample_touch (one device call per batch) against the reference's loops restated
+    literally -- touchq_util.calc_touch (:15-27) and the worker loop of preprocess_surface.sample_touch (:76-96),
+    one scalar transit_state_to_with_contact per sample -- under the same seed: same rays, same rows."""
+    import math
+    import os
+    from puzzletunneldiscovery_b200 import pyosr, sharding, stages
+    tv = np.load(os.path.join(W.assets_dir(), "alpha-1.2.org.tunnel.npz"))["TUNNEL_V"]
+    keys = uw_wt2.translate_to_unit_states(tv)
+
+    def sample_one_touch(uw, q0, stepping):              # touchq_util.py:8-13 on numpy's global generator
+        tr = stages.random_on_sphere(1.0)
+        aa = stages.random_within_sphere(2 * math.pi)
+        return uw.transit_state_to_with_contact(q0, pyosr.apply(q0, tr, aa), stepping)
+    np.random.seed(21)
+    rows = [sample_one_touch(uw_wt2, keys[3], VD_TOUCH) for _ in range(24)]
+    np.random.seed(21)
+    got = stages.calc_touch(uw_wt2, keys[3], 24, VD_TOUCH)
+    for k in range(5):   # the scalar call returns its taus as C floats (std::tuple<..., float, float>)
+        want = np.array([r[k] for r in rows])
+        have = got[k] if k < 3 else got[k].astype(np.float32).astype(np.float64)
+        assert np.array_equal(have, want)
+    tind = sharding.get_task_chunk((len(keys), 3), 4, 1)
+    np.random.seed(22)
+    ref = [(ki,) + tuple(sample_one_touch(uw_wt2, keys[ki], 2e-4)[:3]) for ki, _ in tind]
+    np.random.seed(22)
+    d = stages.sample_touch(uw_wt2, keys, tind, stepping=2e-4, out_fn=str(tmp_path / "touchq_batch-1.npz"))
+    assert np.array_equal(d["FROM_VI"], [r[0] for r in ref]) and np.array_equal(d["FREE_V"], np.array([r[1] for r in ref]))
+    assert np.array_equal(d["TOUCH_V"], np.array([r[2] for r in ref])) and np.array_equal(d["IS_INF"], [r[3] for r in ref])
+    assert np.array_equal(np.load(str(tmp_path / "touchq_batch-1.npz"))["TOUCH_V"], d["TOUCH_V"])
+
+
 @pytest.mark.gpu
 def test_clearance_stats_edge_cases(uw_org, ow_org, oracle_mod):
     """One and two points per candidate (median = the value / the mean of both), targets closer than one step
