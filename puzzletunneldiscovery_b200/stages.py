@@ -82,3 +82,25 @@ def sample_touch(uw, keys, tindices, stepping=None, rng=np.random, out_fn=None):
     if out_fn is not None:
         np.savez(out_fn, **d)
     return d
+
+
+def estimate_keyconf_clearance(uw, oskey_ompl, tindices, nsample, stepping=None, rng=np.random, out_fn=None):
+    """The worker loop of keyconf.estimate_keyconf_clearance (/root/reference/src/GP/pipeline/keyconf.py:300-315):
+    for every (key_index,) of `tindices` the OMPL-frame candidate oskey_ompl[key_index] is mapped to the unit frame,
+    `nsample` touch rays are shot from it at `stepping` (default uw.recommended_cres) and the distances from the
+    candidate to the rays' last free states are kept.  Returns DISTANCE_BATCH (len(tindices), nsample) and writes
+    `clearance_batch-<task>.npz` (key DISTANCE_BATCH) when out_fn is given.  The rays are drawn candidate by
+    candidate, sample by sample, like the reference's nested loops; the walks and the distances of ALL candidates
+    are one device call (K2 + K8, `UnitWorld.clearance_stats`), and only the distances come back."""
+    oskey_ompl = np.asarray(oskey_ompl, dtype=np.float64)
+    ki = [int(t[0]) for t in tindices]
+    if not ki:
+        d = np.zeros((0, nsample))
+    else:
+        q0 = np.asarray(uw.translate_ompl_to_unit(oskey_ompl[ki]), dtype=np.float64).reshape(-1, 7)
+        to = touch_targets(np.repeat(q0, nsample, axis=0), rng).reshape(len(ki), nsample, 7)
+        vd = uw.recommended_cres if stepping is None else stepping
+        _, d = uw.clearance_stats(q0, to, vd, with_distances=True)
+    if out_fn is not None:
+        np.savez(out_fn, DISTANCE_BATCH=d)
+    return d

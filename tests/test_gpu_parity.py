@@ -1004,6 +1004,19 @@ def test_batched_touch_stages_equal_the_reference_loop(uw_wt2, tmp_path):
     assert np.array_equal(d["FROM_VI"], [r[0] for r in ref]) and np.array_equal(d["FREE_V"], np.array([r[1] for r in ref]))
     assert np.array_equal(d["TOUCH_V"], np.array([r[2] for r in ref])) and np.array_equal(d["IS_INF"], [r[3] for r in ref])
     assert np.array_equal(np.load(str(tmp_path / "touchq_batch-1.npz"))["TOUCH_V"], d["TOUCH_V"])
+    # keyconf.estimate_keyconf_clearance's worker loop (:300-315): per candidate calc_touch + multi_distance
+    oskey = uw_wt2.translate_unit_to_ompl(keys)
+    tk = [(2,), (5,), (7,)]
+    np.random.seed(23)
+    want = []
+    for (k,) in tk:
+        uq = uw_wt2.translate_ompl_to_unit(oskey[k:k + 1])[0]
+        fv = stages.calc_touch(uw_wt2, uq, 16, uw_wt2.recommended_cres)[0]
+        want.append(pyosr.multi_distance(uq, fv))
+    np.random.seed(23)
+    got = stages.estimate_keyconf_clearance(uw_wt2, oskey, tk, 16, out_fn=str(tmp_path / "clearance_batch-0.npz"))
+    assert got.shape == (3, 16) and np.abs(got - np.array(want)).max() < 1e-13
+    assert np.array_equal(np.load(str(tmp_path / "clearance_batch-0.npz"))["DISTANCE_BATCH"], got)
 
 
 @pytest.mark.gpu
