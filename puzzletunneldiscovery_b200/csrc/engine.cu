@@ -106,6 +106,7 @@ struct Slot {  // one GPU
   unsigned char* noalloc = nullptr;     // device address of g_noalloc_scratch on this GPU (cudaGetSymbolAddress)
   double* small_in = nullptr;           // mapped page-locked buffers of the small-call path (SMALL_STATES states / labels)
   uint8_t* small_out = nullptr;
+  unsigned char* small_seg = nullptr;   // ... and of small segment calls (SMALL_SEGMENTS x 264 bytes: inputs + outputs)
   int grid_valid = 0, grid_transit = 0, grid_contacts = 0;
   int spill_cap = 0;
   DevBuf in0, in1, vd, out[6], recs, rowrec, seg, faces, cop, bary;
@@ -169,6 +170,7 @@ struct osr_world {
 namespace {
 
 constexpr int MAX_FEED_CHUNKS = 64;
+constexpr int64_t SMALL_SEGMENTS = 1024;  // host segment calls up to this size: mapped buffers, one launch, one wait
 constexpr int64_t SMALL_STATES = 16384;  // host validity calls up to this size take the small-call path
 
 // cuStreamWriteValue64 (driver API stream memory operation) through the runtime's entry-point lookup, so the
@@ -220,6 +222,7 @@ void free_slot(Slot& s) {
   if (s.h_err) cudaFreeHost(s.h_err);
   if (s.small_in) cudaFreeHost(s.small_in);
   if (s.small_out) cudaFreeHost(s.small_out);
+  if (s.small_seg) cudaFreeHost(s.small_seg);
   for (auto& e : s.feed_ev) if (e) cudaEventDestroy(e);
   if (s.stream3) cudaStreamDestroy(s.stream3);
   if (s.stream2) cudaStreamDestroy(s.stream2);
@@ -259,6 +262,7 @@ int init_slot(osr_world* w, Slot& s, int dev) {
   CU(cudaGetSymbolAddress((void**)&s.noalloc, g_noalloc_scratch));   // this device's copy of the static scratch
   CU(cudaHostAlloc((void**)&s.small_in, SMALL_STATES * 56, cudaHostAllocMapped));
   CU(cudaHostAlloc((void**)&s.small_out, SMALL_STATES, cudaHostAllocMapped));
+  CU(cudaHostAlloc((void**)&s.small_seg, SMALL_SEGMENTS * 264, cudaHostAllocMapped));
   // persistent grid: as many blocks as fit, on every SM
   CU(cudaFuncSetAttribute(osr::k_is_valid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_PER_BLOCK));
   CU(cudaFuncSetAttribute(osr::k_ompl_motion, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_PER_BLOCK));
@@ -1229,6 +1233,59 @@ static int transit_host(osr_world* w, const double* from, const double* to, int6
   return OSR_OK;
 }
 
+// Small segment calls (a Python loop walking one ray at a time): inputs and outputs in one mapped page-locked arena,
+// one launch with as many blocks as the segments need, one wait -- no staging copies, no events.
+static int transit_small(osr_world* w, const double* from, const double* to, int64_t n, const double* vd,
+                         int64_t vd_count, double vd_scalar, int transition_mode, double* last_free,
+                         double* first_hit, uint8_t* is_free, double* free_tau, double* touch_tau, int64_t* steps) {
+  Slot& s = w->slots[0];
+  CU(cudaSetDevice(s.dev));
+  unsigned char* a = s.small_seg;     // layout (n segments): from | to | vd | last_free | first_hit | taus | steps | flags
+  double* m_from = (double*)a;
+  double* m_to = m_from + 7 * n;
+  double* m_vd = m_to + 7 * n;
+  double* m_lf = m_vd + n;
+  double* m_fh = m_lf + 7 * n;
+  double* m_ft = m_fh + 7 * n;
+  double* m_tt = m_ft + n;
+  long long* m_st = (long long*)(m_tt + n);
+  uint8_t* m_if = (uint8_t*)(m_st + n);
+  memcpy(m_from, from, (size_t)n * 56);
+  memcpy(m_to, to, (size_t)n * 56);
+  const bool per_seg = vd && vd_count > 1;
+  if (per_seg) memcpy(m_vd, vd, (size_t)n * 8);
+  osr::SegOut O = {last_free ? m_lf : nullptr, first_hit ? m_fh : nullptr, is_free ? m_if : nullptr,
+                   free_tau ? m_ft : nullptr, touch_tau ? m_tt : nullptr, steps ? m_st : nullptr};
+  osr::KParams P = w->params(s);
+  CU(cudaMemsetAsync(s.work, 0, 2 * sizeof(unsigned long long), s.stream));
+  const int grid = (int)std::min<int64_t>(s.grid_transit, (n + osr::WARPS_PER_BLOCK - 1) / osr::WARPS_PER_BLOCK);
+  const double vds = (vd && vd_count == 1) ? vd[0] : vd_scalar;
+  if (s.transit_minb == 4)
+    osr::k_transit<4><<<grid, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK, s.stream>>>(
+        P, m_from, m_to, (long long)n, per_seg ? m_vd : nullptr, per_seg ? (long long)n : 1LL, vds, transition_mode, O);
+  else if (s.transit_minb == 3)
+    osr::k_transit<3><<<grid, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK, s.stream>>>(
+        P, m_from, m_to, (long long)n, per_seg ? m_vd : nullptr, per_seg ? (long long)n : 1LL, vds, transition_mode, O);
+  else
+    osr::k_transit<2><<<grid, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK, s.stream>>>(
+        P, m_from, m_to, (long long)n, per_seg ? m_vd : nullptr, per_seg ? (long long)n : 1LL, vds, transition_mode, O);
+  CU(cudaGetLastError());
+  w->host_counters.kernel_launches++;
+  int rc = check_device_error(w, s);   // the flag and the wait
+  if (rc) return rc;
+  if (last_free) memcpy(last_free, m_lf, (size_t)n * 56);
+  if (first_hit) memcpy(first_hit, m_fh, (size_t)n * 56);
+  if (is_free) memcpy(is_free, m_if, (size_t)n);
+  if (free_tau) memcpy(free_tau, m_ft, (size_t)n * 8);
+  if (touch_tau) memcpy(touch_tau, m_tt, (size_t)n * 8);
+  if (steps) memcpy(steps, m_st, (size_t)n * 8);
+  return OSR_OK;
+}
+static bool small_segments_ok(const osr_world* w, int64_t n) {
+  static const bool off = getenv("OSR_NO_SMALL_PATH") != nullptr;
+  return !off && n <= SMALL_SEGMENTS && !w->seg_dfs;
+}
+
 int osr_transit_states_to_with_contact(osr_world* w, const double* from, const double* to, int64_t n,
                                        const double* vd, int64_t vd_count, double* last_free, double* first_hit,
                                        uint8_t* is_free, double* free_tau, double* touch_tau, int64_t* steps) {
@@ -1242,6 +1299,8 @@ int osr_transit_states_to_with_contact(osr_world* w, const double* from, const d
   for (int64_t i = 0; i < vd_count; i++)
     if (vd[i] < 0.0) return fail(OSR_EINVAL, "verify_delta must not be negative");
   std::lock_guard<std::mutex> lk(w->mu);
+  if (small_segments_ok(w, n))
+    return transit_small(w, from, to, n, vd, vd_count, 0.0, 0, last_free, first_hit, is_free, free_tau, touch_tau, steps);
   return transit_host(w, from, to, n, vd, vd_count, 0.0, 0, last_free, first_hit, is_free, free_tau, touch_tau, steps);
 }
 
@@ -1253,6 +1312,8 @@ int osr_is_valid_transitions(osr_world* w, const double* from, const double* to,
   if (initial_verify_delta < 0.0) return fail(OSR_EINVAL, "verify_delta must not be negative");
   if (n == 0) return OSR_OK;
   std::lock_guard<std::mutex> lk(w->mu);
+  if (small_segments_ok(w, n))
+    return transit_small(w, from, to, n, nullptr, 1, initial_verify_delta, 1, nullptr, nullptr, out, nullptr, nullptr, nullptr);
   return transit_host(w, from, to, n, nullptr, 1, initial_verify_delta, 1, nullptr, nullptr, out, nullptr, nullptr,
                       nullptr);
 }

@@ -1019,6 +1019,29 @@ def test_batched_touch_stages_equal_the_reference_loop(uw_wt2, tmp_path):
     assert np.array_equal(np.load(str(tmp_path / "clearance_batch-0.npz"))["DISTANCE_BATCH"], got)
 
 
+def test_small_segment_calls_equal_the_batch(uw_wt2, uw_org):
+    """Segment calls of up to 1 024 segments take the small-call path (one mapped arena for inputs and outputs, a
+    grid sized to the segments); all six outputs are those of the same segments inside one large batch -- scalar or
+    per-segment verify_delta, transit and is_valid_transition semantics, repeated calls on the shared arena."""
+    import os
+    tv = np.load(os.path.join(W.assets_dir(), "alpha-1.2.org.tunnel.npz"))["TUNNEL_V"]
+    fr, to = W.touch_rays(uw_wt2.translate_to_unit_states(tv), 3000, seed=205)
+    big = uw_wt2.transit_states_to_with_contact(fr, to, VD_TOUCH, with_steps=True)
+    vds = np.where(np.arange(3000) % 2 == 0, VD_TOUCH, 2e-4)
+    bigv = uw_wt2.transit_states_to_with_contact(fr, to, vds, with_steps=True)
+    lab = uw_wt2.is_valid_transitions(fr, to, 1e-3)
+    for n in (1024, 1, 5, 64, 1023, 1025, 2):
+        o = (n * 13) % 1500
+        sl = slice(o, o + n)
+        a = uw_wt2.transit_states_to_with_contact(fr[sl], to[sl], VD_TOUCH, with_steps=True)
+        assert all(np.array_equal(x, y[sl]) for x, y in zip(a, big))
+        b = uw_wt2.transit_states_to_with_contact(fr[sl], to[sl], vds[sl], with_steps=True)
+        assert all(np.array_equal(x, y[sl]) for x, y in zip(b, bigv))
+        assert np.array_equal(uw_wt2.is_valid_transitions(fr[sl], to[sl], 1e-3), lab[sl])
+    one = uw_wt2.transit_state_to_with_contact(fr[7], to[7], VD_TOUCH)
+    assert np.array_equal(one[0], big[0][7]) and np.array_equal(one[1], big[1][7]) and bool(one[2]) == bool(big[2][7])
+
+
 @pytest.mark.gpu
 def test_clearance_stats_edge_cases(uw_org, ow_org, oracle_mod):
     """One and two points per candidate (median = the value / the mean of both), targets closer than one step
