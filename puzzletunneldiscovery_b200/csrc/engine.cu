@@ -1442,6 +1442,18 @@ int osr_is_disentangled_states(osr_world* w, const double* q, int64_t n, uint8_t
   }
   osr::Rigid env_tf;
   osr::state_to_rigid(w->perturb, env_tf);
+  static const bool no_small = getenv("OSR_NO_SMALL_PATH") != nullptr;
+  if (n <= SMALL_STATES && !no_small) {   // small call: mapped buffers, one launch, one wait (as valid_small)
+    Slot& s = w->slots[0];
+    CU(cudaSetDevice(s.dev));
+    memcpy(s.small_in, q, (size_t)n * 56);
+    osr::k_disentangled<<<(unsigned)((n + 255) / 256), 256, 0, s.stream>>>(env_tf, bp, s.small_in, (long long)n, s.small_out);
+    CU(cudaGetLastError());
+    w->host_counters.kernel_launches++;
+    CU(cudaStreamSynchronize(s.stream));
+    memcpy(out, s.small_out, (size_t)n);
+    return OSR_OK;
+  }
   int parts = (int)w->slots.size();
   for (int i = 0; i < parts; i++) {
     Slot& s = w->slots[i];

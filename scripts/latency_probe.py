@@ -40,5 +40,9 @@ for n in (1, 64):
     print("transit_states_to_with_contact n=%3d: %8.1f us per call" % (n, (time.perf_counter() - t) / 100 * 1e6))
 t = time.perf_counter()
 for i in range(300):
+    uw.is_disentangled(q[i])
+print("pyosr.is_disentangled (one state, Python): %.1f us per call" % ((time.perf_counter() - t) / 300 * 1e6))
+t = time.perf_counter()
+for i in range(300):
     uw.is_valid_state(q[i])
 print("pyosr.is_valid_state (one state, Python): %.1f us per call" % ((time.perf_counter() - t) / 300 * 1e6))

@@ -971,6 +971,9 @@ def test_small_host_calls_equal_the_batch(uw_org, uw_wt2, ow_org):
             o = (n * 37) % 20000
             assert np.array_equal(uw.is_valid_states(q[o:o + n]), big[o:o + n])
         assert [bool(uw.is_valid_state(q[i])) for i in range(20)] == big[:20].tolist()
+        dis = uw.is_disentangled_states(q)
+        assert np.array_equal(uw.is_disentangled_states(q[100:1100]), dis[100:1100])
+        assert [bool(uw.is_disentangled(q[i])) for i in range(20)] == dis[:20].tolist() and 0 < dis.sum() < len(dis)
     assert np.array_equal(uw_org.is_valid_states(q[:1024]), ow_org.is_valid_states(q[:1024]).astype(bool))
 
 
