@@ -264,7 +264,8 @@ int init_slot(osr_world* w, Slot& s, int dev) {
   CU(cudaHostAlloc((void**)&s.small_out, SMALL_STATES, cudaHostAllocMapped));
   CU(cudaHostAlloc((void**)&s.small_seg, SMALL_SEGMENTS * 264, cudaHostAllocMapped));
   // persistent grid: as many blocks as fit, on every SM
-  CU(cudaFuncSetAttribute(osr::k_is_valid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_PER_BLOCK));
+  CU(cudaFuncSetAttribute(osr::k_is_valid<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_PER_BLOCK));
+  CU(cudaFuncSetAttribute(osr::k_is_valid<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_PER_BLOCK));
   CU(cudaFuncSetAttribute(osr::k_ompl_motion, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_PER_BLOCK));
   CU(cudaFuncSetAttribute(osr::k_transit<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_PER_BLOCK));
   CU(cudaFuncSetAttribute(osr::k_transit<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_PER_BLOCK));
@@ -276,7 +277,7 @@ int init_slot(osr_world* w, Slot& s, int dev) {
   CU(cudaFuncSetAttribute(osr::k_contacts, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_PER_BLOCK));
   int nsm = 0, bpsm = 0, b2 = 0, b3 = 0;
   CU(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev));
-  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bpsm, osr::k_is_valid, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK));
+  CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bpsm, osr::k_is_valid<false>, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK));
   if (s.transit_minb == 4) CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b2, osr::k_transit<4>, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK));
   else if (s.transit_minb == 3) CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b2, osr::k_transit<3>, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK));
   else CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b2, osr::k_transit<2>, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK));
@@ -679,7 +680,7 @@ static int launch_valid(osr_world* w, Slot& s, const double* d_q, int64_t n, uin
   osr::KParams P = w->params(s);
   P.work_counter = work;
   if (lane == 0) CU(cudaEventRecord(s.ev0, s.stream));
-  osr::k_is_valid<<<s.grid_valid, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK, st>>>(P, d_q, (long long)n, d_out, 32);
+  osr::k_is_valid<false><<<s.grid_valid, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK, st>>>(P, d_q, (long long)n, d_out, 32);
   CU(cudaGetLastError());
   if (lane == 0) CU(cudaEventRecord(s.ev1, s.stream));
   w->host_counters.kernel_launches++;
@@ -1039,20 +1040,29 @@ static int valid_small(osr_world* w, const double* q, int64_t n, uint8_t* out) {
   Slot& s = w->slots[0];
   CU(cudaSetDevice(s.dev));
   memcpy(s.small_in, q, (size_t)n * 56);
-  CU(cudaMemsetAsync(s.work, 0, 2 * sizeof(unsigned long long), s.stream));
   static const int64_t tile_n = [] { const char* e = getenv("OSR_SMALL_TILE_N"); return e ? (int64_t)atoll(e) : SMALL_STATES; }();
   bool tile_kernel = n <= tile_n;
   if (tile_kernel) {
     // a handful of states: one WARP per state on the warp-shared frontier of the tile kernel (32 lanes on one pose's
     // node pairs) -- the lane-owned traversal would walk each pose's tree with a single lane (40 us for one state)
     osr::KParams P = w->params(s);
-    P.work_counter = s.work;
+    P.work_counter = nullptr;                           // a warp per tile (the grid below covers every tile)
     int ppt = 1;                                        // poses per warp: one while the warps fit the GPU at once
     while (ppt < 32 && (n + ppt - 1) / ppt > (int64_t)s.grid_valid * osr::WARPS_PER_BLOCK) ppt *= 2;
     const int64_t tiles = (n + ppt - 1) / ppt;
     const int grid = (int)std::min<int64_t>(s.grid_valid, (tiles + osr::WARPS_PER_BLOCK - 1) / osr::WARPS_PER_BLOCK);
-    osr::k_is_valid<<<grid, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK, s.stream>>>(P, s.small_in, (long long)n, s.small_out, ppt);
+    if (tiles > (int64_t)grid * osr::WARPS_PER_BLOCK) {  // (cannot happen below SMALL_STATES; kept for safety)
+      CU(cudaMemsetAsync(s.work, 0, 2 * sizeof(unsigned long long), s.stream));
+      P.work_counter = s.work;
+    }
+    // few poses per warp: a round descends BOTH trees (half the rounds; OSR_SMALL_BOTH=0 restores one tree a round)
+    static const int both_max = [] { const char* e = getenv("OSR_SMALL_BOTH"); return e ? atoi(e) : 4; }();
+    if (ppt <= both_max)
+      osr::k_is_valid<true><<<grid, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK, s.stream>>>(P, s.small_in, (long long)n, s.small_out, ppt);
+    else
+      osr::k_is_valid<false><<<grid, osr::WARPS_PER_BLOCK * 32, SMEM_PER_BLOCK, s.stream>>>(P, s.small_in, (long long)n, s.small_out, ppt);
   } else {
+    CU(cudaMemsetAsync(s.work, 0, 2 * sizeof(unsigned long long), s.stream));
     osr::DfsParams D = dfs_params(w, s);
     D.work_counter = s.work;
     const int grid = (int)std::min<int64_t>(s.num_sms, (n + osr::DFS_THREADS - 1) / osr::DFS_THREADS);

@@ -353,7 +353,10 @@ enum { MODE_VALID = 0, MODE_SEGMENT = 1, MODE_CONTACTS = 2, MODE_SWEPT = 3, MODE
 // the window without another traversal.  The windows behind the keeping one are blocked (the walk will be at a
 // contact or needs a fresh traversal there anyway); the keeping window itself blocks only when it keeps more than
 // C.surv_limit pairs.
-template <int MODE>
+// BOTH (small validity calls only): a pair of two inner nodes is replaced by its four child-by-child pairs, so one
+// round descends a level in BOTH trees.  More box tests, about half as many rounds: what the latency of one pose
+// is made of.  Pruning stays conservative either way, so the labels do not depend on it.
+template <int MODE, bool BOTH = false>
 __device__ __forceinline__ unsigned traverse_tile(const KParams& P, WarpShared& S, WarpCtx& C, unsigned alive,
                                                   int lane, int state_base = 0, ContactRec* recs = nullptr,
                                                   unsigned long long* rec_count = nullptr,
@@ -445,7 +448,7 @@ __device__ __forceinline__ unsigned traverse_tile(const KParams& P, WarpShared& 
       if (m_swept && (dead & alive) == alive) { C.nspill = 0; break; }   // every window abandoned
       continue;
     }
-    if (top > STACK_CAP - 32) {  // make room: move the oldest entries to global memory
+    if (top > STACK_CAP - (BOTH ? 96 : 32)) {  // make room: move the oldest entries to global memory
       if (C.nspill + SPILL_CHUNK > C.spill_cap) {
         if (m_swept) { hits = alive; C.nspill = 0; break; }   // no room: nothing proven, every window blocked
         C.overflow = true;
@@ -471,8 +474,8 @@ __device__ __forceinline__ unsigned traverse_tile(const KParams& P, WarpShared& 
     __syncwarp();
     unsigned pose = entry_pose(e), n1 = entry_n1(e), n2 = entry_n2(e);
     act = act && !((dead >> pose) & 1u);
-    bool leafpair = false, expand = false;
-    unsigned long long c0 = 0, c1 = 0, lf = 0;
+    bool leafpair = false, expand = false, four = false;
+    unsigned long long c0 = 0, c1 = 0, c2 = 0, c3 = 0, lf = 0;
     if (act) {
       C.n_bv++;
       const float4* na = P.env.nodes + (size_t)4 * n1;
@@ -489,7 +492,13 @@ __device__ __forceinline__ unsigned traverse_tile(const KParams& P, WarpShared& 
           // descent rule: split the box of larger volume (FCL compares extent^2; labels do not depend on it)
           float s1 = a3.x * a3.y * a3.z;
           float s2 = b3.x * b3.y * b3.z;
-          if (l2 < 0 || (l1 >= 0 && s1 > s2)) {  // descend the env node
+          if (BOTH && l1 >= 0 && l2 >= 0) {
+            four = true;
+            c0 = make_entry(pose, (unsigned)l1, (unsigned)l2);
+            c1 = make_entry(pose, (unsigned)l1 + 1u, (unsigned)l2);
+            c2 = make_entry(pose, (unsigned)l1, (unsigned)l2 + 1u);
+            c3 = make_entry(pose, (unsigned)l1 + 1u, (unsigned)l2 + 1u);
+          } else if (l2 < 0 || (l1 >= 0 && s1 > s2)) {  // descend the env node
             c0 = make_entry(pose, (unsigned)l1, n2);
             c1 = make_entry(pose, (unsigned)l1 + 1u, n2);
           } else {
@@ -503,12 +512,17 @@ __device__ __forceinline__ unsigned traverse_tile(const KParams& P, WarpShared& 
     if (leafpair) S.leafq[nleaf + __popc(bl & ltmask)] = lf;
     nleaf += __popc(bl);
     unsigned be = __ballot_sync(FULL, expand);
+    unsigned b4 = BOTH ? __ballot_sync(FULL, four) : 0u;
     if (expand) {
-      int off = top + 2 * __popc(be & ltmask);
+      int off = top + 2 * (__popc(be & ltmask) + __popc(b4 & ltmask));
       S.stack[off] = c0;
       S.stack[off + 1] = c1;
+      if (BOTH && four) {
+        S.stack[off + 2] = c2;
+        S.stack[off + 3] = c3;
+      }
     }
-    top += 2 * __popc(be);
+    top += 2 * (__popc(be) + __popc(b4));
     __syncwarp();
   }
   return hits;
@@ -580,6 +594,7 @@ constexpr int WARPS_PER_BLOCK = 4;
 // ---------------------------------------------------------------------------------------------
 // ppt = poses per tile (32; 1 for small host calls: every warp then puts its 32 lanes on ONE pose's node pairs,
 // which is what the round trip of a handful of states is made of)
+template <bool BOTH>
 __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_is_valid(KParams P, const double* __restrict__ q,
                                                                     long long n, uint8_t* __restrict__ out, int ppt) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -588,11 +603,16 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_is_valid(KParams P, co
   WarpCtx C;
   ctx_init(P, C);
   const long long ntiles = (n + ppt - 1) / ppt;
+  const bool fixed = P.work_counter == nullptr;
   unsigned long long nposes = 0;
   while (true) {
     unsigned long long tile = 0;
-    if (lane == 0) tile = atomicAdd(P.work_counter, 1ull);
-    tile = __shfl_sync(FULL, tile, 0);
+    if (fixed) {   // small host calls: a warp per tile, no counter to reset before the launch
+      tile = (unsigned long long)blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
+    } else {
+      if (lane == 0) tile = atomicAdd(P.work_counter, 1ull);
+      tile = __shfl_sync(FULL, tile, 0);
+    }
     if ((long long)tile >= ntiles) break;
     long long i = (long long)tile * ppt + lane;
     bool have = lane < ppt && i < n;
@@ -605,10 +625,10 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_is_valid(KParams P, co
     unsigned alive = __ballot_sync(FULL, have);
     nposes += __popc(alive);
     __syncwarp();
-    unsigned hits = traverse_tile<MODE_VALID>(P, S, C, alive, lane);
+    unsigned hits = traverse_tile<MODE_VALID, BOTH>(P, S, C, alive, lane);
     if (have) out[i] = (hits >> lane & 1u) ? 0 : 1;
     __syncwarp();
-    if (C.overflow) break;
+    if (C.overflow || fixed) break;
   }
   ctx_flush(P, C, nposes, lane);
 }

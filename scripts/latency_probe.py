@@ -28,6 +28,17 @@ for n in (1, 32, 1024, 2048, 4096, 8192, 16384, 65536):
     dt = (time.perf_counter() - t) / reps
     print("osr_is_valid_states n=%6d: %8.1f us per call  (%.3e configs/s)" % (n, dt * 1e6, n / dt))
 v = uw.is_valid_states(q[:4096])
+for name, qs in (("random", q[:256]), ("free", q[:4096][v][:256])):
+    qs = np.ascontiguousarray(qs)
+    o1 = np.empty(1, np.uint8)
+    ptrs = [(qs[i:i + 1].ctypes.data_as(C.POINTER(C.c_double))) for i in range(len(qs))]
+    op = o1.ctypes.data_as(C.POINTER(C.c_uint8))
+    for rep in range(3):
+        t = time.perf_counter()
+        for p_ in ptrs:
+            L.osr_is_valid_states(h, p_, 1, op)
+        dt = (time.perf_counter() - t) / len(ptrs)
+    print("osr_is_valid_states, one %s state per call over %d different states: %.1f us per call" % (name, len(ptrs), dt * 1e6))
 fr, to = W.touch_rays(q[:4096][v][:64], 64, seed=1)
 for n in (1, 64):
     a, b = np.ascontiguousarray(fr[:n]), np.ascontiguousarray(to[:n])
