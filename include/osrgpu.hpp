@@ -245,5 +245,39 @@ class UnitWorld {
   bool scaled_ = false;
 };
 
+// The batched validators of OmplDriver (/root/reference/lib/pyse3ompl/ompldriver.cc:566-621, setters
+// ompldriver.h:107-116) on a UnitWorld: rows are OMPL-frame states x y z qx qy qz qw, the results int 0/1 like the
+// reference's Eigen::VectorXi.  validateStates = FCLStateValidityChecker::isValid (bounds AND collision free);
+// validateMotionPairs = DiscreteMotionValidator::checkMotion at the resolution given to setCDRes.
+class OmplValidators {
+ public:
+  explicit OmplValidators(const UnitWorld& w) : w_(w) {}
+  void setBB(const StateTrans& mins, const StateTrans& maxs) {
+    for (int k = 0; k < 3; k++) { bounds_[k] = mins[k]; bounds_[3 + k] = maxs[k]; }
+    have_bounds_ = true;
+  }
+  void setCDRes(double cdres) { cdres_ = cdres; }
+  std::vector<int> validateStates(const ArrayOfStates& qs0) const {
+    std::vector<uint8_t> o(qs0.size());
+    check(osr_ompl_validate_states(w_.handle(), qs0.empty() ? nullptr : qs0[0].data(), (int64_t)qs0.size(),
+                                   have_bounds_ ? bounds_ : nullptr, o.data()));
+    return std::vector<int>(o.begin(), o.end());
+  }
+  std::vector<int> validateMotionPairs(const ArrayOfStates& qs0, const ArrayOfStates& qs1) const {
+    if (!have_bounds_) throw std::runtime_error("osrgpu: validateMotionPairs needs setBB (the space's extent)");
+    const size_t n = std::min(qs0.size(), qs1.size());   // the reference's loop bound
+    std::vector<uint8_t> o(n);
+    check(osr_ompl_check_motions(w_.handle(), n ? qs0[0].data() : nullptr, n ? qs1[0].data() : nullptr, (int64_t)n,
+                                 bounds_, cdres_, o.data(), nullptr));
+    return std::vector<int>(o.begin(), o.end());
+  }
+
+ private:
+  const UnitWorld& w_;
+  double bounds_[6] = {0, 0, 0, 0, 0, 0};
+  bool have_bounds_ = false;
+  double cdres_ = 0.01;   // OMPL's default state-validity-checking resolution (1 % of the extent)
+};
+
 }  // namespace osrgpu
 #endif  // OSRGPU_HPP

@@ -3,6 +3,7 @@
 // GPU and compares what it writes with the Python layer's answers on the same states.
 //   usage: host_check <env.obj> <rob.obj> <states.f64> <n> <out.bin> [centre_x centre_y centre_z]
 //   usage: host_check --no-device <env.obj> <rob.obj>     (set-up and error behaviour without a CUDA device)
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -151,6 +152,25 @@ int main(int argc, char** argv) {
   ArrayOfStates un = w.translateOMPLStateToUnitState(om);
   put(out, om[0].data(), 28);
   put(out, un[0].data(), 28);
+
+  // OmplDriver's batched validators on the OMPL-frame images of the first 512 states and of the segments
+  {
+    OmplValidators ov(w);
+    const size_t k = std::min<size_t>(n, 512);
+    ArrayOfStates oq = w.translateUnitStateToOMPLState(ArrayOfStates(qs.begin(), qs.begin() + k));
+    REQUIRE(throws([&] { ov.validateMotionPairs(oq, oq); }));          // no extent yet
+    std::vector<int> v0 = ov.validateStates(oq);                       // collision only
+    ov.setBB(StateTrans{-100, -100, -100}, StateTrans{100, 100, 100});
+    ov.setCDRes(0.002);
+    std::vector<int> v1 = ov.validateStates(oq);                       // bounds AND collision
+    ArrayOfStates of = w.translateUnitStateToOMPLState(fr), ot = w.translateUnitStateToOMPLState(to);
+    std::vector<int> mv = ov.validateMotionPairs(of, ot);
+    const uint64_t kk = k;
+    put(out, &kk, 1);
+    put(out, v0.data(), k);
+    put(out, v1.data(), k);
+    put(out, mv.data(), (size_t)m);
+  }
 
   REQUIRE(throws([&] { w.isValidTransitions(fr, ArrayOfStates(), vd); }) || m == 0);   // shape mismatch
   std::fclose(out);

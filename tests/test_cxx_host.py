@@ -98,4 +98,15 @@ def test_cxx_caller_gets_the_python_layers_answers(tmp_path, uw_org):
     un = take(np.float64, 28).reshape(4, 7)
     assert np.array_equal(om, uw.translate_unit_to_ompl(q[:4]))
     assert np.array_equal(un, uw.translate_ompl_to_unit(om))
+    k = int(take(np.uint64, 1)[0])
+    assert k == 512
+    oq = uw.translate_unit_to_ompl(q[:k])
+    bounds = ((-100.0, -100.0, -100.0), (100.0, 100.0, 100.0))
+    v0 = take(np.int32, k)
+    v1 = take(np.int32, k)
+    mv = take(np.int32, m)
+    assert np.array_equal(v0, uw.ompl_validate_states(oq)) and 0 < v0.sum() < k
+    assert np.array_equal(v1, uw.ompl_validate_states(oq, bounds))
+    assert np.array_equal(mv, uw.ompl_validate_motion_pairs(uw.translate_unit_to_ompl(fr),
+                                                            uw.translate_unit_to_ompl(to), bounds, 0.002))
     assert pos == len(buf)
