@@ -260,10 +260,16 @@ def run_ours(args):
     n, K, Wm = args.states, args.steps, args.warmup
 
     # inputs: NBATCH distinct seeded batches, pinned on the host and resident in HBM
-    host_q = [torch.from_numpy(W.random_states(n, batch_seed(rank, b))).pin_memory() for b in range(NBATCH)]
+    # (page-locked through the library's own allocator, osr_host_alloc: memory on the NUMA node of this rank's GPU --
+    # a rank whose buffers sit on the other socket uploads at about half the PCIe rate and sets the max over ranks)
+    def pinned(a):
+        t = torch.from_numpy(pyosr.pinned_empty(a.shape, a.dtype))
+        t.copy_(torch.from_numpy(a))
+        return t
+    host_q = [pinned(W.random_states(n, batch_seed(rank, b))) for b in range(NBATCH)]
     dev_q = [q.to(dev) for q in host_q]
     dev_out = torch.empty(n, dtype=torch.uint8, device=dev)
-    host_out = torch.empty(n, dtype=torch.uint8).pin_memory()
+    host_out = torch.from_numpy(pyosr.pinned_empty(n, np.uint8))
     torch.cuda.synchronize()
 
     def launch(b):
@@ -323,11 +329,15 @@ def run_ours(args):
     if sampler:
         sampler.window(te0, te1)
     te = torch.tensor([te1 - te0], dtype=torch.float64, device=dev)
+    e2e_rank_rates = [n * K / (te1 - te0)]
     if world > 1:
+        allte = [torch.zeros_like(te) for _ in range(world)]
+        dist.all_gather(allte, te)
+        e2e_rank_rates = [n * K / float(t.item()) for t in allte]
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_value = world * n * K / float(te.item())
     # the same call with float32 host samples (what the reference's Python callers hold; widened on the device)
-    host_q32 = [q.to(torch.float32).pin_memory() for q in host_q[:4]]
+    host_q32 = [pinned(q.to(torch.float32).numpy()) for q in host_q[:4]]
 
     def e2e_call32(b):
         check(L.osr_is_valid_states_f32(h, C.cast(host_q32[b].data_ptr(), C.POINTER(C.c_float)), n,
@@ -468,6 +478,9 @@ def run_ours(args):
                 "pcie_h2d_gbs_measured": h2d_gbs,
                 "pcie_bound_configs_per_s": world * n / (n * 56 / (h2d_gbs * 1e9)),
                 "frac_of_pcie_bound": e2e_value / (world * n / (n * 56 / (h2d_gbs * 1e9))),
+                "per_rank": e2e_rank_rates,
+                "host_memory": "osr_host_alloc: page-locked, first touched on the NUMA node of the rank's GPU"
+                               + (" (off: OSR_NO_NUMA_LOCAL)" if os.environ.get("OSR_NO_NUMA_LOCAL") else ""),
                 "note": "osr_is_valid_states on pinned host float64 states: the upload (56 B/state) is the bound; "
                         "pcie_h2d_gbs_measured = plain pinned copy of the same buffer on rank 0"},
         "e2e_f32_states": {"value": e2e32_value, "unit": UNIT, "h2d_bytes_per_step": n * 28, "d2h_bytes_per_step": n,

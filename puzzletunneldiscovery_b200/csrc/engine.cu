@@ -19,6 +19,9 @@
 #include <vector>
 #if defined(__x86_64__)
 #include <emmintrin.h>
+#include <sched.h>
+#include <sys/mman.h>
+#include <map>
 #endif
 
 #include "../../include/osrgpu.h"
@@ -230,9 +233,67 @@ void free_slot(Slot& s) {
   s = Slot();
 }
 
+// NUMA node the device's PCIe root hangs off (sysfs), -1 when unknown.
+static int device_numa_node(int dev) {
+  if (const char* e = getenv("OSR_NUMA_NODE")) return atoi(e);   // override (guests that hide the topology; tests)
+  char id[32] = {0};
+  if (cudaDeviceGetPCIBusId(id, (int)sizeof id, dev) != cudaSuccess) {
+    cudaGetLastError();
+    return -1;
+  }
+  for (char* c = id; *c; c++) *c = (char)tolower(*c);
+  FILE* f = fopen((std::string("/sys/bus/pci/devices/") + id + "/numa_node").c_str(), "r");
+  if (!f) return -1;
+  int node = -1;
+  if (fscanf(f, "%d", &node) != 1) node = -1;
+  fclose(f);
+  return node;
+}
+
+// While alive the calling thread runs on the CPUs of the device's NUMA node, so that host memory allocated and first
+// touched inside lands next to the GPU's PCIe root: a DMA from the other socket's memory crosses the inter-socket link
+// and runs at about half the PCIe rate (what the slowest rank of a 4- or 8-process run was bound by).  Only the
+// calling thread's mask changes, and it is restored.  OSR_NO_NUMA_LOCAL=1 turns it off.
+struct NumaScope {
+  cpu_set_t old;
+  bool changed = false;
+  int node = -1;
+  explicit NumaScope(int dev) {
+    static const bool off = getenv("OSR_NO_NUMA_LOCAL") != nullptr;
+    if (off) return;
+    node = device_numa_node(dev);
+    if (node < 0 || sched_getaffinity(0, sizeof old, &old) != 0) return;
+    char path[96];
+    snprintf(path, sizeof path, "/sys/devices/system/node/node%d/cpulist", node);
+    FILE* f = fopen(path, "r");
+    if (!f) return;
+    cpu_set_t want;
+    CPU_ZERO(&want);
+    int a = 0, b = 0;
+    while (fscanf(f, "%d", &a) == 1) {   // "0-31,64-95"
+      b = a;
+      int c = fgetc(f);
+      if (c == '-') {
+        if (fscanf(f, "%d", &b) != 1) break;
+        c = fgetc(f);
+      }
+      for (int k = a; k <= b && k < CPU_SETSIZE; k++)
+        if (CPU_ISSET(k, &old)) CPU_SET(k, &want);
+      if (c != ',') break;
+    }
+    fclose(f);
+    if (CPU_COUNT(&want) == 0) return;
+    changed = sched_setaffinity(0, sizeof want, &want) == 0;
+  }
+  ~NumaScope() {
+    if (changed) sched_setaffinity(0, sizeof old, &old);
+  }
+};
+
 int init_slot(osr_world* w, Slot& s, int dev) {
   s.dev = dev;
   CU(cudaSetDevice(dev));
+  NumaScope numa(dev);   // the slot's page-locked buffers (staging ring, mapped small-call buffers) next to the GPU
   CU(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
   CU(cudaStreamCreateWithFlags(&s.stream2, cudaStreamNonBlocking));
   CU(cudaStreamCreateWithFlags(&s.stream3, cudaStreamNonBlocking));
@@ -1402,17 +1463,61 @@ int osr_is_valid_transitions_device_noalloc(osr_world* w, const double* d_from, 
 
 // Page-locked host memory for sample / result arrays: a host call whose buffers are pageable is bounded by the
 // driver's staging copies (~10 GB/s), one on pinned buffers by PCIe.
+// The block is anonymous memory first touched on the NUMA node of the CURRENT device (NumaScope) and then page-locked
+// with cudaHostRegister; cudaHostAlloc is the fallback.
+static std::mutex g_host_mu;
+static std::map<void*, size_t> g_host_blocks;   // registered blocks -> mapped size
 void* osr_host_alloc(size_t bytes) {
-  void* p = nullptr;
-  if (bytes == 0 || cudaHostAlloc(&p, bytes, cudaHostAllocPortable) != cudaSuccess) {
-    cudaGetLastError();
-    g_err = "cudaHostAlloc failed";
+  if (bytes == 0) {
+    g_err = "osr_host_alloc: zero bytes";
     return nullptr;
   }
-  return p;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) {
+    cudaGetLastError();
+    g_err = "osr_host_alloc: no CUDA device";
+    return nullptr;
+  }
+  {
+    NumaScope numa(dev);
+    if (numa.changed) {
+      const size_t len = (bytes + 4095) & ~(size_t)4095;
+      void* p = mmap(nullptr, len, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS, -1, 0);
+      if (p != MAP_FAILED) {
+        memset(p, 0, len);   // first touch: on this thread's (the device's) node
+        if (cudaHostRegister(p, len, cudaHostRegisterPortable) == cudaSuccess) {
+          std::lock_guard<std::mutex> lk(g_host_mu);
+          g_host_blocks[p] = len;
+          return p;
+        }
+        cudaGetLastError();
+        munmap(p, len);
+      }
+    }
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, bytes, cudaHostAllocPortable) == cudaSuccess) return p;
+  }
+  cudaGetLastError();
+  g_err = "cudaHostAlloc failed";
+  return nullptr;
 }
 void osr_host_free(void* p) {
-  if (p) cudaFreeHost(p);
+  if (!p) return;
+  size_t len = 0;
+  {
+    std::lock_guard<std::mutex> lk(g_host_mu);
+    auto it = g_host_blocks.find(p);
+    if (it != g_host_blocks.end()) {
+      len = it->second;
+      g_host_blocks.erase(it);
+    }
+  }
+  if (len) {
+    cudaHostUnregister(p);
+    munmap(p, len);
+  } else {
+    cudaFreeHost(p);
+  }
 }
 
 void* osr_stream(osr_world* w) { return (w && !w->slots.empty()) ? (void*)w->slots[0].stream : nullptr; }

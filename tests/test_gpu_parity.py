@@ -882,6 +882,25 @@ def test_pinned_host_arrays_give_the_same_labels(uw_org):
 
 
 @pytest.mark.gpu
+def test_numa_local_host_blocks_give_the_same_labels(uw_org, monkeypatch):
+    """osr_host_alloc puts a block on the NUMA node of the current GPU (anonymous memory first touched there, then
+    cudaHostRegister) when sysfs names the node; this pool's guests hide it (numa_node = -1, one node), so the path
+    is forced with OSR_NUMA_NODE=0: same labels as pageable arrays, blocks can be freed and made again."""
+    from puzzletunneldiscovery_b200 import pyosr
+    monkeypatch.setenv("OSR_NUMA_NODE", "0")
+    q = W.random_states(200003, seed=96)
+    want = uw_org.is_valid_states(q)
+    for _ in range(3):
+        qp = pyosr.pinned_empty((len(q), 7))
+        line = [l for l in open("/proc/self/numa_maps") if int(l.split()[0], 16) == qp.ctypes.data]
+        assert line and "file=" not in line[0]      # the registered anonymous mapping, not cudaHostAlloc's
+        qp[:] = q
+        out = pyosr.pinned_empty(len(q), np.uint8)
+        assert np.array_equal(uw_org.is_valid_states(qp, out=out), want)
+        del qp, out
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("n", [65536, 65537, 69631, 73729, 131071, 200003, 1048576 + 4097])
 def test_host_call_chunk_schedule_ragged_sizes(uw_org, n):
     """The host validity call uploads in chunks (64 Ki states, then half of what is left, down to 8 Ki) under ONE
