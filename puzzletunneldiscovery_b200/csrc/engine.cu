@@ -5,6 +5,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <thread>
 #include <cmath>
 #include <condition_variable>
@@ -457,9 +458,16 @@ int check_device_error(osr_world* w, Slot& s) {
 namespace {
 // the four tree-size variants of K1 x {resident input, stream-fed input}
 template <bool FEED, typename T>
-void launch_dfs_variant(const Slot& s, const osr::DfsParams& D, const T* d_q, long long n, uint8_t* d_out,
+void launch_dfs_variant(const Slot& s, const osr::DfsParams& D0, const T* d_q, long long n, uint8_t* d_out,
                         cudaStream_t st, int grid = 0) {
   const int g = grid > 0 ? grid : s.num_sms;   // persistent: one block per SM (fewer for the small-call path)
+  // the last (warps x tail_group) states go out in groups of tail_group (DfsParams::tail_start); OSR_K1_TAIL_GROUP=0
+  // = groups of 32 to the end (A/B)
+  static const int tail_group = [] { const char* e = getenv("OSR_K1_TAIL_GROUP"); return e ? std::max(0, std::min(32, atoi(e))) : 8; }();
+  osr::DfsParams D = D0;
+  D.tail_group = tail_group > 0 ? tail_group : 32;
+  const long long tail = (long long)g * (osr::DFS_THREADS / 32) * D.tail_group;
+  D.tail_start = tail_group > 0 ? std::max(0LL, n - tail) / 32 * 32 : (n + 31) / 32 * 32;
   if (s.dfs_variant == 0 && s.dfs_all_smem)
     osr::k_valid_dfs<uint32_t, 32, true, FEED, T><<<g, osr::DFS_THREADS, s.dfs_smem_bytes, st>>>(D, d_q, n, d_out);
   else if (s.dfs_variant == 0)
@@ -1033,7 +1041,15 @@ static int valid_states_host_impl(osr_world* w, const T* q, int64_t n, uint8_t* 
       // is no faster than the kernel and a late start would show), then every chunk is half of what is left, down
       // to 8 Ki states -- 9 chunks for 2^20 states.  OSR_HOST_CHUNK set = uniform chunks of that size (A/B).
       static const bool uniform_chunks = getenv("OSR_HOST_CHUNK") != nullptr;
-      const int64_t min_chunk = 8192;
+      static const bool trace = getenv("OSR_FEED_TRACE") != nullptr;   // development: where a call's time goes
+      static cudaEvent_t tr[3] = {nullptr, nullptr, nullptr};
+      const auto host_t0 = std::chrono::steady_clock::now();
+      if (trace) {
+        for (auto& e : tr)
+          if (!e) CU(cudaEventCreate(&e));
+        CU(cudaEventRecord(tr[0], s.stream2));
+      }
+      static const int64_t min_chunk = [] { const char* e = getenv("OSR_FEED_MIN_CHUNK"); return e ? std::max<int64_t>(1024, atoll(e)) : (int64_t)8192; }();
       int64_t first_len = 0;
       int c = 0;
       for (int64_t c0 = 0, len = 0; c0 < m; c0 += len, c++) {
@@ -1048,6 +1064,13 @@ static int valid_states_host_impl(osr_world* w, const T* q, int64_t n, uint8_t* 
         CU(cudaEventRecord(s.feed_ev[c], s.stream2));
         CU(cudaStreamWaitEvent(s.stream3, s.feed_ev[c], 0));
         s.h_ready[c] = c0 + len;
+        static const bool last_direct = getenv("OSR_FEED_NO_DIRECT_LAST") == nullptr;
+        if (last_direct && c0 + len == m && wv) {
+          // the LAST chunk's word also goes out on the copy stream itself, right behind the copy: nothing follows it
+          // there, and the hop to the third stream (event, wait) delays what the whole call then waits for.  (An older
+          // value landing later from the third stream is repaired by that stream's own final write below.)
+          wv(s.stream2, (unsigned long long)(uintptr_t)s.ready, (unsigned long long)m, 0);
+        }
         if (!wv || wv(s.stream3, (unsigned long long)(uintptr_t)s.ready, (unsigned long long)(c0 + len), 0) != 0)
           CU(cudaMemcpyAsync(s.ready, s.h_ready + c, sizeof(long long), cudaMemcpyHostToDevice, s.stream3));
       }
@@ -1060,6 +1083,27 @@ static int valid_states_host_impl(osr_world* w, const T* q, int64_t n, uint8_t* 
       CU(cudaMemcpyAsync(out + lo, s.out[0].p, (size_t)m, cudaMemcpyDeviceToHost, s.stream));
       CU(cudaEventRecord(s.evq, s.stream3));
       CU(cudaStreamWaitEvent(s.stream, s.evq, 0));
+      if (trace) {
+        CU(cudaEventRecord(tr[1], s.stream2));
+        CU(cudaEventRecord(tr[2], s.stream));
+        const auto host_t1 = std::chrono::steady_clock::now();
+        CU(cudaStreamSynchronize(s.stream));
+        CU(cudaStreamSynchronize(s.stream2));
+        const auto host_t2 = std::chrono::steady_clock::now();
+        float up = 0, k0 = 0, ks = 0, tail = 0, d2h = 0, all = 0;
+        cudaEventElapsedTime(&up, tr[0], tr[1]);
+        cudaEventElapsedTime(&k0, tr[0], s.ev0);
+        cudaEventElapsedTime(&ks, s.ev0, s.ev1);
+        cudaEventElapsedTime(&tail, tr[1], s.ev1);
+        cudaEventElapsedTime(&d2h, s.ev1, tr[2]);
+        cudaEventElapsedTime(&all, tr[0], tr[2]);
+        fprintf(stderr, "[feed trace] m=%lld chunks=%d: host enqueue %.0f us, host total %.0f us | device: upload %.0f us, "
+                "kernel starts +%.0f us, kernel span %.0f us, last chunk -> kernel end %.0f us, kernel end -> labels on "
+                "host %.0f us, first copy -> labels %.0f us\n", (long long)m, c,
+                std::chrono::duration<double, std::micro>(host_t1 - host_t0).count(),
+                std::chrono::duration<double, std::micro>(host_t2 - host_t0).count(), up * 1e3, k0 * 1e3, ks * 1e3,
+                tail * 1e3, d2h * 1e3, all * 1e3);
+      }
       continue;
     }
     if (nchunks > 1) {  // stream2 joins after whatever the main stream still has queued

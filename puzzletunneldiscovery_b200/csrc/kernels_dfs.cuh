@@ -39,9 +39,20 @@ struct DfsParams {
   const long long* ready;
   long long ready_floor;  // states certainly resident when the kernel starts (the launch is ordered behind them)
   unsigned long long feed_timeout_ns;  // give up waiting for an upload after this long (%globaltimer; OSR_FEED_TIMEOUT_S)
+  // Work distribution: the counter hands out GROUPS of states -- 32 states below tail_start (a multiple of 32),
+  // tail_group states from there on.  The last (warps x tail_group) states are spread over every warp of the grid, a
+  // few states each, and the free lanes of a warp share its poses at once: the end of a launch (and the end of a
+  // stream-fed call, which waits for its last chunk with every warp idle) costs ~30 us instead of ~85.
+  long long tail_start;
+  int tail_group;
 };
 
 // Tunables (the -D overrides exist for the A/B builds of scripts/k1_variants.sh; defaults = measured best)
+#ifdef OSR_FEED_BLOCKING
+constexpr bool kFeedDefer = false;   // A/B: a warp waits for its next group's upload with its poses stalled
+#else
+constexpr bool kFeedDefer = true;
+#endif
 #ifndef OSR_LEAF_FLUSH
 #define OSR_LEAF_FLUSH 16
 #endif
@@ -287,6 +298,8 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
   // warp state (uniform)
   int pend_n = 0, nleaf = 0, since_flush = 0;
   bool exhausted = false, draining_leaf = false, steal_mode = false;
+  int held = -1, held_cnt = 0;   // stream-fed launches: a group taken from the counter whose states have not arrived
+  unsigned poll_tick = 0;
   unsigned n_bv = 0, n_leaf = 0, n_fp64 = 0;
   unsigned long long nposes = 0;
   if (FEED) M.ready_seen = (int)min(P.ready_floor, 0x7fffffffLL);  // same value from every lane
@@ -314,13 +327,46 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
     if (idle != 0) {
       if (pend_n == 0 && !exhausted) {  // prepare the next 32 states with the whole warp
         unsigned long long base = 0;
-        if (lane == 0) base = atomicAdd(P.work_counter, 32ull);
-        base = __shfl_sync(FULL, base, 0);
-        if (FEED && (long long)base < n) {
+        int cnt = 32;
+        bool defer = false;
+        if (FEED && held >= 0) {   // the group taken earlier, whose states had not arrived yet
+          base = (unsigned long long)held;
+          cnt = held_cnt;
+        } else {
+          if (lane == 0) base = atomicAdd(P.work_counter, 1ull);   // a group id (DfsParams::tail_start)
+          base = __shfl_sync(FULL, base, 0);
+          const unsigned long long bulk = (unsigned long long)(P.tail_start >> 5);
+          if (base < bulk) base <<= 5;
+          else {
+            cnt = P.tail_group;
+            base = (unsigned long long)P.tail_start + (base - bulk) * (unsigned)cnt;
+          }
+        }
+        if (FEED && kFeedDefer && (long long)base < n && idle != FULL) {
+          // Some lanes still hold poses: do not stop them for an upload.  One look at the word every 8th visit; if
+          // the group's states are not there yet it is kept and the traversal goes on.  (The upload is slower than
+          // the kernel, so warps are here most of the time: waiting with poses half done is what the END of a call
+          // -- last chunk in, every warp still owing its stalled poses -- was made of.)
+          const long long need = min((long long)base + cnt, n);
+          long long seen = __shfl_sync(FULL, (long long)M.ready_seen, 0);
+          if (seen < need && (poll_tick++ & 7) == 0) {
+            long long v;
+            asm volatile("ld.acquire.sys.global.s64 %0, [%1];" : "=l"(v) : "l"(P.ready) : "memory");
+            seen = __shfl_sync(FULL, v, 0);
+            M.ready_seen = (int)min(seen, 0x7fffffffLL);
+          }
+          if (seen < need) {
+            held = (int)base;
+            held_cnt = cnt;
+            defer = true;
+          }
+          __syncwarp();
+        }
+        if (FEED && !defer && (long long)base < n) {
           // Wait until the states [base, base+32) have been uploaded.  Written so that control flow stays
           // warp-uniform (every lane polls, the value of lane 0 decides): a one-lane polling loop or an
           // out-of-line call here costs the whole traversal loop its convergence (+25 % instructions, +8 % time).
-          const long long need = min((long long)base + 32, n);
+          const long long need = min((long long)base + cnt, n);
           long long seen = __shfl_sync(FULL, (long long)M.ready_seen, 0);
           unsigned long long t0 = 0;   // the wait is bounded in TIME (a poll count depends on the clock and on tools)
           for (int spins = 0; seen < need; spins++) {
@@ -343,10 +389,12 @@ __global__ void __launch_bounds__(DFS_THREADS, 1)
           }
           __syncwarp();
         }
-        if ((long long)base >= n) exhausted = true;
+        if (FEED && !defer) held = -1;
+        if (defer) {
+        } else if ((long long)base >= n) exhausted = true;
         else {
           long long i = (long long)base + lane;
-          bool have = i < n;
+          bool have = lane < cnt && i < n;
           unsigned hm = __ballot_sync(FULL, have);
           // the root box test runs here, 32 poses at a time: poses separated at the root are free and never
           // occupy a lane; the others are compacted into the buffer of prepared poses
