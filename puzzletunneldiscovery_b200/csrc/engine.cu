@@ -1064,13 +1064,6 @@ static int valid_states_host_impl(osr_world* w, const T* q, int64_t n, uint8_t* 
         CU(cudaEventRecord(s.feed_ev[c], s.stream2));
         CU(cudaStreamWaitEvent(s.stream3, s.feed_ev[c], 0));
         s.h_ready[c] = c0 + len;
-        static const bool last_direct = getenv("OSR_FEED_NO_DIRECT_LAST") == nullptr;
-        if (last_direct && c0 + len == m && wv) {
-          // the LAST chunk's word also goes out on the copy stream itself, right behind the copy: nothing follows it
-          // there, and the hop to the third stream (event, wait) delays what the whole call then waits for.  (An older
-          // value landing later from the third stream is repaired by that stream's own final write below.)
-          wv(s.stream2, (unsigned long long)(uintptr_t)s.ready, (unsigned long long)m, 0);
-        }
         if (!wv || wv(s.stream3, (unsigned long long)(uintptr_t)s.ready, (unsigned long long)(c0 + len), 0) != 0)
           CU(cudaMemcpyAsync(s.ready, s.h_ready + c, sizeof(long long), cudaMemcpyHostToDevice, s.stream3));
       }
