@@ -85,6 +85,7 @@ struct Slot {  // one GPU
   cudaStream_t stream3 = nullptr;       // stream-fed launches: advances `ready` behind every uploaded chunk
   cudaEvent_t feed_ev[64] = {};         // one per upload chunk (created on first use)
   cudaEvent_t ev0 = nullptr, ev1 = nullptr, evp = nullptr, evq = nullptr;
+  cudaEvent_t trace_ev[3] = {nullptr, nullptr, nullptr};   // OSR_FEED_TRACE (development)
   long long* ready = nullptr;           // device word: states uploaded so far (stream-fed validity launches)
   long long* h_ready = nullptr;         // pinned source values of the copies that advance it
   char* stage = nullptr;                // pinned staging ring of host calls on pageable buffers
@@ -217,6 +218,7 @@ void free_slot(Slot& s) {
   s.clr_q0.release(); s.clr_stats.release(); s.clr_dist.release();
   s.recs.release(); s.rowrec.release(); s.seg.release(); s.faces.release(); s.cop.release(); s.bary.release();
   if (s.ev0) cudaEventDestroy(s.ev0);
+  for (auto& e : s.trace_ev) if (e) cudaEventDestroy(e);
   if (s.ev1) cudaEventDestroy(s.ev1);
   if (s.evp) cudaEventDestroy(s.evp);
   if (s.evq) cudaEventDestroy(s.evq);
@@ -1042,11 +1044,11 @@ static int valid_states_host_impl(osr_world* w, const T* q, int64_t n, uint8_t* 
       // to 8 Ki states -- 9 chunks for 2^20 states.  OSR_HOST_CHUNK set = uniform chunks of that size (A/B).
       static const bool uniform_chunks = getenv("OSR_HOST_CHUNK") != nullptr;
       static const bool trace = getenv("OSR_FEED_TRACE") != nullptr;   // development: where a call's time goes
-      static cudaEvent_t tr[3] = {nullptr, nullptr, nullptr};
+      cudaEvent_t* tr = s.trace_ev;   // per device slot
       const auto host_t0 = std::chrono::steady_clock::now();
       if (trace) {
-        for (auto& e : tr)
-          if (!e) CU(cudaEventCreate(&e));
+        for (int k = 0; k < 3; k++)
+          if (!tr[k]) CU(cudaEventCreate(&tr[k]));
         CU(cudaEventRecord(tr[0], s.stream2));
       }
       static const int64_t min_chunk = [] { const char* e = getenv("OSR_FEED_MIN_CHUNK"); return e ? std::max<int64_t>(1024, atoll(e)) : (int64_t)8192; }();
